@@ -1,0 +1,121 @@
+/* turbo_b200 -- C ABI of the B200-native GP surrogate + acquisition hot path.
+ *
+ * Drop-in boundary for mbway/turbo's surrogate / acquisition plugins.  The reference has no
+ * native code and no FFI: the arithmetic behind its plugin interface runs inside scikit-learn /
+ * SciPy.  Each entry point below therefore cites the reference (or sklearn) call it replaces;
+ * INTEGRATION.md shows the ctypes binding and the plugin classes that sit on top.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host; the caller owns all
+ *     buffers (PyTorch tensors in the shipped host layer), the library allocates nothing;
+ *   - all reals are IEEE FP64, indices int64, matrices C-contiguous row-major;
+ *   - NP = tb200_padded_n(n) = n rounded up to 128.  Padded rows/cols of a factor are the
+ *     identity, padded vector entries are 0, so padding never changes a result;
+ *   - theta is scikit-learn's log-space hyper-parameter vector
+ *       [log const (if has_const), log length_scale (d if ard else 1), log noise (if has_white)];
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream);
+ *   - return value: 0 ok; <0 argument / CUDA error (text in tb200_last_error()).  Numerical
+ *     failure of a Cholesky is reported per matrix in `info` (0 ok, k>0 = first non-positive
+ *     pivot, 1-based, as LAPACK dpotrf / sklearn:_gpr.py:590-593 & :351-362).
+ */
+#ifndef TURBO_B200_H
+#define TURBO_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { TB200_RBF = 0, TB200_MATERN12 = 1, TB200_MATERN32 = 2, TB200_MATERN52 = 3 };
+enum { TB200_EI = 0, TB200_PI = 1, TB200_UCB = 2 };
+enum { TB200_CAND_GIVEN = 0, TB200_CAND_UNIFORM = 1, TB200_CAND_LHS = 2 };
+#define TB200_MAX_D 64
+
+/* kernel family + layout of theta (sklearn:kernels.py Sum/Product/ConstantKernel/WhiteKernel/RBF/Matern) */
+typedef struct {
+    int kind;      /* TB200_RBF .. TB200_MATERN52 */
+    int d;         /* input dimensions (<= TB200_MAX_D) */
+    int ard;       /* 1: one length scale per dimension */
+    int has_const; /* ConstantKernel factor present */
+    int has_white; /* WhiteKernel term present */
+} tb200_kernel_spec;
+
+/* acquisition function of turbo/modules/acquisition_functions.py */
+typedef struct {
+    int acq;          /* TB200_EI (:336-358), TB200_PI (:225-247), TB200_UCB (:147-158) */
+    double sign;      /* scale_factor: +1 'max', -1 'min' */
+    double incumbent; /* incumbent_cost (EI/PI) */
+    double param;     /* xi (EI/PI) or beta (UCB; +inf -> sigma alone) */
+    double y_mean;    /* GaussianProcessRegressor._y_train_mean */
+    double y_std;     /* GaussianProcessRegressor._y_train_std  */
+} tb200_acq_spec;
+
+/* where candidates come from (turbo/modules/naive_selectors.py:41-46 uniform, :65-83 LHS) */
+typedef struct {
+    int mode;            /* TB200_CAND_GIVEN: read Xc; else generate on device from (seed, global index) */
+    uint64_t seed;
+    int64_t m_total;     /* LHS: number of strata = size of the whole (unsharded) candidate set */
+    double lo[TB200_MAX_D];
+    double hi[TB200_MAX_D];
+} tb200_cand_spec;
+
+int tb200_version(void);
+const char* tb200_last_error(void);
+int tb200_padded_n(int n);
+
+/* bytes of scratch the calls below need */
+size_t tb200_fit_workspace_bytes(int n, int d, int R, int with_grad);
+size_t tb200_acquire_workspace_bytes(int n, int d, int64_t batch);
+/* candidate batch size the library would pick for this n (multiple of 128) */
+int64_t tb200_default_batch(int n);
+
+/* log-marginal likelihood (and gradient w.r.t. theta) for R hyper-parameter vectors at once.
+ * Replaces GaussianProcessRegressor.log_marginal_likelihood(theta, eval_gradient=True)
+ * (sklearn:_gpr.py:541-656), called R x n_iter times by fit (:302-333) behind
+ * turbo/modules/surrogates.py:315-318.  y_n is the normalised target (:275-280).
+ * Non-PD member r: info[r] > 0, lml[r] = -inf, grad[r,:] = 0. */
+int tb200_lml_batched(const double* X, const double* y_n, int n, const tb200_kernel_spec* spec_host,
+                      const double* theta, int R, double jitter, int with_grad,
+                      double* lml, double* grad, int* info, void* work, size_t work_bytes, void* stream);
+
+/* final factorisation at one theta: what fit() keeps for predict (sklearn:_gpr.py:349-367).
+ * Outputs: XsT (d x NP) = training inputs / length_scale, transposed; Linv (NP x NP) = inverse of
+ * the Cholesky factor of K + jitter I (lower); alpha (NP) = K^-1 y_n; lml (1); Ldiag (NP) = diag(L). */
+int tb200_factor(const double* X, const double* y_n, int n, const tb200_kernel_spec* spec_host,
+                 const double* theta, double jitter, double* XsT, double* Linv, double* alpha,
+                 double* Ldiag, double* lml, int* info, void* work, size_t work_bytes, void* stream);
+
+/* fused predict + acquisition + argmax over candidates [index_base, index_base + m).
+ * Replaces acq(random_x) + argsort of turbo/modules/auxiliary_optimisers.py:60-66, i.e.
+ * EI/PI/UCB.FunctionInstance.__call__ -> ModelInstance.predict -> sklearn predict
+ * (sklearn:_gpr.py:446-500).  Optional outputs (NULL to skip; indexed by local candidate 0..m-1):
+ * mu_out, sigma_out, acq_out.  best_val/best_idx (1 each) are READ-MODIFY-WRITE: initialise to
+ * (-inf, -1) with tb200_best_reset; ties keep the lowest global index; NaN never wins. */
+int tb200_acquire(const double* Xc, int64_t m, int64_t index_base, const tb200_cand_spec* cand_host,
+                  const double* XsT, const double* Linv, const double* alpha, int n,
+                  const tb200_kernel_spec* spec_host, const double* theta,
+                  const tb200_acq_spec* acq_host, double* mu_out, double* sigma_out, double* acq_out,
+                  double* best_val, int64_t* best_idx, int64_t batch, void* work, size_t work_bytes,
+                  void* stream);
+int tb200_best_reset(double* best_val, int64_t* best_idx, void* stream);
+
+/* write candidates [index_base, index_base+m) of a generated set into out (m x d) */
+int tb200_generate_candidates(const tb200_cand_spec* cand_host, int d, int64_t index_base, int64_t m,
+                              double* out, void* stream);
+
+/* measured FP64 peaks of this device (roofline denominators for the DMMA kernels):
+ * runs register-resident DMMA.8x8x4 / DFMA loops on every SM for ~`ms` milliseconds each. */
+int tb200_fp64_peak(double ms, double* dmma_tflops_host, double* dfma_tflops_host);
+
+/* plain C = alpha*op(A)*op(B) + beta*C on the library's DMMA GEMM (testing / roofline runs);
+ * M,N multiples of 128, K multiple of 16; ta/tb: 0 = [m][k] / [k][n] storage, 1 = transposed. */
+int tb200_dgemm(int ta, int tb, int M, int N, int K, double alpha, const double* A, int lda,
+                const double* B, int ldb, double beta, double* C, int ldc, void* stream);
+
+/* number of kernel launches issued by this library since load (bench.py's gpu_launches) */
+int64_t tb200_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

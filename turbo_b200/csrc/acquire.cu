@@ -1,0 +1,419 @@
+// Predict + acquisition + argmax over candidate batches (the headline path).
+//
+// Replaces acq(random_x) + argsort of turbo/modules/auxiliary_optimisers.py:60-66:
+//   EI/PI/UCB.FunctionInstance.__call__ (acquisition_functions.py:336-358, :225-247, :147-158)
+//   -> ModelInstance.predict (surrogates.py:332-338) -> sklearn predict (sklearn:_gpr.py:446-500).
+//
+// Per batch of `batch` candidates (a multiple of 128 sized so its scratch stays in L2):
+//   1. [optional] generate the candidates on device from (seed, global index)
+//   2. kstar_mean_kernel : Ks[c][j] = sf2 * g(|xc/l - xj/l|) into an L2-resident scratch, and the
+//                          predictive mean  mu_c = sum_j Ks[c][j] alpha_j   (fixed-order reduction)
+//   3. DMMA GEMM         : V = Linv * Ks^T (lower-triangular A) with a column sum-of-squares
+//                          epilogue -> partial[row tile][c]   (V itself is never stored)
+//   4. acquire_epilogue  : var = k** - sum partial, clamp, de-normalise, EI/PI/UCB, running argmax
+// The candidate matrix, K*, V, mu, sigma and the acquisition values are not written to HBM unless
+// the caller asks for them (mu_out / sigma_out / acq_out).
+#include "gemm_f64.cuh"
+
+namespace tb200 {
+
+// ---------------------------------------------------------------------------------------------
+// counter-based candidate generation (Philox4x32-10), identical for any sharding of the index range
+// ---------------------------------------------------------------------------------------------
+__host__ __device__ inline void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+                                              uint32_t k1, uint32_t out[4]) {
+    for (int round = 0; round < 10; ++round) {
+        const uint64_t p0 = (uint64_t)0xD2511F53u * c0;
+        const uint64_t p1 = (uint64_t)0xCD9E8D57u * c2;
+        const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
+        const uint32_t n1 = (uint32_t)p1;
+        const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+        const uint32_t n3 = (uint32_t)p0;
+        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+        k0 += 0x9E3779B9u;
+        k1 += 0xBB67AE85u;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+// uniform double in [0,1) with 53 random bits for (global index, dimension, stream)
+__host__ __device__ inline double uniform01(uint64_t seed, uint64_t idx, uint32_t dim, uint32_t stream) {
+    uint32_t o[4];
+    philox4x32_10((uint32_t)idx, (uint32_t)(idx >> 32), dim, stream, (uint32_t)seed, (uint32_t)(seed >> 32), o);
+    const uint64_t bits = ((uint64_t)o[0] << 21) ^ (uint64_t)(o[1] >> 11);  // 53 bits
+    return (double)(bits & ((1ull << 53) - 1)) * (1.0 / 9007199254740992.0);
+}
+
+// keyed bijection of [0, m): 4-round Feistel on the enclosing power-of-two domain + cycle walking
+__host__ __device__ inline uint64_t permute_index(uint64_t seed, uint32_t dim, uint64_t i, uint64_t m) {
+    int bits = 2;
+    while ((1ull << bits) < m) ++bits;
+    if (bits & 1) ++bits;
+    const int half = bits / 2;
+    const uint64_t mask = (1ull << half) - 1;
+    uint64_t x = i;
+    do {
+        uint64_t l = x >> half, r = x & mask;
+        for (uint32_t round = 0; round < 4; ++round) {
+            uint32_t o[4];
+            philox4x32_10((uint32_t)r, (uint32_t)(r >> 32), dim, 0x5eed0000u + round, (uint32_t)seed,
+                          (uint32_t)(seed >> 32), o);
+            const uint64_t f = (((uint64_t)o[0] << 32) | o[1]) & mask;
+            const uint64_t nl = r, nr = l ^ f;
+            l = nl; r = nr;
+        }
+        x = (l << half) | r;
+    } while (x >= m);
+    return x;
+}
+
+struct CandGen {
+    int mode;
+    uint64_t seed;
+    int64_t m_total;
+    double lo[TB200_MAX_D];
+    double hi[TB200_MAX_D];
+};
+
+inline CandGen make_gen(const tb200_cand_spec& c, int d) {
+    CandGen g;
+    g.mode = c.mode; g.seed = c.seed; g.m_total = c.m_total;
+    for (int k = 0; k < TB200_MAX_D; ++k) { g.lo[k] = k < d ? c.lo[k] : 0.0; g.hi[k] = k < d ? c.hi[k] : 0.0; }
+    return g;
+}
+
+__host__ __device__ inline double gen_coord(const CandGen& g, double lo, double hi, uint64_t idx, uint32_t dim) {
+    const double u = uniform01(g.seed, idx, dim, 0u);
+    if (g.mode == TB200_CAND_UNIFORM) return lo + (hi - lo) * u;
+    // LHS (naive_selectors.py:75-78): lo + range * (stratum + u) / m with a per-dimension permutation
+    const uint64_t s = permute_index(g.seed, dim, idx, (uint64_t)g.m_total);
+    return lo + (hi - lo) * ((double)s + u) / (double)g.m_total;
+}
+
+__global__ void generate_candidates_kernel(const __grid_constant__ CandGen g, int d, int64_t index_base, int64_t m,
+                                           double* __restrict__ out) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= m * d) return;
+    const int64_t c = e / d;
+    const int k = (int)(e - c * d);
+    out[e] = gen_coord(g, g.lo[k], g.hi[k], (uint64_t)(index_base + c), (uint32_t)k);
+}
+
+// ---------------------------------------------------------------------------------------------
+// K* rows and predictive mean.  CPB candidates per CTA; each thread walks training points j.
+// ---------------------------------------------------------------------------------------------
+constexpr int CPB = 8;
+
+__global__ void __launch_bounds__(256) kstar_mean_kernel(const double* __restrict__ Xc, int64_t m_valid,
+                                                         const double* __restrict__ XsT, int n, int NP,
+                                                         tb200_kernel_spec spec, const double* __restrict__ theta,
+                                                         const double* __restrict__ alpha, double* __restrict__ Ks,
+                                                         double* __restrict__ mean) {
+    extern __shared__ double sh[];  // xc[CPB][d] scaled candidates, red[8][CPB]
+    const int d = spec.d;
+    double* xc = sh;
+    double* red = sh + CPB * d;
+    const int64_t c0 = (int64_t)blockIdx.x * CPB;
+    for (int e = threadIdx.x; e < CPB * d; e += blockDim.x) {
+        const int c = e / d, k = e - c * d;
+        const int64_t ci = c0 + c;
+        // sklearn divides the points by the length scale before cdist (kernels.py:1566, :1720)
+        xc[e] = (ci < m_valid) ? Xc[ci * d + k] / length_scale(spec, theta, k) : 0.0;
+    }
+    __syncthreads();
+    const Hyper h = unpack_hyper(spec, theta);
+    double msum[CPB];
+#pragma unroll
+    for (int c = 0; c < CPB; ++c) msum[c] = 0.0;
+    for (int j = threadIdx.x; j < NP; j += blockDim.x) {
+        double r2[CPB];
+#pragma unroll
+        for (int c = 0; c < CPB; ++c) r2[c] = 0.0;
+        for (int k = 0; k < d; ++k) {
+            const double xt = XsT[(long)k * NP + j];
+#pragma unroll
+            for (int c = 0; c < CPB; ++c) {
+                const double df = xc[c * d + k] - xt;
+                r2[c] += df * df;
+            }
+        }
+        const double a = alpha[j];
+        const bool live = j < n;
+#pragma unroll
+        for (int c = 0; c < CPB; ++c) {
+            const double kv = live ? h.sf2 * shape_fn(spec.kind, r2[c]) : 0.0;
+            Ks[(c0 + c) * NP + j] = kv;
+            msum[c] += kv * a;
+        }
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int c = 0; c < CPB; ++c) {
+        const double v = warp_sum(msum[c]);
+        if (lane == 0) red[warp * CPB + c] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < CPB) {
+        double t = 0.0;
+        for (int w = 0; w < 8; ++w) t += red[w * CPB + threadIdx.x];
+        mean[c0 + threadIdx.x] = t;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// variance, acquisition value and running argmax for one batch (single CTA)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double norm_cdf(double z) { return 0.5 * erfc(-z * 0.7071067811865476); }
+__device__ __forceinline__ double norm_pdf(double z) { return exp(-z * z / 2.0) / 2.5066282746310002; }
+
+__device__ __forceinline__ bool better(double v, int64_t i, double bv, int64_t bi) {
+    // NaN never wins; ties keep the lowest index; (−inf, −1) is the empty state
+    if (isnan(v)) return false;
+    if (bi < 0) return true;
+    return v > bv || (v == bv && i < bi);
+}
+
+__global__ void __launch_bounds__(1024) acquire_epilogue_kernel(
+    const double* __restrict__ mean, const double* __restrict__ partial, int ntiles, long ldp, int64_t batch,
+    int64_t m_valid, int64_t local_base, int64_t index_base, tb200_kernel_spec spec,
+    const double* __restrict__ theta, tb200_acq_spec acq,
+    double* __restrict__ mu_out, double* __restrict__ sigma_out, double* __restrict__ acq_out,
+    double* __restrict__ best_val, int64_t* __restrict__ best_idx) {
+    __shared__ double sv[32];
+    __shared__ int64_t si[32];
+    double bv = -INFINITY;
+    int64_t bi = -1;
+    const Hyper hy = unpack_hyper(spec, theta);
+    const double prior_var = hy.sf2 + hy.noise;  // kernel_.diag(X): const*1 + white (kernels.py:1315, :1438)
+    for (int64_t c = threadIdx.x; c < batch && c < m_valid; c += blockDim.x) {
+        double vv = 0.0;
+        for (int t = 0; t < ntiles; ++t) vv += partial[(long)t * ldp + c];
+        double var = prior_var - vv;                // kernel_.diag(X) - einsum(V.T, V)
+        if (var < 0.0) var = 0.0;                   // sklearn:_gpr.py:485-491
+        var = var * (acq.y_std * acq.y_std);        // :494
+        const double sigma = sqrt(var);
+        const double mu = acq.y_std * mean[c] + acq.y_mean;  // :450
+        double a;
+        if (acq.acq == TB200_UCB) {
+            a = isinf(acq.param) ? sigma : acq.sign * mu + acq.param * sigma;
+        } else if (sigma != 0.0) {
+            const double diff = acq.sign * (mu - acq.incumbent) - acq.param;
+            const double Z = diff / sigma;
+            a = (acq.acq == TB200_PI) ? norm_cdf(Z) : diff * norm_cdf(Z) + sigma * norm_pdf(Z);
+        } else {
+            a = 0.0;
+        }
+        const int64_t lc = local_base + c;
+        if (mu_out) mu_out[lc] = mu;
+        if (sigma_out) sigma_out[lc] = sigma;
+        if (acq_out) acq_out[lc] = a;
+        const int64_t gi = index_base + lc;
+        if (better(a, gi, bv, bi)) { bv = a; bi = gi; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double ov = __shfl_xor_sync(0xffffffffu, bv, o);
+        const int64_t oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (oi >= 0 && better(ov, oi, bv, bi)) { bv = ov; bi = oi; }
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) { sv[warp] = bv; si[warp] = bi; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double gv = *best_val;
+        int64_t gi = *best_idx;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w)
+            if (si[w] >= 0 && better(sv[w], si[w], gv, gi)) { gv = sv[w]; gi = si[w]; }
+        *best_val = gv;
+        *best_idx = gi;
+    }
+}
+
+__global__ void best_reset_kernel(double* best_val, int64_t* best_idx) {
+    *best_val = -INFINITY;
+    *best_idx = -1;
+}
+
+// ---------------------------------------------------------------------------------------------
+// FP64 peak microbenchmarks: register-resident DMMA / DFMA chains on every SM
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) dmma_peak_kernel(double* out, int iters) {
+    double c[16][2];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) c[i][0] = c[i][1] = 0.0;
+    const double a = 1.0 + threadIdx.x * 1e-9, b = 1.0 - threadIdx.x * 1e-9;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) dmma884(c[i][0], c[i][1], a, b);
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) s += c[i][0] + c[i][1];
+    if (s == 123.456) out[0] = s;
+}
+
+__global__ void __launch_bounds__(256) dfma_peak_kernel(double* out, int iters) {
+    double c[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) c[i] = i;
+    const double a = 1.0 + threadIdx.x * 1e-9, b = 1e-9;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) c[i] = fma(c[i], a, b);
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) s += c[i];
+    if (s == 123.456) out[0] = s;
+}
+
+struct AcqBuffers {
+    double* cand;     // [batch][d]   generated candidates
+    double* Ks;       // [batch][NP]
+    double* mean;     // [batch]
+    double* partial;  // [NB][batch]
+};
+
+static size_t a256(size_t b) { return (b + 255) / 256 * 256; }
+
+static size_t acquire_layout(int n, int d, int64_t batch, AcqBuffers* ab, char* base) {
+    const size_t NP = pad_n(n), NB = NP / TILE;
+    size_t off = 0;
+    auto take = [&](size_t bytes) {
+        char* ptr = base ? base + off : nullptr;
+        off += a256(bytes);
+        return reinterpret_cast<double*>(ptr);
+    };
+    double* cand = take(sizeof(double) * batch * d);
+    double* Ks = take(sizeof(double) * batch * NP);
+    double* mean = take(sizeof(double) * batch);
+    double* partial = take(sizeof(double) * NB * batch);
+    if (ab) { ab->cand = cand; ab->Ks = Ks; ab->mean = mean; ab->partial = partial; }
+    return off;
+}
+
+}  // namespace tb200
+
+using namespace tb200;
+
+extern "C" {
+
+int64_t tb200_default_batch(int n) {
+    // keep Ks (batch x NP doubles) around 64 MB so it lives in the 126 MB L2 next to the streamed
+    // Linv tiles, but never below 256 candidates (tile balance) nor above 4096
+    const int64_t NP = pad_n(n);
+    int64_t b = (64ll << 20) / (NP * 8);
+    b = b / 128 * 128;
+    if (b < 256) b = 256;
+    if (b > 4096) b = 4096;
+    return b;
+}
+
+size_t tb200_acquire_workspace_bytes(int n, int d, int64_t batch) {
+    if (batch <= 0) batch = tb200_default_batch(n);
+    return acquire_layout(n, d, batch, nullptr, nullptr);
+}
+
+int tb200_best_reset(double* best_val, int64_t* best_idx, void* stream) {
+    TB_CHECK(best_val && best_idx, "NULL pointer argument");
+    TB_LAUNCH(best_reset_kernel, dim3(1), dim3(1), 0, (cudaStream_t)stream, best_val, best_idx);
+    return 0;
+}
+
+int tb200_generate_candidates(const tb200_cand_spec* cand, int d, int64_t index_base, int64_t m, double* out,
+                              void* stream) {
+    TB_CHECK(cand && out, "NULL pointer argument");
+    TB_CHECK(cand->mode == TB200_CAND_UNIFORM || cand->mode == TB200_CAND_LHS, "generator mode required");
+    TB_CHECK(d >= 1 && d <= TB200_MAX_D, "d out of range");
+    TB_CHECK(cand->mode != TB200_CAND_LHS || cand->m_total >= index_base + m, "LHS: m_total smaller than the range");
+    if (m <= 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    const CandGen g = make_gen(*cand, d);
+    const int64_t total = m * d;
+    TB_LAUNCH(generate_candidates_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, st, g, d, index_base, m,
+              out);
+    return 0;
+}
+
+int tb200_acquire(const double* Xc, int64_t m, int64_t index_base, const tb200_cand_spec* cand, const double* XsT,
+                  const double* Linv, const double* alpha, int n, const tb200_kernel_spec* spec, const double* theta,
+                  const tb200_acq_spec* acq, double* mu_out, double* sigma_out, double* acq_out, double* best_val,
+                  int64_t* best_idx, int64_t batch, void* work, size_t work_bytes, void* stream) {
+    TB_CHECK(spec && acq && XsT && Linv && alpha && theta && best_val && best_idx && work, "NULL pointer argument");
+    TB_CHECK(spec->kind >= TB200_RBF && spec->kind <= TB200_MATERN52, "unknown kernel kind");
+    TB_CHECK(spec->d >= 1 && spec->d <= TB200_MAX_D, "d out of range (1..64)");
+    TB_CHECK(acq->acq >= TB200_EI && acq->acq <= TB200_UCB, "unknown acquisition function");
+    const int mode = cand ? cand->mode : TB200_CAND_GIVEN;
+    TB_CHECK(mode != TB200_CAND_GIVEN || Xc, "Xc is NULL and no generator given");
+    TB_CHECK(mode != TB200_CAND_LHS || cand->m_total >= index_base + m, "LHS: m_total smaller than the range");
+    if (m <= 0) return 0;
+    if (batch <= 0) batch = tb200_default_batch(n);
+    TB_CHECK(batch % 128 == 0, "batch must be a multiple of 128");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int NP = pad_n(n), NB = NP / TILE, d = spec->d;
+    AcqBuffers ab;
+    const size_t need = acquire_layout(n, d, batch, &ab, (char*)work);
+    TB_CHECK(work_bytes >= need, "workspace too small (see tb200_acquire_workspace_bytes)");
+
+    const size_t ksm = sizeof(double) * (CPB * d + 8 * CPB);
+    for (int64_t off = 0; off < m; off += batch) {
+        const int64_t mb = (m - off < batch) ? (m - off) : batch;          // valid candidates
+        const int64_t mbp = (mb + 127) / 128 * 128;                          // padded to GEMM tiles
+        const double* xc = Xc ? Xc + off * d : nullptr;
+        if (mode != TB200_CAND_GIVEN) {
+            const CandGen g = make_gen(*cand, d);
+            const int64_t total = mb * d;
+            TB_LAUNCH(generate_candidates_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, st, g, d,
+                      index_base + off, mb, ab.cand);
+            xc = ab.cand;
+        }
+        TB_LAUNCH(kstar_mean_kernel, dim3((unsigned)(mbp / CPB)), dim3(256), ksm, st, xc, mb, XsT, n, NP, *spec, theta,
+                  alpha, ab.Ks, ab.mean);
+        GemmParams gp = gemm_params(Linv, NP, ab.Ks, NP, ab.partial, batch, NB, (int)(mbp / 128), NP, 1.0, 0.0);
+        gp.order = ORDER_RECT_HEAVY_LAST_ROW_FIRST;
+        gp.khi_mode = KHI_BY_TI;
+        gp.epi = EPI_COLSUMSQ;
+        if (launch_gemm<false, true>(gp, 1, 1, st)) return -1;
+        TB_LAUNCH(acquire_epilogue_kernel, dim3(1), dim3(1024), 0, st, ab.mean, ab.partial, NB, (long)batch, mbp, mb,
+                  off, index_base, *spec, theta, *acq, mu_out, sigma_out, acq_out, best_val, best_idx);
+    }
+    return 0;
+}
+
+int tb200_fp64_peak(double ms, double* dmma_tflops, double* dfma_tflops) {
+    TB_CHECK(dmma_tflops && dfma_tflops, "NULL pointer argument");
+    int dev = 0, sms = 0;
+    TB_CUDA(cudaGetDevice(&dev));
+    TB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    double* out = nullptr;
+    TB_CUDA(cudaMalloc((void**)&out, 64));
+    cudaEvent_t e0, e1;
+    TB_CUDA(cudaEventCreate(&e0));
+    TB_CUDA(cudaEventCreate(&e1));
+    const int ctas = sms * 2;
+    for (int which = 0; which < 2; ++which) {
+        int iters = 2000;
+        double best = 0.0;
+        for (int rep = 0; rep < 6; ++rep) {
+            TB_CUDA(cudaEventRecord(e0, 0));
+            if (which == 0) { TB_LAUNCH(dmma_peak_kernel, dim3(ctas), dim3(256), 0, 0, out, iters); }
+            else { TB_LAUNCH(dfma_peak_kernel, dim3(ctas), dim3(256), 0, 0, out, iters); }
+            TB_CUDA(cudaEventRecord(e1, 0));
+            TB_CUDA(cudaEventSynchronize(e1));
+            float t = 0.f;
+            TB_CUDA(cudaEventElapsedTime(&t, e0, e1));
+            // flops: DMMA.8x8x4 = 256 FMA per warp instr; DFMA = 32 FMA per warp instr
+            const double fma = (which == 0 ? 256.0 : 32.0) * 16.0 * iters * 8.0 * ctas;
+            const double tf = 2.0 * fma / (t * 1e-3) / 1e12;
+            if (rep > 0 && tf > best) best = tf;
+            if (t < ms) iters = (int)(iters * (ms / (t > 1e-3 ? t : 1e-3)) * 1.1) + 1;
+        }
+        (which == 0 ? *dmma_tflops : *dfma_tflops) = best;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(out);
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,7 @@
+#!/bin/bash
+# Build libturbo_b200.so in-tree for sm_100a.  Usage: turbo_b200/csrc/build.sh [extra nvcc flags]
+set -e
+cd "$(dirname "$0")"
+NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
+FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC"
+$NVCC $FLAGS "$@" -shared -o ../libturbo_b200.so fit.cu acquire.cu

@@ -1,0 +1,570 @@
+// GP fit path: Gram matrix, blocked FP64 Cholesky, triangular inverse, alpha, log-marginal
+// likelihood and its gradient -- batched over R hyper-parameter restarts.
+//
+// Follows sklearn:_gpr.py:584-651 (log_marginal_likelihood) and :349-367 (final factor) behind
+// turbo/modules/surrogates.py:294-326.  All dense O(n^3) work is DMMA GEMM (gemm_f64.cuh):
+//   potrf : right-looking, 128-wide panels; the 128x128 diagonal block is factored AND inverted in
+//           shared memory so the panel solve is a GEMM with Dinv^T;
+//   trtri : right-looking TRSM of the identity (same dependency shape as potrf), GEMM only;
+//   K^-1  : Linv^T Linv, one triangular GEMM;
+//   grad  : 0.5 * sum_ij (alpha alpha^T - K^-1)_ij dK_ij/dtheta with dK recomputed on the fly
+//           (sklearn materialises an (n,n,p) tensor: kernels.py:1753-1771).
+#include "gemm_f64.cuh"
+
+namespace tb200 {
+
+thread_local char g_err[512] = "";
+int64_t g_launches = 0;
+
+// ---------------------------------------------------------------------------------------------
+// XsT[r][k][j] = X[j][k] / length_scale_k(theta_r)   (j < n; 0 in the padding)
+// ---------------------------------------------------------------------------------------------
+__global__ void scale_points_kernel(const double* __restrict__ X, int n, int NP, tb200_kernel_spec spec,
+                                    const double* __restrict__ theta, int p, double* __restrict__ XsT) {
+    const int r = blockIdx.y;
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= NP) return;
+    const double* th = theta + (long)r * p;
+    double* out = XsT + (long)r * spec.d * NP;
+    for (int k = 0; k < spec.d; ++k) {
+        const double ls = length_scale(spec, th, k);
+        out[(long)k * NP + j] = (j < n) ? X[(long)j * spec.d + k] / ls : 0.0;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1: lower tiles (64x64) of K = sf2 * g(r) [+ noise on the diagonal] + jitter*I; identity padding.
+// sklearn:kernels.py:1558-1565 / :1713-1743 (pdist on X/l, diagonal forced to 1), :1315/:1438,
+// sklearn:_gpr.py:589.
+// ---------------------------------------------------------------------------------------------
+constexpr int GT = 64;
+
+__device__ __forceinline__ void lower_tile(int l, int& ti, int& tj) {
+    ti = (int)((sqrt(8.0 * l + 1.0) - 1.0) * 0.5);
+    while ((long)(ti + 1) * (ti + 2) / 2 <= l) ++ti;
+    while ((long)ti * (ti + 1) / 2 > l) --ti;
+    tj = l - ti * (ti + 1) / 2;
+}
+
+__global__ void __launch_bounds__(256) gram_train_kernel(const double* __restrict__ XsT, int n, int NP,
+                                                         tb200_kernel_spec spec, const double* __restrict__ theta,
+                                                         int p, double jitter, double* __restrict__ K) {
+    extern __shared__ double sh[];  // xi[d][64], xj[d][64]
+    const int d = spec.d;
+    double* xi = sh;
+    double* xj = sh + d * GT;
+    const int r = blockIdx.y;
+    int ti, tj;
+    lower_tile(blockIdx.x, ti, tj);
+    const double* xs = XsT + (long)r * d * NP;
+    for (int e = threadIdx.x; e < d * GT; e += blockDim.x) {
+        const int k = e / GT, c = e - k * GT;
+        xi[e] = xs[(long)k * NP + ti * GT + c];
+        xj[e] = xs[(long)k * NP + tj * GT + c];
+    }
+    __syncthreads();
+    const Hyper h = unpack_hyper(spec, theta + (long)r * p);
+    const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+    double r2[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) r2[a][b] = 0.0;
+    for (int k = 0; k < d; ++k) {
+        double va[4], vb[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) va[a] = xi[k * GT + ty * 4 + a];
+#pragma unroll
+        for (int b = 0; b < 4; ++b) vb[b] = xj[k * GT + tx * 4 + b];
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                const double df = va[a] - vb[b];
+                r2[a][b] += df * df;
+            }
+    }
+    double* Kr = K + (long)r * NP * NP;
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+        const int i = ti * GT + ty * 4 + a;
+        double out[4];
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const int j = tj * GT + tx * 4 + b;
+            double v;
+            if (i >= n || j >= n) {
+                v = (i == j) ? 1.0 : 0.0;
+            } else if (i == j) {
+                v = h.sf2 * 1.0 + h.noise;
+                v += jitter;
+            } else {
+                v = h.sf2 * shape_fn(spec.kind, r2[a][b]);
+            }
+            out[b] = v;
+        }
+        double2* dst = reinterpret_cast<double2*>(Kr + (long)i * NP + tj * GT + tx * 4);
+        dst[0] = make_double2(out[0], out[1]);
+        dst[1] = make_double2(out[2], out[3]);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// 128x128 diagonal block: Cholesky in shared memory, then in-place inverse of the factor.
+//   A block (kb,kb) <- L_kk (upper part zeroed);  Dinv[r][kb] <- L_kk^-1 (lower, upper zeroed)
+//   info[r] = first failing pivot (1-based global index) if not already set; the block is then
+//   completed with pivot 1 so the rest of the batch keeps running.
+// ---------------------------------------------------------------------------------------------
+constexpr int DB = 128, DLD = 129;
+constexpr size_t DIAG_SMEM = (size_t)(DB * DLD + DB) * sizeof(double);
+
+__global__ void __launch_bounds__(256, 1) diag_potrf_inv_kernel(double* __restrict__ Abase, long ld, long strideA,
+                                                                 int kb, double* __restrict__ Dinv, long strideD,
+                                                                 int* __restrict__ info) {
+    extern __shared__ double S[];  // [128][129] + tmp[128]
+    double* tmp = S + DB * DLD;
+    const int tid = threadIdx.x;
+    const int r = blockIdx.x;
+    double* A = Abase + (long)r * strideA + (long)kb * DB * ld + (long)kb * DB;
+    for (int e = tid; e < DB * DB; e += 256) {
+        const int i = e >> 7, j = e & 127;
+        S[i * DLD + j] = (j <= i) ? A[(long)i * ld + j] : 0.0;
+    }
+    __syncthreads();
+    const int ty = tid >> 4, tx = tid & 15;
+    for (int j = 0; j < DB; ++j) {
+        __syncthreads();  // trailing update of step j-1 complete
+        double dj = S[j * DLD + j];
+        if (!(dj > 0.0)) {  // also catches NaN, as LAPACK dpotrf does
+            if (tid == 0) atomicCAS(&info[r], 0, kb * DB + j + 1);
+            dj = 1.0;
+        }
+        const double rd = sqrt(dj);
+        for (int i = j + 1 + tid; i < DB; i += 256) S[i * DLD + j] = S[i * DLD + j] / rd;
+        __syncthreads();  // pivot read by everyone, column j scaled
+        if (tid == 0) S[j * DLD + j] = rd;
+        for (int i = j + 1 + ty; i < DB; i += 16) {
+            const double lij = S[i * DLD + j];
+            for (int k = j + 1 + tx; k <= i; k += 16) S[i * DLD + k] -= lij * S[k * DLD + j];
+        }
+    }
+    __syncthreads();
+    for (int e = tid; e < DB * DB; e += 256) {
+        const int i = e >> 7, j = e & 127;
+        A[(long)i * ld + j] = S[i * DLD + j];  // upper part already 0
+    }
+    __syncthreads();
+    // in-place inverse, columns right to left (LAPACK dtrti2, lower): two threads per row
+    const int row = tid >> 1, half = tid & 1;
+    for (int j = DB - 1; j >= 0; --j) {
+        const double ljj = S[j * DLD + j];
+        if (tid > j && tid < DB) tmp[tid] = S[tid * DLD + j];
+        __syncthreads();
+        const double inv = 1.0 / ljj;
+        double s = 0.0;
+        if (row > j) {
+            for (int k = j + 1 + half; k <= row; k += 2) s += S[row * DLD + k] * tmp[k];
+        }
+        s += __shfl_xor_sync(0xffffffffu, s, 1);
+        if (row > j && half == 0) S[row * DLD + j] = -inv * s;
+        if (tid == 0) S[j * DLD + j] = inv;
+        __syncthreads();
+    }
+    double* D = Dinv + (long)r * strideD + (long)kb * DB * DB;
+    for (int e = tid; e < DB * DB; e += 256) {
+        const int i = e >> 7, j = e & 127;
+        D[e] = S[i * DLD + j];
+    }
+}
+
+// identity (NP x NP) per batch member
+__global__ void set_identity_kernel(double* __restrict__ M, int NP) {
+    const long r = blockIdx.y;
+    const long e = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= (long)NP * NP) return;
+    const int i = (int)(e / NP), j = (int)(e - (long)i * NP);
+    M[r * NP * NP + e] = (i == j) ? 1.0 : 0.0;
+}
+
+// diag(L) and sum(log diag L) per batch member
+__global__ void logdet_kernel(const double* __restrict__ L, int NP, double* __restrict__ Ldiag,
+                              double* __restrict__ logdet) {
+    __shared__ double red[32];
+    const int r = blockIdx.x;
+    const double* Lr = L + (long)r * NP * NP;
+    double s = 0.0;
+    for (int i = threadIdx.x; i < NP; i += blockDim.x) {
+        const double v = Lr[(long)i * NP + i];
+        if (Ldiag) Ldiag[(long)r * NP + i] = v;
+        s += log(v);
+    }
+    s = warp_sum(s);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w];
+        logdet[r] = t;
+    }
+}
+
+// z = Linv * y  (row i: sum_{k<=i}); one warp per row
+__global__ void __launch_bounds__(256) trmv_lower_kernel(const double* __restrict__ Linv, int NP,
+                                                         const double* __restrict__ y, long strideY,
+                                                         double* __restrict__ z) {
+    const int r = blockIdx.y;
+    const int i = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (i >= NP) return;
+    const double* row = Linv + (long)r * NP * NP + (long)i * NP;
+    const double* yr = y + (long)r * strideY;
+    double s = 0.0;
+    for (int k = lane; k <= i; k += 32) s += row[k] * yr[k];
+    s = warp_sum(s);
+    if (lane == 0) z[(long)r * NP + i] = s;
+}
+
+// alpha = Linv^T * z (column i: sum_{k>=i}); 64 columns per CTA, 4 k-groups
+__global__ void __launch_bounds__(256) trmv_lower_t_kernel(const double* __restrict__ Linv, int NP,
+                                                           const double* __restrict__ z,
+                                                           double* __restrict__ alpha) {
+    __shared__ double red[4][64];
+    const int r = blockIdx.y;
+    const int c = threadIdx.x & 63, kg = threadIdx.x >> 6;
+    const int i = blockIdx.x * 64 + c;
+    const double* M = Linv + (long)r * NP * NP;
+    const double* zr = z + (long)r * NP;
+    double s = 0.0;
+    for (int k = blockIdx.x * 64 + kg; k < NP; k += 4) s += M[(long)k * NP + i] * zr[k];
+    red[kg][c] = s;
+    __syncthreads();
+    if (kg == 0) alpha[(long)r * NP + i] = (red[0][c] + red[1][c]) + (red[2][c] + red[3][c]);
+}
+
+// lml[r] = -0.5 y.alpha - logdet - n/2 log(2 pi)   (sklearn:_gpr.py:613-617); -inf if info[r]
+__global__ void lml_kernel(const double* __restrict__ y, long strideY, const double* __restrict__ alpha, int NP,
+                           int n, const double* __restrict__ logdet, const int* __restrict__ info,
+                           double* __restrict__ lml) {
+    __shared__ double red[32];
+    const int r = blockIdx.x;
+    double s = 0.0;
+    for (int i = threadIdx.x; i < NP; i += blockDim.x) s += y[(long)r * strideY + i] * alpha[(long)r * NP + i];
+    s = warp_sum(s);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w];
+        double v = -0.5 * t;
+        v -= logdet[r];
+        v -= n / 2.0 * log(2 * 3.141592653589793);
+        lml[r] = info[r] ? -INFINITY : v;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// gradient trace: partial[r][tile][q] over lower 64x64 tiles of W = alpha alpha^T - K^-1
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) lml_grad_kernel(const double* __restrict__ XsT, int n, int NP,
+                                                       tb200_kernel_spec spec, const double* __restrict__ theta,
+                                                       int p, const double* __restrict__ Kinv,
+                                                       const double* __restrict__ alpha,
+                                                       double* __restrict__ partial, int ntiles) {
+    extern __shared__ double sh[];  // xi[d][64], xj[d][64], red[8][p]
+    const int d = spec.d;
+    double* xi = sh;
+    double* xj = sh + d * GT;
+    double* red = sh + 2 * d * GT;
+    const int r = blockIdx.y;
+    int ti, tj;
+    lower_tile(blockIdx.x, ti, tj);
+    const double* xs = XsT + (long)r * d * NP;
+    for (int e = threadIdx.x; e < d * GT; e += blockDim.x) {
+        const int k = e / GT, c = e - k * GT;
+        xi[e] = xs[(long)k * NP + ti * GT + c];
+        xj[e] = xs[(long)k * NP + tj * GT + c];
+    }
+    __syncthreads();
+    const Hyper h = unpack_hyper(spec, theta + (long)r * p);
+    const double* Kr = Kinv + (long)r * NP * NP;
+    const double* al = alpha + (long)r * NP;
+    const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+    const int nl = spec.ard ? d : 1;
+    const int off_ls = spec.has_const ? 1 : 0;
+    double g_const = 0.0, g_noise = 0.0;
+    double g_ls[TB200_MAX_D];
+    for (int k = 0; k < nl; ++k) g_ls[k] = 0.0;
+
+    for (int a = 0; a < 4; ++a) {
+        const int i = ti * GT + ty * 4 + a;
+        if (i >= n) continue;
+        const double ai = al[i];
+        for (int b = 0; b < 4; ++b) {
+            const int j = tj * GT + tx * 4 + b;
+            if (j > i || j >= n) continue;
+            const double w = ai * al[j] - Kr[(long)i * NP + j];
+            if (i == j) {
+                g_const += w * h.sf2;  // dK/dlog(const) on the diagonal = sf2 * 1
+                g_noise += w * h.noise;
+                continue;
+            }
+            double r2 = 0.0;
+            for (int k = 0; k < d; ++k) {
+                const double df = xi[k * GT + ty * 4 + a] - xj[k * GT + tx * 4 + b];
+                r2 += df * df;
+            }
+            const double w2 = 2.0 * w;  // (i,j) and (j,i)
+            g_const += w2 * h.sf2 * shape_fn(spec.kind, r2);
+            const double f = w2 * h.sf2 * shape_grad_fn(spec.kind, r2);
+            if (spec.ard) {
+                for (int k = 0; k < d; ++k) {
+                    const double df = xi[k * GT + ty * 4 + a] - xj[k * GT + tx * 4 + b];
+                    g_ls[k] += f * (df * df);
+                }
+            } else {
+                g_ls[0] += f * r2;
+            }
+        }
+    }
+    // block reduction of p values, fixed order
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int q = 0; q < p; ++q) {
+        double v;
+        if (spec.has_const && q == 0) v = g_const;
+        else if (q < off_ls + nl) v = g_ls[q - off_ls];
+        else v = g_noise;
+        v = warp_sum(v);
+        if (lane == 0) red[warp * p + q] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < p) {
+        double t = 0.0;
+        for (int w = 0; w < 8; ++w) t += red[w * p + threadIdx.x];
+        partial[((long)r * ntiles + blockIdx.x) * p + threadIdx.x] = t;
+    }
+}
+
+__global__ void lml_grad_reduce_kernel(const double* __restrict__ partial, int ntiles, int p,
+                                       const int* __restrict__ info, double* __restrict__ grad) {
+    __shared__ double red[32];
+    const int r = blockIdx.x, q = blockIdx.y;
+    double s = 0.0;
+    for (int t = threadIdx.x; t < ntiles; t += blockDim.x) s += partial[((long)r * ntiles + t) * p + q];
+    s = warp_sum(s);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w];
+        grad[(long)r * p + q] = info[r] ? 0.0 : 0.5 * t;
+    }
+}
+
+__global__ void pad_vector_kernel(const double* __restrict__ y, int n, int NP, double* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < NP) out[i] = (i < n) ? y[i] : 0.0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// host drivers
+// ---------------------------------------------------------------------------------------------
+struct FitBuffers {
+    double* K;       // [R][NP][NP]   Gram -> L -> (K^-1)
+    double* Linv;    // [R][NP][NP]
+    double* Dinv;    // [R][NB][128][128]
+    double* XsT;     // [R][d][NP]
+    double* ypad;    // [NP]
+    double* z;       // [R][NP]
+    double* alpha;   // [R][NP]
+    double* logdet;  // [R]
+    double* partial; // [R][ntiles64][p]
+};
+
+static size_t align256(size_t b) { return (b + 255) / 256 * 256; }
+
+size_t fit_workspace_layout(int n, int d, int R, int p, bool own_linv, bool own_xst, bool own_alpha, FitBuffers* fb,
+                            char* base) {
+    const size_t NP = pad_n(n), NB = NP / TILE;
+    const size_t nt64 = (NP / GT) * (NP / GT + 1) / 2;
+    size_t off = 0;
+    auto take = [&](size_t bytes) {
+        char* ptr = base ? base + off : nullptr;
+        off += align256(bytes);
+        return reinterpret_cast<double*>(ptr);
+    };
+    double* K = take(sizeof(double) * R * NP * NP);
+    double* Linv = own_linv ? take(sizeof(double) * R * NP * NP) : nullptr;
+    double* Dinv = take(sizeof(double) * R * NB * TILE * TILE);
+    double* XsT = own_xst ? take(sizeof(double) * R * d * NP) : nullptr;
+    double* ypad = take(sizeof(double) * NP);
+    double* z = take(sizeof(double) * R * NP);
+    double* alpha = own_alpha ? take(sizeof(double) * R * NP) : nullptr;
+    double* logdet = take(sizeof(double) * R);
+    double* partial = take(sizeof(double) * R * nt64 * (p > 0 ? p : 1));
+    if (fb) {
+        fb->K = K; fb->Linv = Linv; fb->Dinv = Dinv; fb->XsT = XsT; fb->ypad = ypad; fb->z = z;
+        fb->alpha = alpha; fb->logdet = logdet; fb->partial = partial;
+    }
+    return off;
+}
+
+// blocked right-looking Cholesky of R matrices in fb.K (lower), Dinv blocks kept for trtri
+static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStream_t st) {
+    const int NB = NP / TILE;
+    const long sK = (long)NP * NP, sD = (long)NB * TILE * TILE;
+    static bool configured = false;
+    if (!configured) {
+        TB_CUDA(cudaFuncSetAttribute(diag_potrf_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)DIAG_SMEM));
+        configured = true;
+    }
+    for (int k = 0; k < NB; ++k) {
+        TB_LAUNCH(diag_potrf_inv_kernel, dim3(R), dim3(256), DIAG_SMEM, st, fb.K, (long)NP, sK, k, fb.Dinv, sD, info);
+        const int rem = NB - k - 1;
+        if (rem == 0) break;
+        // panel: A[i,k] <- A[i,k] * Dinv_k^T  (i > k), in place
+        {
+            double* panel = fb.K + (long)(k + 1) * TILE * NP + (long)k * TILE;
+            GemmParams p = gemm_params(panel, NP, fb.Dinv + (long)k * TILE * TILE, TILE, panel, NP, rem, 1, TILE, 1.0, 0.0);
+            p.sA1 = sK; p.sB1 = sD; p.sC1 = sK;
+            if (launch_gemm<false, true>(p, R, 1, st)) return -1;
+        }
+        // trailing: A[i,j] -= A[i,k] A[j,k]^T  (k < j <= i)
+        {
+            const double* panel = fb.K + (long)(k + 1) * TILE * NP + (long)k * TILE;
+            double* trail = fb.K + (long)(k + 1) * TILE * NP + (long)(k + 1) * TILE;
+            GemmParams p = gemm_params(panel, NP, panel, NP, trail, NP, rem, rem, TILE, -1.0, 1.0);
+            p.order = ORDER_LOWER;
+            p.sA1 = sK; p.sB1 = sK; p.sC1 = sK;
+            if (launch_gemm<false, true>(p, R, 1, st)) return -1;
+        }
+    }
+    return 0;
+}
+
+// Linv = L^-1 for R factors: right-looking TRSM of the identity using the inverted diagonal blocks
+static int trtri_batched(const FitBuffers& fb, double* Linv, int NP, int R, cudaStream_t st) {
+    const int NB = NP / TILE;
+    const long sK = (long)NP * NP, sD = (long)NB * TILE * TILE;
+    {
+        const long total = (long)NP * NP;
+        TB_LAUNCH(set_identity_kernel, dim3((unsigned)((total + 255) / 256), R), dim3(256), 0, st, Linv, NP);
+    }
+    for (int j = 0; j < NB; ++j) {
+        // X[j, 0:j+1] = Dinv_j * Acc[j, 0:j+1]   (in place; the diagonal block of Acc is I)
+        {
+            double* rowj = Linv + (long)j * TILE * NP;
+            GemmParams p = gemm_params(fb.Dinv + (long)j * TILE * TILE, TILE, rowj, NP, rowj, NP, 1, j + 1, TILE, 1.0, 0.0);
+            p.sA1 = sD; p.sB1 = sK; p.sC1 = sK;
+            if (launch_gemm<false, false>(p, R, 1, st)) return -1;
+        }
+        const int rem = NB - j - 1;
+        if (rem == 0) break;
+        // Acc[i, 0:j+1] -= L[i,j] * X[j, 0:j+1]   (i > j)
+        {
+            const double* Lcol = fb.K + (long)(j + 1) * TILE * NP + (long)j * TILE;
+            const double* rowj = Linv + (long)j * TILE * NP;
+            double* acc = Linv + (long)(j + 1) * TILE * NP;
+            GemmParams p = gemm_params(Lcol, NP, rowj, NP, acc, NP, rem, j + 1, TILE, -1.0, 1.0);
+            p.sA1 = sK; p.sB1 = sK; p.sC1 = sK;
+            if (launch_gemm<false, false>(p, R, 1, st)) return -1;
+        }
+    }
+    return 0;
+}
+
+// scale -> gram -> potrf -> logdet -> trtri -> z, alpha -> lml [-> K^-1 -> grad]
+static int fit_pipeline(const double* X, const double* y_n, int n, const tb200_kernel_spec& spec, const double* theta,
+                        int R, double jitter, bool with_grad, const FitBuffers& fb, double* XsT, double* Linv,
+                        double* alpha, double* Ldiag, double* lml, double* grad, int* info, cudaStream_t st) {
+    const int NP = pad_n(n), d = spec.d, p = spec_p(spec);
+    const int nt64 = (NP / GT) * (NP / GT + 1) / 2;
+    TB_CUDA(cudaMemsetAsync(info, 0, sizeof(int) * R, st));
+    TB_LAUNCH(pad_vector_kernel, dim3((NP + 255) / 256), dim3(256), 0, st, y_n, n, NP, fb.ypad);
+    TB_LAUNCH(scale_points_kernel, dim3((NP + 255) / 256, R), dim3(256), 0, st, X, n, NP, spec, theta, p, XsT);
+    const size_t gsm = sizeof(double) * 2 * d * GT;
+    TB_LAUNCH(gram_train_kernel, dim3(nt64, R), dim3(256), gsm, st, XsT, n, NP, spec, theta, p, jitter, fb.K);
+    if (potrf_batched(fb, NP, R, info, st)) return -1;
+    TB_LAUNCH(logdet_kernel, dim3(R), dim3(256), 0, st, fb.K, NP, Ldiag, fb.logdet);
+    if (trtri_batched(fb, Linv, NP, R, st)) return -1;
+    TB_LAUNCH(trmv_lower_kernel, dim3(NP / 8, R), dim3(256), 0, st, Linv, NP, fb.ypad, 0L, fb.z);
+    TB_LAUNCH(trmv_lower_t_kernel, dim3(NP / 64, R), dim3(256), 0, st, Linv, NP, fb.z, alpha);
+    TB_LAUNCH(lml_kernel, dim3(R), dim3(256), 0, st, fb.ypad, 0L, alpha, NP, n, fb.logdet, info, lml);
+    if (with_grad) {
+        // K^-1 (lower tiles) = Linv^T Linv, written over L
+        GemmParams q = gemm_params(Linv, NP, Linv, NP, fb.K, NP, NP / TILE, NP / TILE, NP, 1.0, 0.0);
+        q.order = ORDER_LOWER;
+        q.klo_mode = KLO_BY_TI;
+        q.sA1 = q.sB1 = q.sC1 = (long)NP * NP;
+        if (launch_gemm<true, false>(q, R, 1, st)) return -1;
+        const size_t sm = sizeof(double) * (2 * d * GT + 8 * p);
+        TB_LAUNCH(lml_grad_kernel, dim3(nt64, R), dim3(256), sm, st, XsT, n, NP, spec, theta, p, fb.K, alpha,
+                  fb.partial, nt64);
+        TB_LAUNCH(lml_grad_reduce_kernel, dim3(R, p), dim3(256), 0, st, fb.partial, nt64, p, info, grad);
+    }
+    return 0;
+}
+
+}  // namespace tb200
+
+using namespace tb200;
+
+extern "C" {
+
+int tb200_version(void) { return 100; }
+const char* tb200_last_error(void) { return g_err; }
+int tb200_padded_n(int n) { return pad_n(n); }
+int64_t tb200_launch_count(void) { return g_launches; }
+
+size_t tb200_fit_workspace_bytes(int n, int d, int R, int with_grad) {
+    (void)with_grad;
+    return fit_workspace_layout(n, d, R, d + 2, true, true, true, nullptr, nullptr);
+}
+
+static int check_spec(const tb200_kernel_spec* s) {
+    TB_CHECK(s != nullptr, "kernel spec is NULL");
+    TB_CHECK(s->kind >= TB200_RBF && s->kind <= TB200_MATERN52, "unknown kernel kind");
+    TB_CHECK(s->d >= 1 && s->d <= TB200_MAX_D, "d out of range (1..64)");
+    return 0;
+}
+
+int tb200_lml_batched(const double* X, const double* y_n, int n, const tb200_kernel_spec* spec, const double* theta,
+                      int R, double jitter, int with_grad, double* lml, double* grad, int* info, void* work,
+                      size_t work_bytes, void* stream) {
+    if (check_spec(spec)) return -1;
+    TB_CHECK(n >= 1 && R >= 1, "n and R must be >= 1");
+    TB_CHECK(X && y_n && theta && lml && info && work, "NULL pointer argument");
+    TB_CHECK(!with_grad || grad, "grad is NULL but with_grad is set");
+    FitBuffers fb;
+    const size_t need = fit_workspace_layout(n, spec->d, R, spec_p(*spec), true, true, true, &fb, (char*)work);
+    TB_CHECK(work_bytes >= need, "workspace too small (see tb200_fit_workspace_bytes)");
+    return fit_pipeline(X, y_n, n, *spec, theta, R, jitter, with_grad != 0, fb, fb.XsT, fb.Linv, fb.alpha, nullptr,
+                        lml, grad, info, (cudaStream_t)stream);
+}
+
+int tb200_factor(const double* X, const double* y_n, int n, const tb200_kernel_spec* spec, const double* theta,
+                 double jitter, double* XsT, double* Linv, double* alpha, double* Ldiag, double* lml, int* info,
+                 void* work, size_t work_bytes, void* stream) {
+    if (check_spec(spec)) return -1;
+    TB_CHECK(n >= 1, "n must be >= 1");
+    TB_CHECK(X && y_n && theta && XsT && Linv && alpha && lml && info && work, "NULL pointer argument");
+    FitBuffers fb;
+    const size_t need = fit_workspace_layout(n, spec->d, 1, spec_p(*spec), false, false, false, &fb, (char*)work);
+    TB_CHECK(work_bytes >= need, "workspace too small (see tb200_fit_workspace_bytes)");
+    return fit_pipeline(X, y_n, n, *spec, theta, 1, jitter, false, fb, XsT, Linv, alpha, Ldiag, lml, nullptr, info,
+                        (cudaStream_t)stream);
+}
+
+int tb200_dgemm(int ta, int tb, int M, int N, int K, double alpha, const double* A, int lda, const double* B, int ldb,
+                double beta, double* C, int ldc, void* stream) {
+    TB_CHECK(M > 0 && N > 0 && K > 0 && M % G_TM == 0 && N % G_TN == 0 && K % G_TK == 0,
+             "tb200_dgemm: M,N multiples of 128 and K multiple of 16 required");
+    GemmParams p = gemm_params(A, lda, B, ldb, C, ldc, M / G_TM, N / G_TN, K, alpha, beta);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!ta && !tb) return launch_gemm<false, false>(p, 1, 1, st);
+    if (!ta && tb) return launch_gemm<false, true>(p, 1, 1, st);
+    if (ta && !tb) return launch_gemm<true, false>(p, 1, 1, st);
+    return launch_gemm<true, true>(p, 1, 1, st);
+}
+
+}  // extern "C"
