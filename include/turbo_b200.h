@@ -107,6 +107,12 @@ int tb200_generate_candidates(const tb200_cand_spec* cand_host, int d, int64_t i
  * runs register-resident DMMA.8x8x4 / DFMA loops on every SM for ~`ms` milliseconds each. */
 int tb200_fp64_peak(double ms, double* dmma_tflops_host, double* dfma_tflops_host);
 
+/* CUDA-event timing of the dominant kernel (the variance GEMM inside tb200_acquire), recorded on the
+ * stream the kernel is launched on.  enable(1) starts collecting; read() synchronises, returns the
+ * summed duration and the number of timed launches, and clears the record. */
+int tb200_timing_enable(int on);
+int tb200_timing_read(double* gemm_ms_host, int64_t* gemm_launches_host);
+
 /* plain C = alpha*op(A)*op(B) + beta*C on the library's DMMA GEMM (testing / roofline runs);
  * M,N multiples of 128, K multiple of 16; ta/tb: 0 = [m][k] / [k][n] storage, 1 = transposed. */
 int tb200_dgemm(int ta, int tb, int M, int N, int K, double alpha, const double* A, int lda,

@@ -1,0 +1,14 @@
+"""turbo_b200: B200-native GP surrogate + acquisition plugins for mbway/turbo.
+
+Host layer (Python, mirrors turbo.modules' plugin interface) over libturbo_b200.so (hand-written
+sm_100a CUDA behind the C ABI in include/turbo_b200.h).  No CPU fallback anywhere.
+"""
+from . import _lib
+from .kernels import KernelSpec, from_sklearn
+from .surrogate import GpuGPSurrogate
+from .acquisition import GpuEI, GpuPI, GpuUCB
+from .aux_optimiser import GpuCandidateArgmax
+from .presets import load_gpu_preset
+
+__all__ = ['KernelSpec', 'from_sklearn', 'GpuGPSurrogate', 'GpuEI', 'GpuPI', 'GpuUCB', 'GpuCandidateArgmax',
+           'load_gpu_preset']

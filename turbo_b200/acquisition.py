@@ -1,0 +1,134 @@
+"""GpuEI / GpuPI / GpuUCB: drop-ins for turbo.modules.EI / PI / UCB
+(turbo/modules/acquisition_functions.py:80-358).
+
+The factories subclass the reference's so ``isinstance(acq, tm.EI)`` checks in turbo.plotting keep
+working (plotting/overview.py:53-61, plotting/trials.py:373).  Each FunctionInstance offers
+
+* ``__call__(X) -> (m,) ndarray``: the reference contract (values for host points), and
+* ``argmax_over(...) -> (value, index, x)``: the fused device path -- predict, acquisition and argmax
+  in one pass over a candidate set that is either given (host array, streamed in chunks) or generated
+  on the device from (seed, global index), optionally sharded across ranks.
+"""
+import math
+
+import numpy as np
+
+from . import _lib, device
+from ._reference_api import EI, PI, UCB
+
+
+class _DeviceFunction:
+    """mixin: everything that talks to the device for one (model, acquisition) pair"""
+
+    _acq_code = None
+
+    def _acq_param(self):
+        raise NotImplementedError()
+
+    def _spec_c(self):
+        m = self.model
+        return device.acq_spec(self._acq_code, self.scale_factor, getattr(self, 'incumbent_cost', 0.0),
+                               self._acq_param(), m.y_mean, m.y_std)
+
+    def __call__(self, X):
+        import torch
+        X = np.ascontiguousarray(np.atleast_2d(X), dtype=np.float64)
+        m = X.shape[0]
+        out = torch.empty(m, dtype=torch.float64, device=device.device())
+        a = device.Acquirer(self.model.factor, self._spec_c())
+        a.run(device.to_device(X), m, 0, None, acq=out)
+        return out.cpu().numpy()
+
+    def argmax_over(self, candidates=None, generator=None, m=None, lo=None, hi=None, seed=0, group=None,
+                    chunk=1 << 18, batch=0):
+        """argmax of the acquisition function over a candidate set.
+
+        candidates: (m,d) host array (every rank passes the same full set when ``group`` is given), or
+        generator : 'uniform' | 'lhs' with ``m``, ``lo``, ``hi``, ``seed`` -- generated on the device
+                    from the global index, so the result does not depend on how ranks split the range.
+        Returns (value, global index, x (1,d)); (-inf, -1, None) if no candidate is selectable.
+        Ties keep the lowest index; NaN never wins (auxiliary_optimisers.py:63-66 picks argsort's first).
+        """
+        import torch
+        from . import dist
+        rank, world = dist.rank_world(group)
+        a = device.Acquirer(self.model.factor, self._spec_c(), batch)
+        d = self.model.spec.d
+        if candidates is not None:
+            if isinstance(candidates, torch.Tensor):  # a (pinned) host tensor is used in place
+                assert candidates.device.type == 'cpu' and candidates.dtype == torch.float64
+                X = candidates.contiguous().numpy()
+            else:
+                X = np.ascontiguousarray(np.atleast_2d(candidates), dtype=np.float64)
+            m = X.shape[0]
+            lo_i, hi_i = dist.shard_range(m, rank, world)
+            host = candidates[lo_i:hi_i] if isinstance(candidates, torch.Tensor) else torch.from_numpy(X[lo_i:hi_i])
+            if host.numel() * 8 >= (1 << 20) and not host.is_pinned():
+                host = host.pin_memory()
+            # stream the shard in chunks: H2D of chunk i+1 overlaps the kernels of chunk i
+            copy_stream = torch.cuda.Stream()
+            main = torch.cuda.current_stream()
+            pending = None
+            for off in range(0, hi_i - lo_i, chunk):
+                cnt = min(chunk, hi_i - lo_i - off)
+                with torch.cuda.stream(copy_stream):
+                    buf = host[off:off + cnt].to(device.device(), non_blocking=True)
+                    ev = torch.cuda.Event()
+                    ev.record(copy_stream)
+                main.wait_event(ev)
+                a.run(buf, cnt, lo_i + off, None)
+                buf.record_stream(main)
+                pending = buf
+            del pending
+            cand_c = None
+        else:
+            mode = {'uniform': _lib.CAND_UNIFORM, 'lhs': _lib.CAND_LHS}[generator]
+            cand_c = _lib.cand_spec(mode, seed, m, lo, hi)
+            lo_i, hi_i = dist.shard_range(m, rank, world)
+            if hi_i > lo_i:
+                a.run(None, hi_i - lo_i, lo_i, cand_c)
+        val, idx = a.best()
+        val, idx = dist.allreduce_argmax(val, idx, group)
+        if idx < 0:
+            return -math.inf, -1, None
+        if candidates is not None:
+            x = X[idx:idx + 1].copy()
+        else:
+            x = _lib.host_candidates(cand_c.mode, seed, m, lo, hi, [idx])
+        return val, idx, x
+
+
+class GpuUCB(UCB):
+    def construct_function(self, trial_num, model, desired_extremum):
+        beta = self.beta(trial_num) if callable(self.beta) else self.beta
+        return GpuUCB.FunctionInstance(model, desired_extremum, beta), {'beta': beta}
+
+    class FunctionInstance(_DeviceFunction, UCB.FunctionInstance):
+        _acq_code = _lib.ACQ_UCB
+
+        def _acq_param(self):
+            return self.beta
+
+
+class GpuPI(PI):
+    def construct_function(self, trial_num, model, desired_extremum, incumbent_cost):
+        xi = self.xi(trial_num) if callable(self.xi) else self.xi
+        return GpuPI.FunctionInstance(model, desired_extremum, incumbent_cost, xi), {'xi': xi}
+
+    class FunctionInstance(_DeviceFunction, PI.FunctionInstance):
+        _acq_code = _lib.ACQ_PI
+
+        def _acq_param(self):
+            return self.xi
+
+
+class GpuEI(EI):
+    def construct_function(self, trial_num, model, desired_extremum, incumbent_cost):
+        xi = self.xi(trial_num) if callable(self.xi) else self.xi
+        return GpuEI.FunctionInstance(model, desired_extremum, incumbent_cost, xi), {'xi': xi}
+
+    class FunctionInstance(_DeviceFunction, EI.FunctionInstance):
+        _acq_code = _lib.ACQ_EI
+
+        def _acq_param(self):
+            return self.xi

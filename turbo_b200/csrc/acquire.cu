@@ -13,6 +13,8 @@
 //   4. acquire_epilogue  : var = k** - sum partial, clamp, de-normalise, EI/PI/UCB, running argmax
 // The candidate matrix, K*, V, mu, sigma and the acquisition values are not written to HBM unless
 // the caller asks for them (mu_out / sigma_out / acq_out).
+#include <vector>
+
 #include "gemm_f64.cuh"
 
 namespace tb200 {
@@ -84,7 +86,13 @@ inline CandGen make_gen(const tb200_cand_spec& c, int d) {
 
 __host__ __device__ inline double gen_coord(const CandGen& g, double lo, double hi, uint64_t idx, uint32_t dim) {
     const double u = uniform01(g.seed, idx, dim, 0u);
-    if (g.mode == TB200_CAND_UNIFORM) return lo + (hi - lo) * u;
+    if (g.mode == TB200_CAND_UNIFORM) {
+#ifdef __CUDA_ARCH__
+        return __dadd_rn(lo, __dmul_rn(hi - lo, u));  // no FMA contraction: bit-identical to the NumPy mirror
+#else
+        return lo + (hi - lo) * u;
+#endif
+    }
     // LHS (naive_selectors.py:75-78): lo + range * (stratum + u) / m with a per-dimension permutation
     const uint64_t s = permute_index(g.seed, dim, idx, (uint64_t)g.m_total);
     return lo + (hi - lo) * ((double)s + u) / (double)g.m_total;
@@ -267,6 +275,20 @@ __global__ void __launch_bounds__(256) dfma_peak_kernel(double* out, int iters) 
     if (s == 123.456) out[0] = s;
 }
 
+// optional CUDA-event timing of the dominant kernel (the variance GEMM), for bench.py's roofline
+static bool g_time_gemm = false;
+static std::vector<cudaEvent_t> g_events;
+static size_t g_events_used = 0;
+
+static cudaEvent_t next_event() {
+    if (g_events_used == g_events.size()) {
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        g_events.push_back(e);
+    }
+    return g_events[g_events_used++];
+}
+
 struct AcqBuffers {
     double* cand;     // [batch][d]   generated candidates
     double* Ks;       // [batch][NP]
@@ -344,6 +366,7 @@ int tb200_acquire(const double* Xc, int64_t m, int64_t index_base, const tb200_c
     TB_CHECK(spec->d >= 1 && spec->d <= TB200_MAX_D, "d out of range (1..64)");
     TB_CHECK(acq->acq >= TB200_EI && acq->acq <= TB200_UCB, "unknown acquisition function");
     const int mode = cand ? cand->mode : TB200_CAND_GIVEN;
+    if (m <= 0) return 0;
     TB_CHECK(mode != TB200_CAND_GIVEN || Xc, "Xc is NULL and no generator given");
     TB_CHECK(mode != TB200_CAND_LHS || cand->m_total >= index_base + m, "LHS: m_total smaller than the range");
     if (m <= 0) return 0;
@@ -373,10 +396,33 @@ int tb200_acquire(const double* Xc, int64_t m, int64_t index_base, const tb200_c
         gp.order = ORDER_RECT_HEAVY_LAST_ROW_FIRST;
         gp.khi_mode = KHI_BY_TI;
         gp.epi = EPI_COLSUMSQ;
+        if (g_time_gemm) TB_CUDA(cudaEventRecord(next_event(), st));
         if (launch_gemm<false, true>(gp, 1, 1, st)) return -1;
+        if (g_time_gemm) TB_CUDA(cudaEventRecord(next_event(), st));
         TB_LAUNCH(acquire_epilogue_kernel, dim3(1), dim3(1024), 0, st, ab.mean, ab.partial, NB, (long)batch, mbp, mb,
                   off, index_base, *spec, theta, *acq, mu_out, sigma_out, acq_out, best_val, best_idx);
     }
+    return 0;
+}
+
+int tb200_timing_enable(int on) {
+    g_time_gemm = on != 0;
+    g_events_used = 0;
+    return 0;
+}
+
+int tb200_timing_read(double* gemm_ms, int64_t* gemm_launches) {
+    TB_CHECK(gemm_ms && gemm_launches, "NULL pointer argument");
+    double total = 0.0;
+    for (size_t i = 0; i + 1 < g_events_used; i += 2) {
+        TB_CUDA(cudaEventSynchronize(g_events[i + 1]));
+        float t = 0.f;
+        TB_CUDA(cudaEventElapsedTime(&t, g_events[i], g_events[i + 1]));
+        total += t;
+    }
+    *gemm_ms = total;
+    *gemm_launches = (int64_t)(g_events_used / 2);
+    g_events_used = 0;
     return 0;
 }
 

@@ -1,0 +1,157 @@
+"""Thin wrappers that call the C ABI on PyTorch device buffers (the buffer/stream layer only).
+
+Every function raises if CUDA or libturbo_b200.so is unavailable; there is no CPU path.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+
+
+def _require_cuda():
+    if not torch.cuda.is_available():
+        raise RuntimeError("turbo_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+
+
+def device():
+    _require_cuda()
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def to_device(a):
+    """host float64 array -> device tensor (pinned staging for large arrays)"""
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    t = torch.from_numpy(a)
+    if a.nbytes >= (1 << 20):
+        t = t.pin_memory()
+    return t.to(device(), non_blocking=True)
+
+
+def _workspace(nbytes):
+    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device())
+
+
+def padded_n(n):
+    return _lib.load().tb200_padded_n(int(n))
+
+
+def lml_batched(X_dev, yn_dev, n, spec, thetas, jitter, with_grad=True):
+    """log-marginal likelihood (+ gradient) of R theta rows in one device call.
+    -> (lml (R,), grad (R,p) or None, info (R,)) as NumPy."""
+    lib = _lib.load()
+    thetas = np.ascontiguousarray(np.atleast_2d(thetas), dtype=np.float64)
+    R, p = thetas.shape
+    assert p == spec.p
+    dev = device()
+    th = torch.from_numpy(thetas).to(dev)
+    lml = torch.empty(R, dtype=torch.float64, device=dev)
+    grad = torch.empty((R, p), dtype=torch.float64, device=dev) if with_grad else None
+    info = torch.empty(R, dtype=torch.int32, device=dev)
+    nbytes = lib.tb200_fit_workspace_bytes(n, spec.d, R, int(with_grad))
+    work = _workspace(nbytes)
+    cs = spec.to_c()
+    _lib.check(lib.tb200_lml_batched(_lib.ptr(X_dev), _lib.ptr(yn_dev), n, C.byref(cs), _lib.ptr(th), R,
+                                     float(jitter), int(with_grad), _lib.ptr(lml), _lib.ptr(grad), _lib.ptr(info),
+                                     _lib.ptr(work), nbytes, _lib.stream_ptr()))
+    out = (lml.cpu().numpy(), grad.cpu().numpy() if with_grad else None, info.cpu().numpy())
+    del work
+    return out
+
+
+class Factor:
+    """device-resident state predict/acquire need: XsT, Linv, alpha (+ theta), see tb200_factor"""
+
+    def __init__(self, X_dev, yn_dev, n, spec, theta, jitter):
+        lib = _lib.load()
+        dev = device()
+        self.n, self.spec = int(n), spec
+        NP = padded_n(n)
+        self.NP = NP
+        self.theta = torch.from_numpy(np.ascontiguousarray(theta, dtype=np.float64)).to(dev)
+        self.XsT = torch.empty((spec.d, NP), dtype=torch.float64, device=dev)
+        self.Linv = torch.empty((NP, NP), dtype=torch.float64, device=dev)
+        self.alpha = torch.empty(NP, dtype=torch.float64, device=dev)
+        self.Ldiag = torch.empty(NP, dtype=torch.float64, device=dev)
+        lml = torch.empty(1, dtype=torch.float64, device=dev)
+        info = torch.empty(1, dtype=torch.int32, device=dev)
+        nbytes = lib.tb200_fit_workspace_bytes(n, spec.d, 1, 0)
+        work = _workspace(nbytes)
+        cs = spec.to_c()
+        _lib.check(lib.tb200_factor(_lib.ptr(X_dev), _lib.ptr(yn_dev), n, C.byref(cs), _lib.ptr(self.theta),
+                                    float(jitter), _lib.ptr(self.XsT), _lib.ptr(self.Linv), _lib.ptr(self.alpha),
+                                    _lib.ptr(self.Ldiag), _lib.ptr(lml), _lib.ptr(info), _lib.ptr(work), nbytes,
+                                    _lib.stream_ptr()))
+        self.info = int(info.item())
+        self.lml = float(lml.item())
+        del work
+
+    def nbytes(self):
+        return sum(t.numel() * t.element_size() for t in (self.XsT, self.Linv, self.alpha, self.Ldiag))
+
+
+class Acquirer:
+    """runs tb200_acquire over device candidates / a generated set, keeping the running best on device"""
+
+    def __init__(self, factor, acq_c, batch=0):
+        lib = _lib.load()
+        self.lib, self.f, self.acq_c = lib, factor, acq_c
+        self.batch = int(batch) if batch else int(lib.tb200_default_batch(factor.n))
+        self.nbytes = lib.tb200_acquire_workspace_bytes(factor.n, factor.spec.d, self.batch)
+        self.work = _workspace(self.nbytes)
+        dev = device()
+        self.best_val = torch.empty(1, dtype=torch.float64, device=dev)
+        self.best_idx = torch.empty(1, dtype=torch.int64, device=dev)
+        self.spec_c = factor.spec.to_c()
+        self.reset()
+
+    def reset(self):
+        _lib.check(self.lib.tb200_best_reset(_lib.ptr(self.best_val), _lib.ptr(self.best_idx), _lib.stream_ptr()))
+
+    def run(self, Xc_dev, m, index_base=0, cand_c=None, mu=None, sigma=None, acq=None):
+        """candidates [index_base, index_base+m): Xc_dev (m,d) device tensor, or generated from cand_c"""
+        f = self.f
+        _lib.check(self.lib.tb200_acquire(
+            _lib.ptr(Xc_dev), int(m), int(index_base), C.byref(cand_c) if cand_c is not None else None,
+            _lib.ptr(f.XsT), _lib.ptr(f.Linv), _lib.ptr(f.alpha), f.n, C.byref(self.spec_c), _lib.ptr(f.theta),
+            C.byref(self.acq_c), _lib.ptr(mu), _lib.ptr(sigma), _lib.ptr(acq), _lib.ptr(self.best_val),
+            _lib.ptr(self.best_idx), self.batch, _lib.ptr(self.work), self.nbytes, _lib.stream_ptr()))
+
+    def best(self):
+        """(value, global index); index -1 when nothing was selectable (all NaN / empty)"""
+        return float(self.best_val.item()), int(self.best_idx.item())
+
+
+def acq_spec(acq, sign, incumbent, param, y_mean, y_std):
+    return _lib.AcqSpecC(int(acq), float(sign), float(incumbent), float(param), float(y_mean), float(y_std))
+
+
+def generate_candidates(cand_c, d, index_base, m):
+    """device tensor (m,d) of generated candidates (tests / winner-row recovery)"""
+    out = torch.empty((int(m), int(d)), dtype=torch.float64, device=device())
+    _lib.check(_lib.load().tb200_generate_candidates(C.byref(cand_c), int(d), int(index_base), int(m),
+                                                     _lib.ptr(out), _lib.stream_ptr()))
+    return out
+
+
+def fp64_peak(ms=50.0):
+    """measured (DMMA TFLOP/s, DFMA TFLOP/s) of the current device"""
+    _require_cuda()
+    a, b = C.c_double(), C.c_double()
+    _lib.check(_lib.load().tb200_fp64_peak(float(ms), C.byref(a), C.byref(b)))
+    return a.value, b.value
+
+
+def dgemm(ta, tb, alpha, A, B, beta, Cm):
+    """C = alpha*op(A)op(B) + beta*C on the library's DMMA GEMM (row-major torch tensors)"""
+    M, N = Cm.shape
+    K = A.shape[0] if ta else A.shape[1]
+    _lib.check(_lib.load().tb200_dgemm(int(ta), int(tb), M, N, K, float(alpha), _lib.ptr(A), A.stride(0),
+                                       _lib.ptr(B), B.stride(0), float(beta), _lib.ptr(Cm), Cm.stride(0),
+                                       _lib.stream_ptr()))
+    return Cm
+
+
+def launch_count():
+    return int(_lib.load().tb200_launch_count())
