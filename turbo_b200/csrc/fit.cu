@@ -408,8 +408,15 @@ size_t fit_workspace_layout(int n, int d, int R, int p, bool own_linv, bool own_
     return off;
 }
 
-// blocked right-looking Cholesky of R matrices in fb.K (lower), Dinv blocks kept for trtri
-static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStream_t st) {
+// Two schedules of the same blocked algorithms, chosen by how many independent matrices there are:
+//  * many matrices (batched restarts): LEFT-looking.  Every tile accumulates its whole update in
+//    registers over a long K range and is written once, so the GEMMs run at long-K efficiency and
+//    each tile of C is read/written O(1) times instead of once per 128-wide step;
+//  * few matrices (the final factor, n large): RIGHT-looking, which exposes (NB-k)^2/2 tiles per
+//    step to fill 148 SMs from a single matrix.
+static bool use_left_looking(int NB, int R) { return (long)R * NB >= 4 * 148; }
+
+static int launch_diag(const FitBuffers& fb, int NP, int R, int k, int* info, cudaStream_t st) {
     const int NB = NP / TILE;
     const long sK = (long)NP * NP, sD = (long)NB * TILE * TILE;
     static bool configured = false;
@@ -418,19 +425,40 @@ static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStr
                                      (int)DIAG_SMEM));
         configured = true;
     }
+    TB_LAUNCH(diag_potrf_inv_kernel, dim3(R), dim3(256), DIAG_SMEM, st, fb.K, (long)NP, sK, k, fb.Dinv, sD, info);
+    return 0;
+}
+
+// panel: A[i,k] <- A[i,k] * Dinv_k^T  (i > k), in place
+static int launch_panel(const FitBuffers& fb, int NP, int R, int k, cudaStream_t st) {
+    const int NB = NP / TILE, rem = NB - k - 1;
+    const long sK = (long)NP * NP, sD = (long)NB * TILE * TILE;
+    double* panel = fb.K + (long)(k + 1) * TILE * NP + (long)k * TILE;
+    GemmParams p = gemm_params(panel, NP, fb.Dinv + (long)k * TILE * TILE, TILE, panel, NP, rem, 1, TILE, 1.0, 0.0);
+    p.sA1 = sK; p.sB1 = sD; p.sC1 = sK;
+    return launch_gemm<false, true>(p, R, 1, st);
+}
+
+// blocked Cholesky of R matrices in fb.K (lower), Dinv blocks kept for trtri
+static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStream_t st) {
+    const int NB = NP / TILE;
+    const long sK = (long)NP * NP;
+    const bool left = use_left_looking(NB, R);
     for (int k = 0; k < NB; ++k) {
-        TB_LAUNCH(diag_potrf_inv_kernel, dim3(R), dim3(256), DIAG_SMEM, st, fb.K, (long)NP, sK, k, fb.Dinv, sD, info);
-        const int rem = NB - k - 1;
-        if (rem == 0) break;
-        // panel: A[i,k] <- A[i,k] * Dinv_k^T  (i > k), in place
-        {
-            double* panel = fb.K + (long)(k + 1) * TILE * NP + (long)k * TILE;
-            GemmParams p = gemm_params(panel, NP, fb.Dinv + (long)k * TILE * TILE, TILE, panel, NP, rem, 1, TILE, 1.0, 0.0);
-            p.sA1 = sK; p.sB1 = sD; p.sC1 = sK;
+        if (left && k > 0) {
+            // block column k: A[i,k] -= L[i,0:k] L[k,0:k]^T  (i >= k), K = k*128 accumulated in registers
+            const double* rows = fb.K + (long)k * TILE * NP;
+            double* col = fb.K + (long)k * TILE * NP + (long)k * TILE;
+            GemmParams p = gemm_params(rows, NP, rows, NP, col, NP, NB - k, 1, k * TILE, -1.0, 1.0);
+            p.sA1 = sK; p.sB1 = sK; p.sC1 = sK;
             if (launch_gemm<false, true>(p, R, 1, st)) return -1;
         }
-        // trailing: A[i,j] -= A[i,k] A[j,k]^T  (k < j <= i)
-        {
+        if (launch_diag(fb, NP, R, k, info, st)) return -1;
+        const int rem = NB - k - 1;
+        if (rem == 0) break;
+        if (launch_panel(fb, NP, R, k, st)) return -1;
+        if (!left) {
+            // trailing: A[i,j] -= A[i,k] A[j,k]^T  (k < j <= i)
             const double* panel = fb.K + (long)(k + 1) * TILE * NP + (long)k * TILE;
             double* trail = fb.K + (long)(k + 1) * TILE * NP + (long)(k + 1) * TILE;
             GemmParams p = gemm_params(panel, NP, panel, NP, trail, NP, rem, rem, TILE, -1.0, 1.0);
@@ -442,10 +470,40 @@ static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStr
     return 0;
 }
 
-// Linv = L^-1 for R factors: right-looking TRSM of the identity using the inverted diagonal blocks
+// Linv diagonal tiles <- Dinv blocks (everything else of Linv was zeroed)
+__global__ void __launch_bounds__(256) place_diag_blocks_kernel(const double* __restrict__ Dinv, long strideD,
+                                                                double* __restrict__ Linv, int NP) {
+    const int kb = blockIdx.x, r = blockIdx.y;
+    const double* D = Dinv + (long)r * strideD + (long)kb * TILE * TILE;
+    double* out = Linv + (long)r * NP * NP + (long)kb * TILE * NP + (long)kb * TILE;
+    for (int e = threadIdx.x; e < TILE * TILE; e += blockDim.x) {
+        const int i = e >> 7, j = e & 127;
+        out[(long)i * NP + j] = D[e];
+    }
+}
+
+// Linv = L^-1 for R factors, from the inverted diagonal blocks; GEMM only
 static int trtri_batched(const FitBuffers& fb, double* Linv, int NP, int R, cudaStream_t st) {
     const int NB = NP / TILE;
     const long sK = (long)NP * NP, sD = (long)NB * TILE * TILE;
+    if (use_left_looking(NB, R)) {
+        // row block i:  X[i,c] = -Dinv_i * sum_{k=c}^{i-1} L[i,k] X[k,c]  (c < i),  X[i,i] = Dinv_i
+        TB_CUDA(cudaMemsetAsync(Linv, 0, sizeof(double) * (size_t)R * NP * NP, st));
+        TB_LAUNCH(place_diag_blocks_kernel, dim3(NB, R), dim3(256), 0, st, fb.Dinv, sD, Linv, NP);
+        for (int i = 1; i < NB; ++i) {
+            const double* Lrow = fb.K + (long)i * TILE * NP;
+            double* Xrow = Linv + (long)i * TILE * NP;
+            GemmParams p = gemm_params(Lrow, NP, Linv, NP, Xrow, NP, 1, i, i * TILE, -1.0, 0.0);
+            p.klo_mode = KLO_BY_TJ;  // X[k,c] = 0 for k < c
+            p.sA1 = sK; p.sB1 = sK; p.sC1 = sK;
+            if (launch_gemm<false, false>(p, R, 1, st)) return -1;
+            GemmParams q = gemm_params(fb.Dinv + (long)i * TILE * TILE, TILE, Xrow, NP, Xrow, NP, 1, i, TILE, 1.0, 0.0);
+            q.sA1 = sD; q.sB1 = sK; q.sC1 = sK;
+            if (launch_gemm<false, false>(q, R, 1, st)) return -1;
+        }
+        return 0;
+    }
+    // right-looking TRSM of the identity
     {
         const long total = (long)NP * NP;
         TB_LAUNCH(set_identity_kernel, dim3((unsigned)((total + 255) / 256), R), dim3(256), 0, st, Linv, NP);

@@ -3,17 +3,20 @@
 // variance V = Linv * Kstar^T with a fused column sum-of-squares epilogue.
 //
 // sm_100a has no FP64 kind on tcgen05/TMEM; FP64 tensor work is warp-level mma.sync m8n8k4
-// (every larger f64 shape lowers to DMMA.8x8x4 in SASS), so this is a classic multi-stage
-// cp.async (LDGSTS) pipeline: 128x128x16 CTA tile, 8 warps of 32x64, accumulators in registers.
-// FP64 math is slow enough (64 FMA/clk/SM) that the L2->SMEM stream (8 B/clk/SM) and the SMEM
-// fragment loads (24 B/clk/SM) are far from their limits; the design goal is simply to keep the
-// DMMA pipe issuing back to back.
+// (every larger f64 shape lowers to DMMA.8x8x4 in SASS) and DMMA shares the FP64 pipe with DFMA
+// (measured: half DMMA / half DFMA warps = 34 TFLOP/s, no concurrency), so the only lever is to keep
+// that one pipe issuing back to back.  128x128x16 CTA tile, 16 warps of 32x32 (4 per scheduler),
+// 4-stage cp.async (LDGSTS) pipeline where tile kt+1 is guaranteed landed one iteration early so
+// the first fragments of the next k-tile are fetched BEFORE the per-tile barrier: the DMMA pipe
+// never waits on an LDS after a barrier (profiles/r1_gemm_sweep.md: 29.8 -> 33.1 TFLOP/s).
 #pragma once
 #include "common.cuh"
 
 namespace tb200 {
 
-constexpr int G_TM = 128, G_TN = 128, G_TK = 16, G_STAGES = 3, G_THREADS = 256;
+constexpr int G_TM = 128, G_TN = 128, G_TK = 16, G_STAGES = 4, G_THREADS = 512;
+constexpr int G_WM = 4, G_WN = 4;  // warp grid; warp tile 32 x 32
+constexpr int G_MI = G_TM / G_WM / 8, G_NJ = G_TN / G_WN / 8;
 constexpr int G_LDN = G_TK + 4;    // row stride (doubles) of a [row][k] tile: conflict-free fragment loads
 constexpr int G_LDT = G_TM + 4;    // row stride of a [k][row] tile
 constexpr int G_TILE_ELEMS = (G_TM * G_LDN > G_TK * G_LDT) ? G_TM * G_LDN : G_TK * G_LDT;
@@ -60,14 +63,14 @@ template <bool TRANS>
 __device__ __forceinline__ void load_tile(double* s, const double* g, long ld, int row0, int k0, int tid) {
     if (!TRANS) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
+        for (int i = 0; i < G_TM * G_TK / 2 / G_THREADS; ++i) {
             const int c = tid + i * G_THREADS;  // 1024 chunks of 16 B
             const int r = c >> 3, kc = c & 7;
             cp_async16(s + r * G_LDN + kc * 2, g + (long)(row0 + r) * ld + k0 + kc * 2);
         }
     } else {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
+        for (int i = 0; i < G_TM * G_TK / 2 / G_THREADS; ++i) {
             const int c = tid + i * G_THREADS;
             const int kr = c >> 6, cc = c & 63;
             cp_async16(s + kr * G_LDT + cc * 2, g + (long)(k0 + kr) * ld + row0 + cc * 2);
@@ -87,7 +90,7 @@ template <bool TA, bool TB>
 __global__ void __launch_bounds__(G_THREADS, 1) gemm_f64_kernel(const GemmParams p) {
     extern __shared__ __align__(16) double smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int wm = warp & 3, wn = warp >> 2;  // 4 x 2 warps, warp tile 32 x 64
+    const int wm = warp % G_WM, wn = warp / G_WM;  // 4 x 4 warps, warp tile 32 x 32
     const int g = lane >> 2, kk = lane & 3;
 
     int ti, tj;
@@ -113,11 +116,11 @@ __global__ void __launch_bounds__(G_THREADS, 1) gemm_f64_kernel(const GemmParams
     double* C = p.C + blockIdx.y * p.sC1 + blockIdx.z * p.sC2;
     const int row0 = ti * G_TM, col0 = tj * G_TN;
 
-    double acc[4][8][2];
+    double acc[G_MI][G_NJ][2];
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
+    for (int i = 0; i < G_MI; ++i)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+        for (int j = 0; j < G_NJ; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
     auto sA = [&](int st) { return smem + (size_t)st * 2 * G_TILE_ELEMS; };
     auto sB = [&](int st) { return smem + (size_t)st * 2 * G_TILE_ELEMS + G_TILE_ELEMS; };
@@ -130,27 +133,42 @@ __global__ void __launch_bounds__(G_THREADS, 1) gemm_f64_kernel(const GemmParams
         }
         cp_async_commit();
     };
+    const int arow = wm * (G_TM / G_WM) + g, bcol = wn * (G_TN / G_WN) + g;
+    auto load_frags = [&](int st, int ks, double (&af)[G_MI], double (&bf)[G_NJ]) {
+        const double* a_s = sA(st);
+        const double* b_s = sB(st);
+#pragma unroll
+        for (int i = 0; i < G_MI; ++i) af[i] = frag<TA>(a_s, arow + i * 8, ks * 4 + kk);
+#pragma unroll
+        for (int j = 0; j < G_NJ; ++j) bf[j] = frag<!TB>(b_s, bcol + j * 8, ks * 4 + kk);
+    };
 
 #pragma unroll
     for (int s = 0; s < G_STAGES - 1; ++s) issue(s);
 
+    double af[G_MI], bf[G_NJ];
+    cp_async_wait<G_STAGES - 2>();
+    __syncthreads();
+    load_frags(0, 0, af, bf);
     for (int kt = 0; kt < nk; ++kt) {
-        cp_async_wait<G_STAGES - 2>();
+        // after this barrier tile kt+1 has landed for every thread and stage (kt-1)%STAGES is free
+        cp_async_wait<G_STAGES - 3>();
         __syncthreads();
         issue(kt + G_STAGES - 1);
-        const double* a_s = sA(kt % G_STAGES);
-        const double* b_s = sB(kt % G_STAGES);
+        const int st = kt % G_STAGES, stn = (kt + 1) % G_STAGES;
 #pragma unroll
         for (int ks = 0; ks < G_TK / 4; ++ks) {
-            double af[4], bf[8];
+            double an[G_MI], bn[G_NJ];
+            if (ks + 1 < G_TK / 4) load_frags(st, ks + 1, an, bn);
+            else if (kt + 1 < nk) load_frags(stn, 0, an, bn);
 #pragma unroll
-            for (int i = 0; i < 4; ++i) af[i] = frag<TA>(a_s, wm * 32 + i * 8 + g, ks * 4 + kk);
+            for (int i = 0; i < G_MI; ++i)
 #pragma unroll
-            for (int j = 0; j < 8; ++j) bf[j] = frag<!TB>(b_s, wn * 64 + j * 8 + g, ks * 4 + kk);
+                for (int j = 0; j < G_NJ; ++j) dmma884(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+            for (int i = 0; i < G_MI; ++i) af[i] = an[i];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) dmma884(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+            for (int j = 0; j < G_NJ; ++j) bf[j] = bn[j];
         }
     }
     cp_async_wait<0>();
@@ -158,11 +176,11 @@ __global__ void __launch_bounds__(G_THREADS, 1) gemm_f64_kernel(const GemmParams
 
     if (p.epi == EPI_STORE) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const long r = row0 + wm * 32 + i * 8 + g;
+        for (int i = 0; i < G_MI; ++i) {
+            const long r = row0 + arow + i * 8;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                double2* dst = reinterpret_cast<double2*>(C + r * p.ldc + col0 + wn * 64 + j * 8 + kk * 2);
+            for (int j = 0; j < G_NJ; ++j) {
+                double2* dst = reinterpret_cast<double2*>(C + r * p.ldc + col0 + wn * (G_TN / G_WN) + j * 8 + kk * 2);
                 double2 v;
                 v.x = p.alpha * acc[i][j][0];
                 v.y = p.alpha * acc[i][j][1];
@@ -175,12 +193,12 @@ __global__ void __launch_bounds__(G_THREADS, 1) gemm_f64_kernel(const GemmParams
             }
         }
     } else {  // EPI_COLSUMSQ: partial[ti][col] = sum over the tile's 128 rows of acc^2 (fixed order)
-        double* red = smem;  // [4 warps along M][128 cols]
+        double* red = smem;  // [G_WM warps along M][128 cols]
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
+        for (int j = 0; j < G_NJ; ++j) {
             double s0 = 0.0, s1 = 0.0;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
+            for (int i = 0; i < G_MI; ++i) {
                 s0 += acc[i][j][0] * acc[i][j][0];
                 s1 += acc[i][j][1] * acc[i][j][1];
             }
@@ -190,8 +208,8 @@ __global__ void __launch_bounds__(G_THREADS, 1) gemm_f64_kernel(const GemmParams
                 s1 += __shfl_xor_sync(0xffffffffu, s1, o);
             }
             if (g == 0) {
-                red[wm * G_TN + wn * 64 + j * 8 + kk * 2] = s0;
-                red[wm * G_TN + wn * 64 + j * 8 + kk * 2 + 1] = s1;
+                red[wm * G_TN + wn * (G_TN / G_WN) + j * 8 + kk * 2] = s0;
+                red[wm * G_TN + wn * (G_TN / G_WN) + j * 8 + kk * 2 + 1] = s1;
             }
         }
         __syncthreads();
