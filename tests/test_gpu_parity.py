@@ -156,6 +156,41 @@ def test_lml_batched_members_are_independent(golden):
         np.testing.assert_allclose(grad[r], og, rtol=1e-6, atol=1e-6 * np.abs(og).max())
 
 
+def test_left_looking_schedule_matches_right_looking_and_oracle():
+    """many restarts switch potrf/trtri to the left-looking (long-K) schedule (fit.cu use_left_looking):
+    same numbers as the right-looking schedule used for a single matrix, and as the oracle"""
+    from turbo_b200 import device
+    tb = _tb()
+    rng = np.random.default_rng(11)
+    n, d, R = 520, 4, 120            # NB = 5 -> R*NB = 600 >= 4*148: left-looking
+    X = rng.random((n, d))
+    y = np.sin(3 * X).sum(axis=1) + 0.05 * rng.standard_normal(n)
+    y = (y - y.mean()) / y.std()
+    spec = tb.KernelSpec(3, d, True)
+    base = np.log(np.r_[1.0, np.full(d, 0.4), 1e-3])
+    T = base + rng.normal(0, 0.3, (R, base.size))
+    X_dev, y_dev = device.to_device(X), device.to_device(y)
+    lml, grad, info = device.lml_batched(X_dev, y_dev, n, spec, T, 1e-10, True)
+    assert not info.any()
+    ospec = O.KernelSpec(3, d, True)
+    for r in (0, 7, R - 1):
+        l1, g1, _ = device.lml_batched(X_dev, y_dev, n, spec, T[r:r + 1], 1e-10, True)   # right-looking
+        assert lml[r] == pytest.approx(l1[0], rel=1e-10)
+        np.testing.assert_allclose(grad[r], g1[0], rtol=1e-8, atol=1e-8 * np.abs(g1[0]).max())
+        ol, og = O.log_marginal_likelihood(ospec, T[r], X, y, 1e-10, True)
+        assert lml[r] == pytest.approx(ol, rel=1e-6)
+        np.testing.assert_allclose(grad[r], og, rtol=1e-6, atol=1e-6 * np.abs(og).max())
+    # a non-PD member inside a left-looking batch is flagged and does not disturb the others
+    T2 = T.copy()
+    T2[5, -1] = -80.0                # noise ~ 0
+    T2[5, 1:-1] = 6.0                # huge length scales -> numerically singular with jitter 0
+    lml2, grad2, info2 = device.lml_batched(X_dev, y_dev, n, spec, T2, 0.0, True)
+    assert info2[5] > 0 and lml2[5] == -np.inf and not grad2[5].any()
+    keep = np.arange(R) != 5
+    lml0, _, info0 = device.lml_batched(X_dev, y_dev, n, spec, T, 0.0, True)
+    assert not info2[keep].any() and np.array_equal(lml2[keep], lml0[keep])
+
+
 def test_non_positive_definite_member_is_flagged():
     from turbo_b200 import device
     tb = _tb()
