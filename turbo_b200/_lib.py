@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libturbo_b200.so")
+LIB_PATH = os.environ.get("TB200_LIB") or os.path.join(_HERE, "libturbo_b200.so")  # TB200_LIB: A/B builds
 MAX_D = 64
 
 KIND_RBF, KIND_MATERN12, KIND_MATERN32, KIND_MATERN52 = 0, 1, 2, 3

@@ -13,6 +13,8 @@
 //   4. acquire_epilogue  : var = k** - sum partial, clamp, de-normalise, EI/PI/UCB, running argmax
 // The candidate matrix, K*, V, mu, sigma and the acquisition values are not written to HBM unless
 // the caller asks for them (mu_out / sigma_out / acq_out).
+#include <stdlib.h>
+
 #include <vector>
 
 #include "gemm_f64.cuh"
@@ -116,7 +118,7 @@ __global__ void __launch_bounds__(256) kstar_mean_kernel(const double* __restric
                                                          const double* __restrict__ XsT, int n, int NP,
                                                          tb200_kernel_spec spec, const double* __restrict__ theta,
                                                          const double* __restrict__ alpha, double* __restrict__ Ks,
-                                                         double* __restrict__ mean) {
+                                                         double* __restrict__ mean, int jchunk, long mean_stride) {
     extern __shared__ double sh[];  // xc[CPB][d] scaled candidates, red[8][CPB]
     const int d = spec.d;
     double* xc = sh;
@@ -133,7 +135,9 @@ __global__ void __launch_bounds__(256) kstar_mean_kernel(const double* __restric
     double msum[CPB];
 #pragma unroll
     for (int c = 0; c < CPB; ++c) msum[c] = 0.0;
-    for (int j = threadIdx.x; j < NP; j += blockDim.x) {
+    // blockIdx.y owns training points [jlo, jhi): enough CTAs to fill the SMs at batch ~ 2048
+    const int jlo = blockIdx.y * jchunk, jhi = min(NP, jlo + jchunk);
+    for (int j = jlo + threadIdx.x; j < jhi; j += blockDim.x) {
         double r2[CPB];
 #pragma unroll
         for (int c = 0; c < CPB; ++c) r2[c] = 0.0;
@@ -164,7 +168,7 @@ __global__ void __launch_bounds__(256) kstar_mean_kernel(const double* __restric
     if (threadIdx.x < CPB) {
         double t = 0.0;
         for (int w = 0; w < 8; ++w) t += red[w * CPB + threadIdx.x];
-        mean[c0 + threadIdx.x] = t;
+        mean[blockIdx.y * mean_stride + c0 + threadIdx.x] = t;  // partial mean; the epilogue adds the splits in order
     }
 }
 
@@ -182,7 +186,7 @@ __device__ __forceinline__ bool better(double v, int64_t i, double bv, int64_t b
 }
 
 __global__ void __launch_bounds__(1024) acquire_epilogue_kernel(
-    const double* __restrict__ mean, const double* __restrict__ partial, int ntiles, long ldp, int64_t batch,
+    const double* __restrict__ mean, int nsplit, const double* __restrict__ partial, int ntiles, long ldp, int64_t batch,
     int64_t m_valid, int64_t local_base, int64_t index_base, tb200_kernel_spec spec,
     const double* __restrict__ theta, tb200_acq_spec acq,
     double* __restrict__ mu_out, double* __restrict__ sigma_out, double* __restrict__ acq_out,
@@ -200,7 +204,9 @@ __global__ void __launch_bounds__(1024) acquire_epilogue_kernel(
         if (var < 0.0) var = 0.0;                   // sklearn:_gpr.py:485-491
         var = var * (acq.y_std * acq.y_std);        // :494
         const double sigma = sqrt(var);
-        const double mu = acq.y_std * mean[c] + acq.y_mean;  // :450
+        double ms = 0.0;
+        for (int t = 0; t < nsplit; ++t) ms += mean[(long)t * ldp + c];
+        const double mu = acq.y_std * ms + acq.y_mean;  // :450
         double a;
         if (acq.acq == TB200_UCB) {
             a = isinf(acq.param) ? sigma : acq.sign * mu + acq.param * sigma;
@@ -294,9 +300,16 @@ struct AcqBuffers {
     double* Ks;       // [batch][NP]
     double* mean;     // [batch]
     double* partial;  // [NB][batch]
+    double* best_val; // [1] running best of this slot
+    int64_t* best_idx;
 };
 
 static size_t a256(size_t b) { return (b + 255) / 256 * 256; }
+
+// Two slots: consecutive candidate batches alternate between two internal streams so that the tail
+// of one batch's triangular GEMM, its epilogue and the next batch's K* kernel overlap.
+constexpr int ACQ_SLOTS = 2;
+constexpr int KSPLIT_MAX = 8;  // K* kernel: training points split over up to 8 CTAs per candidate group
 
 static size_t acquire_layout(int n, int d, int64_t batch, AcqBuffers* ab, char* base) {
     const size_t NP = pad_n(n), NB = NP / TILE;
@@ -306,12 +319,54 @@ static size_t acquire_layout(int n, int d, int64_t batch, AcqBuffers* ab, char* 
         off += a256(bytes);
         return reinterpret_cast<double*>(ptr);
     };
-    double* cand = take(sizeof(double) * batch * d);
-    double* Ks = take(sizeof(double) * batch * NP);
-    double* mean = take(sizeof(double) * batch);
-    double* partial = take(sizeof(double) * NB * batch);
-    if (ab) { ab->cand = cand; ab->Ks = Ks; ab->mean = mean; ab->partial = partial; }
+    for (int s = 0; s < ACQ_SLOTS; ++s) {
+        double* cand = take(sizeof(double) * batch * d);
+        double* Ks = take(sizeof(double) * batch * NP);
+        double* mean = take(sizeof(double) * KSPLIT_MAX * batch);
+        double* partial = take(sizeof(double) * NB * batch);
+        double* bv = take(sizeof(double));
+        int64_t* bi = reinterpret_cast<int64_t*>(take(sizeof(int64_t)));
+        if (ab) { ab[s].cand = cand; ab[s].Ks = Ks; ab[s].mean = mean; ab[s].partial = partial;
+                  ab[s].best_val = bv; ab[s].best_idx = bi; }
+    }
     return off;
+}
+
+// merge the per-slot bests into the caller's running best (read-modify-write, single thread)
+__global__ void best_merge_kernel(const double* v0, const int64_t* i0, const double* v1, const int64_t* i1,
+                                  double* best_val, int64_t* best_idx) {
+    double gv = *best_val;
+    int64_t gi = *best_idx;
+    if (*i0 >= 0 && better(*v0, *i0, gv, gi)) { gv = *v0; gi = *i0; }
+    if (v1 && *i1 >= 0 && better(*v1, *i1, gv, gi)) { gv = *v1; gi = *i1; }
+    *best_val = gv;
+    *best_idx = gi;
+}
+
+// internal streams / events, one set per device, created on first use
+struct AcqStreams {
+    bool ready = false;
+    cudaStream_t s[ACQ_SLOTS];
+    cudaEvent_t fork, join[ACQ_SLOTS];
+};
+static AcqStreams g_streams[64];
+static int g_acq_streams = -1;  // -1: read TB200_ACQ_STREAMS on first use
+
+static int acq_streams_for_device(AcqStreams** out) {
+    int dev = 0;
+    TB_CUDA(cudaGetDevice(&dev));
+    TB_CHECK(dev >= 0 && dev < 64, "device ordinal out of range");
+    AcqStreams& a = g_streams[dev];
+    if (!a.ready) {
+        for (int i = 0; i < ACQ_SLOTS; ++i) {
+            TB_CUDA(cudaStreamCreateWithFlags(&a.s[i], cudaStreamNonBlocking));
+            TB_CUDA(cudaEventCreateWithFlags(&a.join[i], cudaEventDisableTiming));
+        }
+        TB_CUDA(cudaEventCreateWithFlags(&a.fork, cudaEventDisableTiming));
+        a.ready = true;
+    }
+    *out = &a;
+    return 0;
 }
 
 }  // namespace tb200
@@ -321,8 +376,10 @@ using namespace tb200;
 extern "C" {
 
 int64_t tb200_default_batch(int n) {
-    // keep Ks (batch x NP doubles) around 64 MB so it lives in the 126 MB L2 next to the streamed
-    // Linv tiles, but never below 256 candidates (tile balance) nor above 4096
+    // 64 MB of K* per slot: large enough that one launch is >= 3 waves of GEMM tiles at n = 4096
+    // (measured: 2048 per slot beats 1024 by 3 % even though two slots + Linv exceed the 126 MB L2;
+    // the GEMM re-reads K* tiles from L2/HBM at < 5 % of HBM bandwidth), never below 256 candidates
+    // (tile balance) nor above 4096
     const int64_t NP = pad_n(n);
     int64_t b = (64ll << 20) / (NP * 8);
     b = b / 128 * 128;
@@ -374,34 +431,72 @@ int tb200_acquire(const double* Xc, int64_t m, int64_t index_base, const tb200_c
     TB_CHECK(batch % 128 == 0, "batch must be a multiple of 128");
     cudaStream_t st = (cudaStream_t)stream;
     const int NP = pad_n(n), NB = NP / TILE, d = spec->d;
-    AcqBuffers ab;
-    const size_t need = acquire_layout(n, d, batch, &ab, (char*)work);
+    AcqBuffers ab[ACQ_SLOTS];
+    const size_t need = acquire_layout(n, d, batch, ab, (char*)work);
     TB_CHECK(work_bytes >= need, "workspace too small (see tb200_acquire_workspace_bytes)");
 
+    if (g_acq_streams < 0) {
+        const char* e = getenv("TB200_ACQ_STREAMS");
+        g_acq_streams = (e && atoi(e) == 1) ? 1 : ACQ_SLOTS;
+    }
+    // one batch, serial mode, or GEMM timing requested: everything on the caller's stream
+    const int64_t nbatches = (m + batch - 1) / batch;
+    const int slots = (nbatches < 2 || g_time_gemm) ? 1 : g_acq_streams;
+    AcqStreams* as = nullptr;
+    cudaStream_t ss[ACQ_SLOTS] = {st, st};
+    if (slots > 1) {
+        if (acq_streams_for_device(&as)) return -1;
+        TB_CUDA(cudaEventRecord(as->fork, st));
+        for (int i = 0; i < slots; ++i) {
+            ss[i] = as->s[i];
+            TB_CUDA(cudaStreamWaitEvent(ss[i], as->fork, 0));
+        }
+    }
+    for (int i = 0; i < slots; ++i)
+        TB_LAUNCH(best_reset_kernel, dim3(1), dim3(1), 0, ss[i], ab[i].best_val, ab[i].best_idx);
+
     const size_t ksm = sizeof(double) * (CPB * d + 8 * CPB);
-    for (int64_t off = 0; off < m; off += batch) {
+    // split the training points so one K* launch is ~2k CTAs (3 resident per SM): NB/ksplit tiles each
+    int ksplit = NB < KSPLIT_MAX ? NB : KSPLIT_MAX;
+    const int jchunk = (NB + ksplit - 1) / ksplit * TILE;
+    ksplit = (NP + jchunk - 1) / jchunk;
+    int64_t bno = 0;
+    for (int64_t off = 0; off < m; off += batch, ++bno) {
+        const int sl = (int)(bno % slots);
+        const AcqBuffers& w = ab[sl];
+        cudaStream_t cs = ss[sl];
         const int64_t mb = (m - off < batch) ? (m - off) : batch;          // valid candidates
         const int64_t mbp = (mb + 127) / 128 * 128;                          // padded to GEMM tiles
         const double* xc = Xc ? Xc + off * d : nullptr;
         if (mode != TB200_CAND_GIVEN) {
             const CandGen g = make_gen(*cand, d);
             const int64_t total = mb * d;
-            TB_LAUNCH(generate_candidates_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, st, g, d,
-                      index_base + off, mb, ab.cand);
-            xc = ab.cand;
+            TB_LAUNCH(generate_candidates_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, cs, g, d,
+                      index_base + off, mb, w.cand);
+            xc = w.cand;
         }
-        TB_LAUNCH(kstar_mean_kernel, dim3((unsigned)(mbp / CPB)), dim3(256), ksm, st, xc, mb, XsT, n, NP, *spec, theta,
-                  alpha, ab.Ks, ab.mean);
-        GemmParams gp = gemm_params(Linv, NP, ab.Ks, NP, ab.partial, batch, NB, (int)(mbp / 128), NP, 1.0, 0.0);
+        TB_LAUNCH(kstar_mean_kernel, dim3((unsigned)(mbp / CPB), ksplit), dim3(256), ksm, cs, xc, mb, XsT, n, NP, *spec,
+                  theta, alpha, w.Ks, w.mean, jchunk, (long)batch);
+        GemmParams gp = gemm_params(Linv, NP, w.Ks, NP, w.partial, batch, NB, (int)(mbp / 128), NP, 1.0, 0.0);
         gp.order = ORDER_RECT_HEAVY_LAST_ROW_FIRST;
         gp.khi_mode = KHI_BY_TI;
+        gp.a_tri_diag = getenv("TB200_NO_TRI") ? 0 : 1;  // Linv is lower triangular
         gp.epi = EPI_COLSUMSQ;
-        if (g_time_gemm) TB_CUDA(cudaEventRecord(next_event(), st));
-        if (launch_gemm<false, true>(gp, 1, 1, st)) return -1;
-        if (g_time_gemm) TB_CUDA(cudaEventRecord(next_event(), st));
-        TB_LAUNCH(acquire_epilogue_kernel, dim3(1), dim3(1024), 0, st, ab.mean, ab.partial, NB, (long)batch, mbp, mb,
-                  off, index_base, *spec, theta, *acq, mu_out, sigma_out, acq_out, best_val, best_idx);
+        if (g_time_gemm) TB_CUDA(cudaEventRecord(next_event(), cs));
+        if (launch_gemm<false, true>(gp, 1, 1, cs)) return -1;
+        if (g_time_gemm) TB_CUDA(cudaEventRecord(next_event(), cs));
+        TB_LAUNCH(acquire_epilogue_kernel, dim3(1), dim3(1024), 0, cs, w.mean, ksplit, w.partial, NB, (long)batch, mbp, mb,
+                  off, index_base, *spec, theta, *acq, mu_out, sigma_out, acq_out, w.best_val, w.best_idx);
     }
+    if (slots > 1) {
+        for (int i = 0; i < slots; ++i) {
+            TB_CUDA(cudaEventRecord(as->join[i], ss[i]));
+            TB_CUDA(cudaStreamWaitEvent(st, as->join[i], 0));
+        }
+    }
+    TB_LAUNCH(best_merge_kernel, dim3(1), dim3(1), 0, st, ab[0].best_val, ab[0].best_idx,
+              slots > 1 ? ab[1].best_val : (const double*)nullptr, slots > 1 ? ab[1].best_idx : (const int64_t*)nullptr,
+              best_val, best_idx);
     return 0;
 }
 

@@ -38,6 +38,7 @@ struct GemmParams {
     int K;               // multiple of 16
     double alpha, beta;
     int order, klo_mode, khi_mode, epi;
+    int a_tri_diag;      // with KHI_BY_TI: A's diagonal 128-block is lower triangular -> warps skip its zero k-range
 };
 
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
@@ -90,7 +91,13 @@ template <bool TA, bool TB>
 __global__ void __launch_bounds__(G_THREADS, 1) gemm_f64_kernel(const GemmParams p) {
     extern __shared__ __align__(16) double smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int wm = warp % G_WM, wn = warp / G_WM;  // 4 x 4 warps, warp tile 32 x 32
+    // 4 x 4 warps, warp tile 32 x 32; the four warps of one scheduler (warp % 4) cover all four wm, so the
+    // triangular skip below removes the same amount of work from every scheduler
+#ifdef TB_MAP_OLD
+    const int wm = warp % G_WM, wn = warp / G_WM;
+#else
+    const int wm = warp / G_WN, wn = warp % G_WN;
+#endif
     const int g = lane >> 2, kk = lane & 3;
 
     int ti, tj;
@@ -150,11 +157,13 @@ __global__ void __launch_bounds__(G_THREADS, 1) gemm_f64_kernel(const GemmParams
     cp_async_wait<G_STAGES - 2>();
     __syncthreads();
     load_frags(0, 0, af, bf);
-    for (int kt = 0; kt < nk; ++kt) {
+    auto sync_and_issue = [&](int kt) {
         // after this barrier tile kt+1 has landed for every thread and stage (kt-1)%STAGES is free
         cp_async_wait<G_STAGES - 3>();
         __syncthreads();
         issue(kt + G_STAGES - 1);
+    };
+    auto compute = [&](int kt) {
         const int st = kt % G_STAGES, stn = (kt + 1) % G_STAGES;
 #pragma unroll
         for (int ks = 0; ks < G_TK / 4; ++ks) {
@@ -169,6 +178,20 @@ __global__ void __launch_bounds__(G_THREADS, 1) gemm_f64_kernel(const GemmParams
             for (int i = 0; i < G_MI; ++i) af[i] = an[i];
 #pragma unroll
             for (int j = 0; j < G_NJ; ++j) bf[j] = bn[j];
+        }
+    };
+    // main k-range, then (a_tri_diag) the lower-triangular diagonal block where rows wm*32..+31 are zero
+    // for k >= (wm+1)*32: those warps skip the DMMAs but keep taking part in barriers and copies
+    const int nk_main = p.a_tri_diag ? nk - G_TM / G_TK : nk;
+    for (int kt = 0; kt < nk_main; ++kt) {
+        sync_and_issue(kt);
+        compute(kt);
+    }
+    if (p.a_tri_diag) {
+        const int kt_end = nk_main + (wm + 1) * (G_TM / G_WM / G_TK);
+        for (int kt = nk_main; kt < nk; ++kt) {
+            sync_and_issue(kt);
+            if (kt < kt_end) compute(kt);
         }
     }
     cp_async_wait<0>();
@@ -242,7 +265,7 @@ inline GemmParams gemm_params(const double* A, long lda, const double* B, long l
     p.lda = lda; p.ldb = ldb; p.ldc = ldc;
     p.tilesM = tilesM; p.tilesN = tilesN; p.K = K;
     p.alpha = alpha; p.beta = beta;
-    p.order = ORDER_RECT; p.klo_mode = KLO_ZERO; p.khi_mode = KHI_FULL; p.epi = EPI_STORE;
+    p.order = ORDER_RECT; p.klo_mode = KLO_ZERO; p.khi_mode = KHI_FULL; p.epi = EPI_STORE; p.a_tri_diag = 0;
     return p;
 }
 
