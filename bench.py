@@ -27,11 +27,17 @@ import time
 
 import numpy as np
 
+if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+    os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 N_TRAIN, DIM = 4096, 10
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
+# `ncu --set full` captures under profiles/ (None until captured for that engine)
+TRAFFIC = {"dmma": 197.2e6, "i8": None, "i8x": None}
 METRIC = "EI candidates/sec (n=4096,d=10)"
 
 
@@ -172,7 +178,8 @@ def run_ours(args):
     torch.cuda.synchronize()
     factor_ms_cold = 1e3 * (time.perf_counter() - t0)
     acq, _ = tb.GpuEI(0.01).construct_function(0, model, "min", float(y.min()))
-    a = device.Acquirer(model.factor, acq._spec_c(), args.batch)
+    a = device.Acquirer(model.factor, acq._spec_c(), args.batch, engine=args.engine)
+    engine = a.engine
 
     # synthetic candidates: this rank's slice of a global uniform set (335 MB at m=2^22 > 126 MB L2)
     gen = _lib.cand_spec(_lib.CAND_UNIFORM, 7, m * world, [0.0] * d, [1.0] * d)
@@ -195,7 +202,7 @@ def run_ours(args):
     def step_e2e():
         # the plugin call a user makes: host candidates in, (value, index, x) out
         if world > 1:
-            a2 = device.Acquirer(model.factor, acq._spec_c(), args.batch)
+            a2 = device.Acquirer(model.factor, acq._spec_c(), args.batch, engine=args.engine)
             copy_stream, main = torch.cuda.Stream(), torch.cuda.current_stream()
             for off in range(0, m, 1 << 18):
                 cnt = min(1 << 18, m - off)
@@ -207,7 +214,7 @@ def run_ours(args):
                 buf.record_stream(main)
             v, i = a2.best()
             return dist.allreduce_argmax(v, i, group)
-        v, i, _x = acq.argmax_over(candidates=Xc_host, batch=args.batch)
+        v, i, _x = acq.argmax_over(candidates=Xc_host, batch=args.batch, engine=args.engine)
         return v, i
 
     def timed(fn, steps, warmup, sample_clocks=False, time_gemm=False):
@@ -251,22 +258,47 @@ def run_ours(args):
     e2e = m * world * args.steps / (ms_e2e * 1e-3)
     assert res_e2e[1] == res[1], "e2e and resident paths disagree on the argmax"
 
-    # roofline of the dominant kernel (variance GEMM): algorithmic n^2 flop per candidate
+    # roofline of the dominant kernel (the variance contraction V = L^-1 k*, n^2 flop per candidate)
     dmma_tf, dfma_tf = device.fp64_peak(30.0)
     batch = a.batch
     g_ms, g_n = gemm
-    per_launch_flop = float(n) * n * batch  # full batches dominate; the last partial batch is counted full
-    achieved = per_launch_flop / (g_ms / max(g_n, 1) * 1e-3) / 1e12
-    roofline = {"bound": "tensor", "achieved": achieved, "peak": dmma_tf, "unit": "TFLOP/s",
-                "frac": achieved / dmma_tf if dmma_tf else None, "traffic": None,
-                "kernel": "gemm_f64_kernel<false,true> (V = Linv * Kstar^T, DMMA.8x8x4, column sum-of-squares epilogue)",
-                "algorithmic_flop_per_launch": per_launch_flop, "launches_timed": g_n,
-                "avg_launch_ms": g_ms / max(g_n, 1),
-                "gemm_share_of_step": g_ms / ms_serial,
-                "timed_in": "a separate single-stream pass of the same step (%.1f ms/step); the headline pass overlaps "
-                            "consecutive batches on two internal streams" % (ms_serial / max(1, min(2, args.steps))),
-                "peak_source": "tb200_fp64_peak DMMA microbenchmark on this device (MEASURED_PEAKS.json has no FP64 "
-                               "figure); DFMA vector peak %.2f TFLOP/s" % dfma_tf}
+    avg_ms = g_ms / max(g_n, 1)
+    fp64_flop = float(n) * n * batch  # full batches dominate; the last partial batch is counted full
+    fp64_equiv = fp64_flop / (avg_ms * 1e-3) / 1e12
+    timed_in = ("a separate single-stream pass of the same step (%.1f ms/step); the headline pass overlaps consecutive "
+                "batches on two internal streams" % (ms_serial / max(1, min(2, args.steps))))
+    if engine == "dmma":
+        roofline = {"bound": "tensor", "achieved": fp64_equiv, "peak": dmma_tf, "unit": "TFLOP/s",
+                    "frac": fp64_equiv / dmma_tf if dmma_tf else None, "traffic": TRAFFIC.get("dmma"),
+                    "kernel": "gemm_f64_kernel<false,true> (V = Linv * Kstar^T, DMMA.8x8x4, column sum-of-squares epilogue)",
+                    "algorithmic_flop_per_launch": fp64_flop, "launches_timed": g_n, "avg_launch_ms": avg_ms,
+                    "gemm_share_of_step": g_ms / ms_serial, "timed_in": timed_in,
+                    "peak_source": "tb200_fp64_peak DMMA microbenchmark on this device (MEASURED_PEAKS.json has no "
+                                   "FP64 figure); DFMA vector peak %.2f TFLOP/s" % dfma_tf}
+    else:
+        pairs = 28 if engine == "i8" else 34
+        NP = (n + 127) // 128 * 128
+        int8_ops = 2.0 * pairs * 0.5 * NP * (NP + 64) * batch  # 2 ops per INT8 MAC, lower-triangular k-range
+        achieved = int8_ops / (avg_ms * 1e-3) / 1e12
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        bf16 = float(peaks.get("bf16_tflops", 0) or 0)
+        peak = 2.0 * bf16 if bf16 else 4500.0
+        roofline = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s (INT8 tensor ops)",
+                    "frac": achieved / peak, "traffic": TRAFFIC.get(engine),
+                    "kernel": "i8::colsumsq_i8_kernel<%d> (tcgen05.mma kind::i8, %d byte-slice products of V = Linv * "
+                              "Kstar^T accumulated exactly in INT32 TMEM, FP64 sum-of-squares epilogue)"
+                              % (8 if engine == "i8" else 9, pairs),
+                    "algorithmic_flop_per_launch": int8_ops, "launches_timed": g_n, "avg_launch_ms": avg_ms,
+                    "gemm_share_of_step": g_ms / ms_serial, "timed_in": timed_in,
+                    "fp64_equivalent_tflops": fp64_equiv, "fp64_dmma_peak_tflops": dmma_tf,
+                    "peak_source": ("2 x the measured dense bf16 burst peak in MEASURED_PEAKS.json (%.1f TFLOP/s): INT8 "
+                                    "tcgen05 MMAs retire K=32 per instruction where bf16 retires K=16 (no INT8 figure "
+                                    "is measured by the driver)" % bf16) if bf16 else
+                                   "nominal 4.5 PFLOP/s dense INT8 (B200_PROFILING.md fallback; MEASURED_PEAKS.json absent)"}
 
     # GP fit ms: one batched LML+gradient evaluation over R restarts (split across ranks)
     R = args.restarts
@@ -308,7 +340,7 @@ def run_ours(args):
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": "GP predict + EI + argmax, n_train=%d, d=%d, ARD Matern-5/2 + white, fixed "
                                        "theta (BASELINE.json headline; configs[3] shape)" % (n, d),
-                           "candidates_per_gpu_per_step": m, "candidate_batch": batch,
+                           "candidates_per_gpu_per_step": m, "candidate_batch": batch, "variance_engine": engine,
                            "l2": "candidate set %.0f MB per GPU > 126 MB L2" % (m * d * 8 / 1e6),
                            "parallelism": "candidates sharded x%d, model replicated" % world},
                 "e2e": {"value": e2e, "unit": "candidates/s", "h2d_bytes_per_step": m * d * 8 * world,
@@ -332,6 +364,7 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="candidate batch per kernel pass (0 = library default)")
     ap.add_argument("--restarts", type=int, default=64)
     ap.add_argument("--cpu-sample", type=int, default=1 << 14)
+    ap.add_argument("--engine", default=None, help="variance engine: auto (default) | dmma | i8 | i8x")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -99,6 +99,25 @@ int tb200_acquire(const double* Xc, int64_t m, int64_t index_base, const tb200_c
                   void* stream);
 int tb200_best_reset(double* best_val, int64_t* best_idx, void* stream);
 
+/* INT8-tensor-core engine for the predictive variance (tcgen05.mma kind::i8 + TMEM, csrc/ozaki_i8.cuh).
+ * Same contract and results as tb200_acquire (same sklearn lines); the O(n^2)-per-candidate contraction
+ * V = L^-1 k* is assembled exactly from 7 byte slices per operand with INT32 accumulation.
+ *   tb200_i8_prepare: slice the inverse factor once per model.  linvS: tb200_i8_factor_bytes(n) bytes;
+ *     rowscale: 2*NP doubles (scale sf2*2^e_r per row, then the exponents e_r).
+ *   gmax = 8: 28 slice products (truncation ~2^-54 of row-max*sf2 per term, >= 40x inside the parity floor);
+ *   gmax = 9: 34 products, indistinguishable from an FP64 GEMM.  n <= TB200_I8_MAX_N (INT32 exactness). */
+#define TB200_I8_MAX_N 4096
+size_t tb200_i8_factor_bytes(int n);
+int tb200_i8_prepare(const double* Linv, int n, const tb200_kernel_spec* spec_host, const double* theta,
+                     uint8_t* linvS, double* rowscale, void* stream);
+size_t tb200_acquire_i8_workspace_bytes(int n, int d, int64_t batch);
+int tb200_acquire_i8(const double* Xc, int64_t m, int64_t index_base, const tb200_cand_spec* cand_host,
+                     const double* XsT, const uint8_t* linvS, const double* rowscale, int gmax,
+                     const double* alpha, int n, const tb200_kernel_spec* spec_host, const double* theta,
+                     const tb200_acq_spec* acq_host, double* mu_out, double* sigma_out, double* acq_out,
+                     double* best_val, int64_t* best_idx, int64_t batch, void* work, size_t work_bytes,
+                     void* stream);
+
 /* write candidates [index_base, index_base+m) of a generated set into out (m x d) */
 int tb200_generate_candidates(const tb200_cand_spec* cand_host, int d, int64_t index_base, int64_t m,
                               double* out, void* stream);

@@ -1,0 +1,91 @@
+"""INT8 tensor-core variance engine (csrc/ozaki_i8.cuh) against the DMMA engine, the oracle and the golden
+vectors: same tolerances as the FP64 path (mean/variance/acquisition 1e-8 relative with the documented
+absolute variance floor; argmax exact)."""
+import numpy as np
+import pytest
+
+from oracle import gp_oracle as O
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+EPS = np.finfo(float).eps
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _need_gpu():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+
+
+def _model(g, engine):
+    import turbo_b200 as tb
+    d = g["X"].shape[1]
+    spec = tb.KernelSpec(g["kind"], d, g["ard"], g["has_const"], g["has_white"])
+    sur = tb.GpuGPSurrogate(model_params=dict(kernel=(spec, g["theta"]), normalize_y=bool(g["normalize_y"])),
+                            training_iterations=0, variance_engine=engine)
+    return sur.construct_model(0, g["X"], g["y"])[0]
+
+
+@pytest.mark.parametrize("engine", ["i8", "i8x"])
+def test_i8_predict_and_acquisition_match_reference(golden, engine):
+    import turbo_b200 as tb
+    g = golden
+    model = _model(g, engine)
+    mu, sd = model.predict(g["Xc"], return_std_dev=True)
+    prior = np.exp(g["theta"][0]) if g["has_const"] else 1.0
+    floor = 256 * EPS * g["X"].shape[0] * prior * model.y_std ** 2
+    np.testing.assert_allclose(mu, g["mu"], rtol=1e-8, atol=1e-8 * np.abs(g["mu"]).max())
+    np.testing.assert_allclose(sd ** 2, g["sigma"] ** 2, rtol=1e-8, atol=floor)
+    acq, _ = tb.GpuEI(g["xi"]).construct_function(0, model, g["extremum"], g["incumbent"])
+    vals = acq(g["Xc"])
+    ref = g["ei"]
+    tol = 1e-8 * np.abs(ref).max() + np.sqrt(floor)  # EI moves by at most |d sigma| = sqrt(var floor) near sigma = 0
+    np.testing.assert_allclose(vals, ref, rtol=1e-8, atol=tol)
+    val, idx, x = acq.argmax_over(candidates=g["Xc"])
+    order = np.argsort(-ref, kind="stable")
+    gap = ref[order[0]] - ref[order[1]]
+    if gap > 1e-9 * abs(ref[order[0]]):
+        assert idx == g["ei_argmax"]
+        np.testing.assert_array_equal(x[0], g["Xc"][idx])
+
+
+@pytest.mark.parametrize("n,d,kind,noise", [(1000, 6, 3, 1e-6), (2048, 3, 0, 1e-8), (4096, 10, 3, 1e-4)])
+def test_i8_matches_dmma_at_size(n, d, kind, noise):
+    """full-size, including an ill-conditioned factor (large rows of L^-1): the three engines agree on the
+    variance to the parity floor, and on the selected candidate"""
+    import turbo_b200 as tb
+    rng = np.random.default_rng(n)
+    X = rng.random((n, d))
+    y = np.sin(2 * np.pi * X).sum(axis=1) + 0.01 * rng.standard_normal(n)
+    spec = tb.KernelSpec(kind, d, True)
+    theta = np.log(np.r_[1.0, np.full(d, 0.5), noise])
+    m = 5000
+    Xc = rng.random((m, d))
+    Xc[:16] = X[:16]  # duplicates of training points: var cancels to ~noise
+    out = {}
+    for engine in ("dmma", "i8", "i8x"):
+        sur = tb.GpuGPSurrogate(model_params=dict(kernel=(spec, theta), normalize_y=True), training_iterations=0,
+                                variance_engine=engine)
+        model = sur.construct_model(0, X, y)[0]
+        mu, sd = model.predict(Xc, return_std_dev=True)
+        acq, _ = tb.GpuEI(0.01).construct_function(0, model, 'min', float(y.min()))
+        val, idx, _ = acq.argmax_over(candidates=Xc)
+        out[engine] = (mu, sd ** 2, idx, model.y_std)
+    floor = 256 * EPS * n * out["dmma"][3] ** 2
+    for engine in ("i8", "i8x"):
+        np.testing.assert_allclose(out[engine][0], out["dmma"][0], rtol=1e-10, atol=1e-12)
+        np.testing.assert_allclose(out[engine][1], out["dmma"][1], rtol=1e-8, atol=floor)
+        assert out[engine][2] == out["dmma"][2]
+    # i8x (34 slice products) is as accurate as the FP64 GEMM: compare both to the oracle's TRSM form
+    og = O.FittedGP(O.KernelSpec(kind, d, True), theta, X, y)
+    _, sd_o = og.predict(Xc[:512])
+    e_dmma = np.abs(out["dmma"][1][:512] - sd_o ** 2).max()
+    e_i8x = np.abs(out["i8x"][1][:512] - sd_o ** 2).max()
+    assert e_i8x <= 4 * e_dmma + 64 * EPS * out["dmma"][3] ** 2
+
+
+def test_i8_rejects_large_n():
+    from turbo_b200 import device
+    with pytest.raises(ValueError):
+        device.resolve_engine("i8", 8192)
+    assert device.resolve_engine("auto", 8192) == "dmma" and device.resolve_engine("auto", 4096) == "i8"

@@ -12,6 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("TB200_LIB") or os.path.join(_HERE, "libturbo_b200.so")  # TB200_LIB: A/B builds
 MAX_D = 64
+I8_MAX_N = 4096  # TB200_I8_MAX_N
 
 KIND_RBF, KIND_MATERN12, KIND_MATERN32, KIND_MATERN52 = 0, 1, 2, 3
 ACQ_EI, ACQ_PI, ACQ_UCB = 0, 1, 2
@@ -49,6 +50,12 @@ _SIGNATURES = {
                                 C.POINTER(KernelSpecC), _P, C.POINTER(AcqSpecC), _P, _P, _P, _P, _P, C.c_int64,
                                 _P, C.c_size_t, _P]),
     "tb200_best_reset": (C.c_int, [_P, _P, _P]),
+    "tb200_i8_factor_bytes": (C.c_size_t, [C.c_int]),
+    "tb200_i8_prepare": (C.c_int, [_P, C.c_int, C.POINTER(KernelSpecC), _P, _P, _P, _P]),
+    "tb200_acquire_i8_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int64]),
+    "tb200_acquire_i8": (C.c_int, [_P, C.c_int64, C.c_int64, C.POINTER(CandSpecC), _P, _P, _P, C.c_int, _P, C.c_int,
+                                   C.POINTER(KernelSpecC), _P, C.POINTER(AcqSpecC), _P, _P, _P, _P, _P, C.c_int64,
+                                   _P, C.c_size_t, _P]),
     "tb200_generate_candidates": (C.c_int, [C.POINTER(CandSpecC), C.c_int, C.c_int64, C.c_int64, _P, _P]),
     "tb200_fp64_peak": (C.c_int, [C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "tb200_timing_enable": (C.c_int, [C.c_int]),

@@ -35,12 +35,12 @@ class _DeviceFunction:
         X = np.ascontiguousarray(np.atleast_2d(X), dtype=np.float64)
         m = X.shape[0]
         out = torch.empty(m, dtype=torch.float64, device=device.device())
-        a = device.Acquirer(self.model.factor, self._spec_c())
+        a = device.Acquirer(self.model.factor, self._spec_c(), engine=getattr(self.model, 'variance_engine', None))
         a.run(device.to_device(X), m, 0, None, acq=out)
         return out.cpu().numpy()
 
     def argmax_over(self, candidates=None, generator=None, m=None, lo=None, hi=None, seed=0, group=None,
-                    chunk=1 << 18, batch=0):
+                    chunk=1 << 18, batch=0, engine=None):
         """argmax of the acquisition function over a candidate set.
 
         candidates: (m,d) host array (every rank passes the same full set when ``group`` is given), or
@@ -52,7 +52,8 @@ class _DeviceFunction:
         import torch
         from . import dist
         rank, world = dist.rank_world(group)
-        a = device.Acquirer(self.model.factor, self._spec_c(), batch)
+        a = device.Acquirer(self.model.factor, self._spec_c(), batch,
+                            engine=engine or getattr(self.model, 'variance_engine', None))
         d = self.model.spec.d
         if candidates is not None:
             if isinstance(candidates, torch.Tensor):  # a (pinned) host tensor is used in place

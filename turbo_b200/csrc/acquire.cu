@@ -18,6 +18,7 @@
 #include <vector>
 
 #include "gemm_f64.cuh"
+#include "ozaki_i8.cuh"
 
 namespace tb200 {
 
@@ -173,6 +174,165 @@ __global__ void __launch_bounds__(256) kstar_mean_kernel(const double* __restric
 }
 
 // ---------------------------------------------------------------------------------------------
+// INT8 engine (ozaki_i8.cuh): byte slicing of the two operands
+// ---------------------------------------------------------------------------------------------
+// digits of b in [0,1]:  b ~= sum_{s=1..7} u_s 2^(-8s), u_s in [0,255]; exact arithmetic (scaling by 256,
+// floor and the subtraction are error-free in FP64); the last digit is rounded
+__device__ __forceinline__ void slice_unsigned(double t, uint8_t (&u)[i8::S]) {
+#pragma unroll
+    for (int s = 0; s < i8::S; ++s) {
+        t *= 256.0;
+        int q = (s == i8::S - 1) ? __double2int_rd(t + 0.5) : __double2int_rd(t);
+        q = min(q, 255);
+        u[s] = (uint8_t)q;
+        t -= (double)q;
+    }
+}
+// digits of a in (-1,1):  a = b_1 2^-7 + sum_{s=2..7} b_s 2^(1-8s), b_1 = floor(128 a) in [-128,127]
+__device__ __forceinline__ void slice_signed(double a, uint8_t (&u)[i8::S]) {
+    double t = a * 128.0;
+    const int q1 = __double2int_rd(t);
+    u[0] = (uint8_t)(int8_t)q1;
+    t -= (double)q1;
+#pragma unroll
+    for (int s = 1; s < i8::S; ++s) {
+        t *= 256.0;
+        int q = (s == i8::S - 1) ? __double2int_rd(t + 0.5) : __double2int_rd(t);
+        q = min(q, 255);
+        u[s] = (uint8_t)q;
+        t -= (double)q;
+    }
+}
+
+// K* rows of CPB candidates as byte slices in the tiled layout ozaki_i8 reads, plus the predictive mean.
+// One CTA = 8 candidates (one core-matrix row group) x jchunk training points; 16 consecutive j of the 8
+// candidates form one contiguous 128-byte core matrix per slice, staged in shared memory and written
+// with 16-byte stores.
+__global__ void __launch_bounds__(256) kstar_mean_i8_kernel(const double* __restrict__ Xc, int64_t m_valid,
+                                                            const double* __restrict__ XsT, int n, int NP,
+                                                            tb200_kernel_spec spec, const double* __restrict__ theta,
+                                                            const double* __restrict__ alpha,
+                                                            uint8_t* __restrict__ KsS, long slice_stride,
+                                                            double* __restrict__ mean, int jchunk, long mean_stride) {
+    extern __shared__ double sh[];  // xc[CPB][d], red[8][CPB], then bytes[S][16 chunks][CPB][16]
+    const int d = spec.d;
+    double* xc = sh;
+    double* red = sh + CPB * d;
+    uint8_t* stage = reinterpret_cast<uint8_t*>(red + 8 * CPB);
+    const int64_t c0 = (int64_t)blockIdx.x * CPB;
+    for (int e = threadIdx.x; e < CPB * d; e += blockDim.x) {
+        const int c = e / d, k = e - c * d;
+        const int64_t ci = c0 + c;
+        xc[e] = (ci < m_valid) ? Xc[ci * d + k] / length_scale(spec, theta, k) : 0.0;
+    }
+    __syncthreads();
+    const Hyper h = unpack_hyper(spec, theta);
+    const int kblks = NP / i8::KB;
+    const int ct = (int)(c0 / i8::TM), rg = (int)((c0 % i8::TM) >> 3);
+    double msum[CPB];
+#pragma unroll
+    for (int c = 0; c < CPB; ++c) msum[c] = 0.0;
+    const int jlo = blockIdx.y * jchunk, jhi = min(NP, jlo + jchunk);
+    for (int jb = jlo; jb < jhi; jb += 256) {
+        const int j = jb + threadIdx.x;
+        if (j < jhi) {
+            double r2[CPB];
+#pragma unroll
+            for (int c = 0; c < CPB; ++c) r2[c] = 0.0;
+            for (int k = 0; k < d; ++k) {
+                const double xt = XsT[(long)k * NP + j];
+#pragma unroll
+                for (int c = 0; c < CPB; ++c) {
+                    const double df = xc[c * d + k] - xt;
+                    r2[c] += df * df;
+                }
+            }
+            const double a = alpha[j];
+            const bool live = j < n;
+#pragma unroll
+            for (int c = 0; c < CPB; ++c) {
+                const double g = live ? shape_fn(spec.kind, r2[c]) : 0.0;
+                msum[c] += (h.sf2 * g) * a;
+                uint8_t u[i8::S];
+                slice_unsigned(g, u);
+#pragma unroll
+                for (int s = 0; s < i8::S; ++s)
+                    stage[((s * 16 + (threadIdx.x >> 4)) * CPB + c) * 16 + (threadIdx.x & 15)] = u[s];
+            }
+        }
+        __syncthreads();
+        // 7 slices x (up to 16) core matrices of 128 B -> global, 16 B per thread
+        const int nchunks = min(16, (jhi - jb) >> 4);
+        for (int e = threadIdx.x; e < i8::S * nchunks * CPB; e += 256) {
+            const int row = e % CPB, jc = (e / CPB) % nchunks, sl = e / (CPB * nchunks);
+            const int jj = jb + jc * 16;
+            const size_t off = (size_t)sl * slice_stride + ((size_t)ct * kblks + jj / i8::KB) * i8::A_TILE +
+                               (size_t)rg * i8::SBO + ((jj % i8::KB) >> 4) * i8::LBO + row * 16;
+            *reinterpret_cast<uint4*>(KsS + off) =
+                *reinterpret_cast<const uint4*>(stage + ((sl * 16 + jc) * CPB + row) * 16);
+        }
+        __syncthreads();
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int c = 0; c < CPB; ++c) {
+        const double v = warp_sum(msum[c]);
+        if (lane == 0) red[warp * CPB + c] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < CPB) {
+        double t = 0.0;
+        for (int w = 0; w < 8; ++w) t += red[w * CPB + threadIdx.x];
+        mean[blockIdx.y * mean_stride + c0 + threadIdx.x] = t;
+    }
+}
+
+// rowscale[r] = sf2 * 2^(e_r) with 2^(e_r) > max_k |Linv[r,k]|  (one warp per row)
+__global__ void __launch_bounds__(256) linv_rowscale_kernel(const double* __restrict__ Linv, int NP,
+                                                            tb200_kernel_spec spec, const double* __restrict__ theta,
+                                                            double* __restrict__ rowscale) {
+    const int r = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (r >= NP) return;
+    double mx = 0.0;
+    for (int k = lane; k <= r; k += 32) mx = fmax(mx, fabs(Linv[(long)r * NP + k]));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 0) {
+        int e = 0;
+        frexp(mx, &e);  // mx = f * 2^e, f in [0.5, 1)  ->  |Linv / 2^e| < 1
+        rowscale[NP + r] = (double)e;  // second half of the buffer keeps the exponent for the slicing kernel
+        rowscale[r] = unpack_hyper(spec, theta).sf2 * ldexp(1.0, e);
+    }
+}
+
+// Linv (lower) -> byte slices in the tiled layout: thread = (row, 16-byte K chunk) of the lower tiles
+__global__ void __launch_bounds__(256) linv_slice_kernel(const double* __restrict__ Linv, int NP,
+                                                         const double* __restrict__ rowscale, uint8_t* __restrict__ out,
+                                                         long slice_stride) {
+    const int chunks_per_row = NP / 16;
+    const long e = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= (long)NP * chunks_per_row) return;
+    const int r = (int)(e / chunks_per_row), kc = (int)(e % chunks_per_row);
+    const int rt = r / i8::TN, kb = (kc * 16) / i8::KB;
+    if (kb > rt) return;  // tiles above the diagonal are never read
+    const double sc = ldexp(1.0, -(int)rowscale[NP + r]);
+    __align__(16) uint8_t bytes[i8::S][16];
+#pragma unroll
+    for (int q = 0; q < 16; ++q) {
+        uint8_t u[i8::S];
+        slice_signed(Linv[(long)r * NP + kc * 16 + q] * sc, u);
+#pragma unroll
+        for (int s = 0; s < i8::S; ++s) bytes[s][q] = u[s];
+    }
+    const int kblks = NP / i8::KB;
+    const size_t off = ((size_t)rt * kblks + kb) * i8::B_TILE + (size_t)((r % i8::TN) >> 3) * i8::SBO +
+                       (((kc * 16) % i8::KB) >> 4) * i8::LBO + (r & 7) * 16;
+#pragma unroll
+    for (int s = 0; s < i8::S; ++s)
+        *reinterpret_cast<uint4*>(out + (size_t)s * slice_stride + off) = *reinterpret_cast<const uint4*>(bytes[s]);
+}
+
+// ---------------------------------------------------------------------------------------------
 // variance, acquisition value and running argmax for one batch (single CTA)
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ double norm_cdf(double z) { return 0.5 * erfc(-z * 0.7071067811865476); }
@@ -311,7 +471,7 @@ static size_t a256(size_t b) { return (b + 255) / 256 * 256; }
 constexpr int ACQ_SLOTS = 2;
 constexpr int KSPLIT_MAX = 8;  // K* kernel: training points split over up to 8 CTAs per candidate group
 
-static size_t acquire_layout(int n, int d, int64_t batch, AcqBuffers* ab, char* base) {
+static size_t acquire_layout(int n, int d, int64_t batch, AcqBuffers* ab, char* base, bool use_i8 = false) {
     const size_t NP = pad_n(n), NB = NP / TILE;
     size_t off = 0;
     auto take = [&](size_t bytes) {
@@ -321,9 +481,10 @@ static size_t acquire_layout(int n, int d, int64_t batch, AcqBuffers* ab, char* 
     };
     for (int s = 0; s < ACQ_SLOTS; ++s) {
         double* cand = take(sizeof(double) * batch * d);
-        double* Ks = take(sizeof(double) * batch * NP);
+        // DMMA engine: K* in FP64 (batch x NP); INT8 engine: 7 byte slices of it (tiled), partials per 64 rows
+        double* Ks = take(use_i8 ? (size_t)i8::S * batch * NP : sizeof(double) * batch * NP);
         double* mean = take(sizeof(double) * KSPLIT_MAX * batch);
-        double* partial = take(sizeof(double) * NB * batch);
+        double* partial = take(sizeof(double) * (use_i8 ? NP / i8::TN : NB) * batch);
         double* bv = take(sizeof(double));
         int64_t* bi = reinterpret_cast<int64_t*>(take(sizeof(int64_t)));
         if (ab) { ab[s].cand = cand; ab[s].Ks = Ks; ab[s].mean = mean; ab[s].partial = partial;
@@ -414,14 +575,25 @@ int tb200_generate_candidates(const tb200_cand_spec* cand, int d, int64_t index_
     return 0;
 }
 
-int tb200_acquire(const double* Xc, int64_t m, int64_t index_base, const tb200_cand_spec* cand, const double* XsT,
-                  const double* Linv, const double* alpha, int n, const tb200_kernel_spec* spec, const double* theta,
-                  const tb200_acq_spec* acq, double* mu_out, double* sigma_out, double* acq_out, double* best_val,
-                  int64_t* best_idx, int64_t batch, void* work, size_t work_bytes, void* stream) {
-    TB_CHECK(spec && acq && XsT && Linv && alpha && theta && best_val && best_idx && work, "NULL pointer argument");
+struct I8Factor {
+    const uint8_t* linvS;    // NULL: DMMA engine
+    const double* rowscale;
+    int gmax;
+};
+
+static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const tb200_cand_spec* cand, const double* XsT,
+                        const double* Linv, const I8Factor& f8, const double* alpha, int n,
+                        const tb200_kernel_spec* spec, const double* theta, const tb200_acq_spec* acq, double* mu_out,
+                        double* sigma_out, double* acq_out, double* best_val, int64_t* best_idx, int64_t batch,
+                        void* work, size_t work_bytes, void* stream) {
+    const bool use_i8 = f8.linvS != nullptr;
+    TB_CHECK(spec && acq && XsT && alpha && theta && best_val && best_idx && work, "NULL pointer argument");
+    TB_CHECK(use_i8 ? f8.rowscale != nullptr : Linv != nullptr, "NULL factor pointer");
     TB_CHECK(spec->kind >= TB200_RBF && spec->kind <= TB200_MATERN52, "unknown kernel kind");
     TB_CHECK(spec->d >= 1 && spec->d <= TB200_MAX_D, "d out of range (1..64)");
     TB_CHECK(acq->acq >= TB200_EI && acq->acq <= TB200_UCB, "unknown acquisition function");
+    TB_CHECK(!use_i8 || (f8.gmax == 8 || f8.gmax == 9), "i8 engine: gmax must be 8 or 9");
+    TB_CHECK(!use_i8 || pad_n(n) <= TB200_I8_MAX_N, "i8 engine: n > 4096 would overflow the INT32 accumulators");
     const int mode = cand ? cand->mode : TB200_CAND_GIVEN;
     if (m <= 0) return 0;
     TB_CHECK(mode != TB200_CAND_GIVEN || Xc, "Xc is NULL and no generator given");
@@ -432,8 +604,10 @@ int tb200_acquire(const double* Xc, int64_t m, int64_t index_base, const tb200_c
     cudaStream_t st = (cudaStream_t)stream;
     const int NP = pad_n(n), NB = NP / TILE, d = spec->d;
     AcqBuffers ab[ACQ_SLOTS];
-    const size_t need = acquire_layout(n, d, batch, ab, (char*)work);
+    const size_t need = acquire_layout(n, d, batch, ab, (char*)work, use_i8);
     TB_CHECK(work_bytes >= need, "workspace too small (see tb200_acquire_workspace_bytes)");
+    const int ntiles = use_i8 ? NP / i8::TN : NB;  // row tiles of the variance partials
+    const long slice_stride = (long)batch * NP;   // bytes between K* byte slices (i8 engine)
 
     if (g_acq_streams < 0) {
         const char* e = getenv("TB200_ACQ_STREAMS");
@@ -475,17 +649,37 @@ int tb200_acquire(const double* Xc, int64_t m, int64_t index_base, const tb200_c
                       index_base + off, mb, w.cand);
             xc = w.cand;
         }
-        TB_LAUNCH(kstar_mean_kernel, dim3((unsigned)(mbp / CPB), ksplit), dim3(256), ksm, cs, xc, mb, XsT, n, NP, *spec,
-                  theta, alpha, w.Ks, w.mean, jchunk, (long)batch);
-        GemmParams gp = gemm_params(Linv, NP, w.Ks, NP, w.partial, batch, NB, (int)(mbp / 128), NP, 1.0, 0.0);
-        gp.order = ORDER_RECT_HEAVY_LAST_ROW_FIRST;
-        gp.khi_mode = KHI_BY_TI;
-        gp.a_tri_diag = getenv("TB200_NO_TRI") ? 0 : 1;  // Linv is lower triangular
-        gp.epi = EPI_COLSUMSQ;
-        if (g_time_gemm) TB_CUDA(cudaEventRecord(next_event(), cs));
-        if (launch_gemm<false, true>(gp, 1, 1, cs)) return -1;
-        if (g_time_gemm) TB_CUDA(cudaEventRecord(next_event(), cs));
-        TB_LAUNCH(acquire_epilogue_kernel, dim3(1), dim3(1024), 0, cs, w.mean, ksplit, w.partial, NB, (long)batch, mbp, mb,
+        if (use_i8) {
+            const size_t ksm8 = ksm + (size_t)i8::S * 16 * CPB * 16;
+            TB_LAUNCH(kstar_mean_i8_kernel, dim3((unsigned)(mbp / CPB), ksplit), dim3(256), ksm8, cs, xc, mb, XsT, n, NP,
+                      *spec, theta, alpha, reinterpret_cast<uint8_t*>(w.Ks), slice_stride, w.mean, jchunk, (long)batch);
+            i8::Params ip;
+            ip.candS = reinterpret_cast<const uint8_t*>(w.Ks);
+            ip.linvS = f8.linvS;
+            ip.rowscale = f8.rowscale;
+            ip.partial = w.partial;
+            ip.ldp = batch;
+            ip.candSliceStride = slice_stride;
+            ip.linvSliceStride = (long)NP * NP;
+            ip.kblks = NP / i8::KB;
+            ip.rowTiles = NP / i8::TN;
+            ip.candTiles = (int)(mbp / i8::TM);
+            if (g_time_gemm) TB_CUDA(cudaEventRecord(next_event(), cs));
+            if (f8.gmax == 8 ? i8::launch_colsumsq_i8<8>(ip, cs) : i8::launch_colsumsq_i8<9>(ip, cs)) return -1;
+            if (g_time_gemm) TB_CUDA(cudaEventRecord(next_event(), cs));
+        } else {
+            TB_LAUNCH(kstar_mean_kernel, dim3((unsigned)(mbp / CPB), ksplit), dim3(256), ksm, cs, xc, mb, XsT, n, NP,
+                      *spec, theta, alpha, w.Ks, w.mean, jchunk, (long)batch);
+            GemmParams gp = gemm_params(Linv, NP, w.Ks, NP, w.partial, batch, NB, (int)(mbp / 128), NP, 1.0, 0.0);
+            gp.order = ORDER_RECT_HEAVY_LAST_ROW_FIRST;
+            gp.khi_mode = KHI_BY_TI;
+            gp.a_tri_diag = 1;  // Linv is lower triangular
+            gp.epi = EPI_COLSUMSQ;
+            if (g_time_gemm) TB_CUDA(cudaEventRecord(next_event(), cs));
+            if (launch_gemm<false, true>(gp, 1, 1, cs)) return -1;
+            if (g_time_gemm) TB_CUDA(cudaEventRecord(next_event(), cs));
+        }
+        TB_LAUNCH(acquire_epilogue_kernel, dim3(1), dim3(1024), 0, cs, w.mean, ksplit, w.partial, ntiles, (long)batch, mbp, mb,
                   off, index_base, *spec, theta, *acq, mu_out, sigma_out, acq_out, w.best_val, w.best_idx);
     }
     if (slots > 1) {
@@ -497,6 +691,46 @@ int tb200_acquire(const double* Xc, int64_t m, int64_t index_base, const tb200_c
     TB_LAUNCH(best_merge_kernel, dim3(1), dim3(1), 0, st, ab[0].best_val, ab[0].best_idx,
               slots > 1 ? ab[1].best_val : (const double*)nullptr, slots > 1 ? ab[1].best_idx : (const int64_t*)nullptr,
               best_val, best_idx);
+    return 0;
+}
+
+int tb200_acquire(const double* Xc, int64_t m, int64_t index_base, const tb200_cand_spec* cand, const double* XsT,
+                  const double* Linv, const double* alpha, int n, const tb200_kernel_spec* spec, const double* theta,
+                  const tb200_acq_spec* acq, double* mu_out, double* sigma_out, double* acq_out, double* best_val,
+                  int64_t* best_idx, int64_t batch, void* work, size_t work_bytes, void* stream) {
+    const I8Factor none{nullptr, nullptr, 0};
+    return acquire_impl(Xc, m, index_base, cand, XsT, Linv, none, alpha, n, spec, theta, acq, mu_out, sigma_out, acq_out,
+                        best_val, best_idx, batch, work, work_bytes, stream);
+}
+
+int tb200_acquire_i8(const double* Xc, int64_t m, int64_t index_base, const tb200_cand_spec* cand, const double* XsT,
+                     const uint8_t* linvS, const double* rowscale, int gmax, const double* alpha, int n,
+                     const tb200_kernel_spec* spec, const double* theta, const tb200_acq_spec* acq, double* mu_out,
+                     double* sigma_out, double* acq_out, double* best_val, int64_t* best_idx, int64_t batch, void* work,
+                     size_t work_bytes, void* stream) {
+    TB_CHECK(linvS && rowscale, "NULL pointer argument");
+    const I8Factor f8{linvS, rowscale, gmax};
+    return acquire_impl(Xc, m, index_base, cand, XsT, nullptr, f8, alpha, n, spec, theta, acq, mu_out, sigma_out,
+                        acq_out, best_val, best_idx, batch, work, work_bytes, stream);
+}
+
+size_t tb200_acquire_i8_workspace_bytes(int n, int d, int64_t batch) {
+    if (batch <= 0) batch = tb200_default_batch(n);
+    return acquire_layout(n, d, batch, nullptr, nullptr, true);
+}
+
+size_t tb200_i8_factor_bytes(int n) { return (size_t)i8::S * pad_n(n) * pad_n(n); }
+
+int tb200_i8_prepare(const double* Linv, int n, const tb200_kernel_spec* spec, const double* theta, uint8_t* linvS,
+                     double* rowscale, void* stream) {
+    TB_CHECK(Linv && spec && theta && linvS && rowscale, "NULL pointer argument");
+    const int NP = pad_n(n);
+    TB_CHECK(NP <= TB200_I8_MAX_N, "i8 engine: n > 4096 would overflow the INT32 accumulators");
+    cudaStream_t st = (cudaStream_t)stream;
+    TB_LAUNCH(linv_rowscale_kernel, dim3(NP / 8), dim3(256), 0, st, Linv, NP, *spec, theta, rowscale);
+    const long total = (long)NP * (NP / 16);
+    TB_LAUNCH(linv_slice_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, st, Linv, NP, rowscale, linvS,
+              (long)NP * NP);
     return 0;
 }
 

@@ -1,0 +1,252 @@
+// Predictive-variance contraction on the INT8 tensor cores (tcgen05.mma kind::i8, TMEM accumulators):
+// an error-free-transformation ("Ozaki scheme") evaluation of  V = Linv * Kstar^T  followed by the
+// column sums of squares, as an alternative engine to the DMMA GEMM of gemm_f64.cuh.
+//
+// Why: FP64 has no tcgen05 kind, and DMMA shares the 64 FMA/clk/SM FP64 pipe with DFMA (37 TFLOP/s
+// measured).  The 5th-gen tensor cores do 8192 INT8 MAC/clk/SM with exact INT32 accumulation, so a
+// product of two FP64 matrices can be assembled EXACTLY from byte slices:
+//
+//   Kstar[c,k] / sf2          = sum_{i=1..7} a_i[c,k] * 2^(-8i)              a_i in [0,255]   (u8)
+//   Linv[r,k]  / 2^(e_r)      = b_1[r,k] * 2^-7 + sum_{j=2..7} b_j 2^(1-8j)  b_1 in [-128,127] (s8),
+//                                                                            b_j in [0,255]   (u8)
+//   V[c,r] = sf2 * 2^(e_r) * sum_g 2^(1-8g) * G_g[c,r],   G_g = sum_{i+j=g} sum_k a_i[c,k] b_j[r,k]
+//
+// Every G_g is an integer matrix product accumulated exactly in INT32 TMEM (7 pairs * 4096 * 255^2
+// < 2^31, hence n <= 4096 per accumulation pass).  Pairs with i+j > GMAX are dropped: GMAX = 8 keeps 28
+// products and truncates at ~2^-54 of (row max * sf2) per term; GMAX = 9 keeps 34 and is
+// indistinguishable from an FP64 GEMM (tests/test_gpu_i8.py, profiles/r1_ozaki_accuracy.md).
+//
+// Kernel shape: one CTA per (64 Linv rows) x (128 candidates) tile.  A-operand (M = 128) = candidate
+// slices, B-operand (N = 64) = Linv-row slices, both K-major in the canonical no-swizzle core-matrix
+// layout, pre-tiled in global memory so that one k-block (64 bytes of K) of one slice is ONE contiguous
+// bulk-async copy (cp.async.bulk, the TMA engine, no tensor map needed).  Warp 0 = copy producer,
+// warp 1 = MMA issuer (one elected lane) + TMEM owner, warps 2-5 = epilogue: each thread owns one
+// candidate (TMEM lane) and reduces its 64 columns in registers, so no cross-thread reduction.
+#pragma once
+#include "common.cuh"
+
+namespace tb200 {
+namespace i8 {
+
+constexpr int S = 7;                 // byte slices per operand
+constexpr int KB = 64;               // bytes of K per pipeline stage
+constexpr int TM = 128;              // candidates per CTA tile (UMMA M)
+constexpr int TN = 64;               // Linv rows per CTA tile (UMMA N)
+constexpr int A_TILE = TM * KB;      // 8192 B
+constexpr int B_TILE = TN * KB;      // 4096 B
+constexpr int STAGE_BYTES = S * (A_TILE + B_TILE);  // 86016
+constexpr int STAGES = 2;
+constexpr int THREADS = 192;
+constexpr int TMEM_COLS = 512;
+constexpr int LBO = 128;             // bytes between the two 16-byte K chunks of one core-matrix row group
+constexpr int SBO = (KB / 16) * 128; // bytes between groups of 8 rows
+constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_BYTES + 1024;
+
+// byte offset of element (row r, k in [0,64)) inside a canonical K-major no-swizzle tile
+__host__ __device__ inline int tile_offset(int r, int k) {
+    return (r >> 3) * SBO + (k >> 4) * LBO + (r & 7) * 16 + (k & 15);
+}
+
+struct Params {
+    const uint8_t* candS;    // [S][candTiles][kblks][A_TILE]
+    const uint8_t* linvS;    // [S][rowTiles][kblks][B_TILE]
+    const double* rowscale;  // [rowTiles*64]  sf2 * 2^(e_r)
+    double* partial;         // [rowTiles][ldp]
+    long ldp;
+    long candSliceStride, linvSliceStride;  // bytes
+    int kblks;               // K / 64 (tiles per row of tiles)
+    int rowTiles, candTiles;
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+// bounded wait: a protocol bug traps instead of hanging the GPU
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t spins = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        if (++spins > (1u << 24)) __trap();
+    }
+}
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst_smem)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
+    // K-major, SWIZZLE_NONE: start>>4 [0,14), LBO>>4 [16,30), SBO>>4 [32,46), version=1 [46,48)
+    return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)(LBO >> 4) << 16) | ((uint64_t)(SBO >> 4) << 32) |
+           (1ull << 46);
+}
+__device__ __forceinline__ void umma_i8(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                        uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}"
+        :
+        : "r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(0), "r"(0), "r"(0), "r"(0)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "r"(taddr));
+}
+
+// instruction descriptor: D = S32 (c_format 2 @4), A u8 (0 @7), B u8/s8 (@10), K-major both,
+// N>>3 @17, M>>4 @24
+__host__ __device__ constexpr uint32_t idesc(int b_signed) {
+    return (2u << 4) | (0u << 7) | ((uint32_t)b_signed << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+}
+
+template <int GMAX>
+__global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p) {
+    constexpr int NG = GMAX - 1;  // groups g = 2..GMAX, one 64-column INT32 accumulator each
+    static_assert(NG * TN <= TMEM_COLS, "accumulators exceed TMEM");
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], done_bar;
+    __shared__ uint32_t tmem_base_s;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // heavy row tiles first (k-range grows with the row tile)
+    const int rt = p.rowTiles - 1 - (int)(blockIdx.x / p.candTiles);
+    const int ct = blockIdx.x % p.candTiles;
+    const int nkb = rt + 1;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(&done_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)),
+                     "r"(TMEM_COLS)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = tmem_base_s;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ===== producer: 14 bulk copies per k-block =====
+            const uint8_t* a_src = p.candS + ((size_t)ct * p.kblks) * A_TILE;
+            const uint8_t* b_src = p.linvS + ((size_t)rt * p.kblks) * B_TILE;
+            for (int kb = 0; kb < nkb; ++kb) {
+                const int s = kb % STAGES;
+                if (kb >= STAGES) mbar_wait(&empty_bar[s], ((kb / STAGES) - 1) & 1);
+                uint8_t* st = smem + (size_t)s * STAGE_BYTES;
+                mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+#pragma unroll
+                for (int sl = 0; sl < S; ++sl) {
+                    bulk_g2s(st + sl * A_TILE, a_src + (size_t)sl * p.candSliceStride + (size_t)kb * A_TILE, A_TILE,
+                             &full_bar[s]);
+                    bulk_g2s(st + S * A_TILE + sl * B_TILE, b_src + (size_t)sl * p.linvSliceStride + (size_t)kb * B_TILE,
+                             B_TILE, &full_bar[s]);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ===== MMA issuer =====
+            uint32_t started = 0;  // bit g set once group g has received its first (overwriting) MMA
+            for (int kb = 0; kb < nkb; ++kb) {
+                const int s = kb % STAGES;
+                mbar_wait(&full_bar[s], (kb / STAGES) & 1);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t a0 = smem_u32(smem + (size_t)s * STAGE_BYTES);
+                const uint32_t b0 = a0 + S * A_TILE;
+#pragma unroll
+                for (int ks = 0; ks < KB / 32; ++ks) {
+#pragma unroll
+                    for (int i = 1; i <= S; ++i) {
+#pragma unroll
+                        for (int j = 1; j <= S; ++j) {
+                            if (i + j > GMAX) continue;
+                            const int g = i + j - 2;
+                            const uint64_t ad = make_desc(a0 + (i - 1) * A_TILE + ks * 2 * LBO);
+                            const uint64_t bd = make_desc(b0 + (j - 1) * B_TILE + ks * 2 * LBO);
+                            umma_i8(tmem_base + g * TN, ad, bd, idesc(j == 1 ? 1 : 0), (started >> g) & 1u);
+                            started |= 1u << g;
+                        }
+                    }
+                }
+                umma_commit(&empty_bar[s]);  // frees the stage once these MMAs have read it
+            }
+            umma_commit(&done_bar);
+        }
+    } else {
+        // ===== epilogue: thread = candidate (TMEM lane), 64 columns = Linv rows of this tile =====
+        const int q = warp & 3;  // TMEM lane quarter this warp may access
+        mbar_wait(&done_bar, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
+        double acc = 0.0;
+#pragma unroll 1
+        for (int cc = 0; cc < TN / 8; ++cc) {
+            uint32_t r[NG][8];
+#pragma unroll
+            for (int g = 0; g < NG; ++g) tmem_ld8(lane_base + g * TN + cc * 8, r[g]);
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                // sum_g 2^(1-8(g+2)) G_g, smallest weight first
+                double v = 0.0;
+#pragma unroll
+                for (int g = NG - 1; g >= 0; --g) v = fma((double)(int)r[g][c], ldexp(1.0, 1 - 8 * (g + 2)), v);
+                v *= __ldg(p.rowscale + rt * TN + cc * 8 + c);
+                acc = fma(v, v, acc);
+            }
+        }
+        p.partial[(long)rt * p.ldp + (long)ct * TM + q * 32 + lane] = acc;
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+    }
+}
+
+template <int GMAX>
+inline int launch_colsumsq_i8(const Params& p, cudaStream_t stream) {
+    static bool configured = false;
+    if (!configured) {
+        TB_CUDA(cudaFuncSetAttribute(colsumsq_i8_kernel<GMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)SMEM_BYTES));
+        configured = true;
+    }
+    TB_LAUNCH((colsumsq_i8_kernel<GMAX>), dim3((unsigned)(p.rowTiles * p.candTiles)), dim3(THREADS), SMEM_BYTES, stream,
+              p);
+    return 0;
+}
+
+}  // namespace i8
+}  // namespace tb200

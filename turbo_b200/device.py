@@ -3,6 +3,7 @@
 Every function raises if CUDA or libturbo_b200.so is unavailable; there is no CPU path.
 """
 import ctypes as C
+import os
 
 import numpy as np
 import torch
@@ -87,18 +88,54 @@ class Factor:
         self.lml = float(lml.item())
         del work
 
+        self.linvS = self.rowscale = None
+
+    def prepare_i8(self):
+        """byte-slice the inverse factor for the INT8 tensor-core variance engine (once per model)"""
+        if self.linvS is None:
+            lib = _lib.load()
+            dev = device()
+            self.linvS = torch.empty(int(lib.tb200_i8_factor_bytes(self.n)), dtype=torch.uint8, device=dev)
+            self.rowscale = torch.empty(2 * self.NP, dtype=torch.float64, device=dev)
+            cs = self.spec.to_c()
+            _lib.check(lib.tb200_i8_prepare(_lib.ptr(self.Linv), self.n, C.byref(cs), _lib.ptr(self.theta),
+                                            _lib.ptr(self.linvS), _lib.ptr(self.rowscale), _lib.stream_ptr()))
+        return self
+
     def nbytes(self):
-        return sum(t.numel() * t.element_size() for t in (self.XsT, self.Linv, self.alpha, self.Ldiag))
+        ts = [self.XsT, self.Linv, self.alpha, self.Ldiag] + ([self.linvS, self.rowscale] if self.linvS is not None else [])
+        return sum(t.numel() * t.element_size() for t in ts)
+
+
+def resolve_engine(engine, NP):
+    """'auto' -> the INT8 tensor-core engine whenever its INT32 accumulation is exact (n <= 4096)"""
+    engine = (engine or os.environ.get("TB200_ENGINE") or "auto").lower()
+    if engine == "auto":
+        engine = "i8" if NP <= _lib.I8_MAX_N else "dmma"
+    if engine in ("i8", "i8x"):
+        if NP > _lib.I8_MAX_N:
+            raise ValueError("the i8 variance engine needs n <= %d (INT32 exactness); use engine='dmma'" % _lib.I8_MAX_N)
+        return engine
+    if engine != "dmma":
+        raise ValueError("unknown variance engine %r (auto | dmma | i8 | i8x)" % engine)
+    return engine
 
 
 class Acquirer:
-    """runs tb200_acquire over device candidates / a generated set, keeping the running best on device"""
+    """runs tb200_acquire / tb200_acquire_i8 over device candidates or a generated set, keeping the running
+    best on device.  engine: 'dmma' (FP64 tensor-core GEMM), 'i8' (INT8 tensor cores, 28 slice products),
+    'i8x' (34 slice products), 'auto' (i8 when n <= 4096)."""
 
-    def __init__(self, factor, acq_c, batch=0):
+    def __init__(self, factor, acq_c, batch=0, engine=None):
         lib = _lib.load()
         self.lib, self.f, self.acq_c = lib, factor, acq_c
+        self.engine = resolve_engine(engine, factor.NP)
         self.batch = int(batch) if batch else int(lib.tb200_default_batch(factor.n))
-        self.nbytes = lib.tb200_acquire_workspace_bytes(factor.n, factor.spec.d, self.batch)
+        if self.engine == "dmma":
+            self.nbytes = lib.tb200_acquire_workspace_bytes(factor.n, factor.spec.d, self.batch)
+        else:
+            factor.prepare_i8()
+            self.nbytes = lib.tb200_acquire_i8_workspace_bytes(factor.n, factor.spec.d, self.batch)
         self.work = _workspace(self.nbytes)
         dev = device()
         self.best_val = torch.empty(1, dtype=torch.float64, device=dev)
@@ -112,6 +149,14 @@ class Acquirer:
     def run(self, Xc_dev, m, index_base=0, cand_c=None, mu=None, sigma=None, acq=None):
         """candidates [index_base, index_base+m): Xc_dev (m,d) device tensor, or generated from cand_c"""
         f = self.f
+        if self.engine != "dmma":
+            _lib.check(self.lib.tb200_acquire_i8(
+                _lib.ptr(Xc_dev), int(m), int(index_base), C.byref(cand_c) if cand_c is not None else None,
+                _lib.ptr(f.XsT), _lib.ptr(f.linvS), _lib.ptr(f.rowscale), 8 if self.engine == "i8" else 9,
+                _lib.ptr(f.alpha), f.n, C.byref(self.spec_c), _lib.ptr(f.theta), C.byref(self.acq_c), _lib.ptr(mu),
+                _lib.ptr(sigma), _lib.ptr(acq), _lib.ptr(self.best_val), _lib.ptr(self.best_idx), self.batch,
+                _lib.ptr(self.work), self.nbytes, _lib.stream_ptr()))
+            return
         _lib.check(self.lib.tb200_acquire(
             _lib.ptr(Xc_dev), int(m), int(index_base), C.byref(cand_c) if cand_c is not None else None,
             _lib.ptr(f.XsT), _lib.ptr(f.Linv), _lib.ptr(f.alpha), f.n, C.byref(self.spec_c), _lib.ptr(f.theta),

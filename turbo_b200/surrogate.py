@@ -55,7 +55,7 @@ class GpuGPSurrogate(Surrogate):
     default_model_params = {'kernel': 'default', 'normalize_y': True}
 
     def __init__(self, model_params=None, training_iterations=None, param_continuity=True, max_iter=200,
-                 seed=None, group=None):
+                 seed=None, group=None, variance_engine=None):
         """model_params: as for SciKitGPSurrogate -- ``kernel`` (a scikit-learn kernel of the supported
         family, a KernelSpec, or (KernelSpec, theta0[, bounds])), ``normalize_y``, ``alpha`` (jitter),
         ``n_restarts_optimizer``, ``random_state``.  The default kernel is the reference's
@@ -71,6 +71,8 @@ class GpuGPSurrogate(Surrogate):
         self.param_continuity = param_continuity
         self.max_iter = max_iter
         self.group = group
+        # predictive-variance engine: 'auto' (default) | 'dmma' | 'i8' | 'i8x' (device.resolve_engine)
+        self.variance_engine = variance_engine
         rs = self.model_params.get('random_state', seed)
         self._rng = rs if isinstance(rs, np.random.RandomState) else np.random.RandomState(rs)
         self._last_model_params = None
@@ -119,7 +121,7 @@ class GpuGPSurrogate(Surrogate):
                                                   start_thetas)
                 fitting_info.update(fit_stats)
             model = GpuGPSurrogate.ModelInstance(spec, theta, X, y_n, y_mean, y_std, jitter,
-                                                 device_inputs=(X_dev, yn_dev))
+                                                 device_inputs=(X_dev, yn_dev), variance_engine=self.variance_engine)
         if len(ws) > 0:
             fitting_info['warnings'] = [w.message for w in ws]
         if iterations > 0:
@@ -168,7 +170,8 @@ class GpuGPSurrogate(Surrogate):
     class ModelInstance(SciKitModelInstance):
         """surrogates.py:328-365 contract; holds only NumPy state + lazily built device buffers."""
 
-        def __init__(self, spec, theta, X, y_n, y_mean, y_std, jitter, device_inputs=None):
+        def __init__(self, spec, theta, X, y_n, y_mean, y_std, jitter, device_inputs=None, variance_engine=None):
+            self.variance_engine = variance_engine
             self.spec, self.theta = spec, np.asarray(theta, dtype=np.float64).copy()
             self.X, self.y_n = X, y_n
             self.y_mean, self.y_std, self.jitter = float(y_mean), float(y_std), float(jitter)
@@ -221,7 +224,7 @@ class GpuGPSurrogate(Surrogate):
             mu = torch.empty(m, dtype=torch.float64, device=dev)
             sigma = torch.empty(m, dtype=torch.float64, device=dev)
             acq_c = device.acq_spec(_lib.ACQ_UCB, 1.0, 0.0, 0.0, self.y_mean, self.y_std)
-            a = device.Acquirer(self.factor, acq_c)
+            a = device.Acquirer(self.factor, acq_c, engine=getattr(self, 'variance_engine', None))
             a.run(device.to_device(X), m, 0, None, mu=mu, sigma=sigma)
             if return_std_dev:
                 return mu.cpu().numpy(), sigma.cpu().numpy()
