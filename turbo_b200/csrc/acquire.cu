@@ -188,19 +188,21 @@ __device__ __forceinline__ void slice_unsigned(double t, uint8_t (&u)[i8::S]) {
         t -= (double)q;
     }
 }
-// digits of a in (-1,1):  a = b_1 2^-7 + sum_{s=2..7} b_s 2^(1-8s), b_1 = floor(128 a) in [-128,127]
+// balanced digits of a, |a| <= 0.98:  a = sum_{s=1..7} b_s 2^(1-8s), b_s in [-128,127].  Every step is exact in
+// FP64 (power-of-two scaling, integer subtraction).  Invariant: the remainder stays in [-128/255, 127/255], so the
+// next digit 256*rem fits in s8; the last digit is rounded.
 __device__ __forceinline__ void slice_signed(double a, uint8_t (&u)[i8::S]) {
     double t = a * 128.0;
-    const int q1 = __double2int_rd(t);
-    u[0] = (uint8_t)(int8_t)q1;
-    t -= (double)q1;
 #pragma unroll
-    for (int s = 1; s < i8::S; ++s) {
-        t *= 256.0;
-        int q = (s == i8::S - 1) ? __double2int_rd(t + 0.5) : __double2int_rd(t);
-        q = min(q, 255);
-        u[s] = (uint8_t)q;
-        t -= (double)q;
+    for (int s = 0; s < i8::S; ++s) {
+        if (s > 0) t *= 256.0;
+        int q = __double2int_rn(t);
+        q = max(q, -128);
+        q = min(q, 127);
+        double rem = t - (double)q;
+        if (s < i8::S - 1 && rem > 127.0 / 255.0 && q < 127) { q += 1; rem -= 1.0; }
+        u[s] = (uint8_t)(int8_t)q;
+        t = rem;
     }
 }
 
@@ -287,7 +289,7 @@ __global__ void __launch_bounds__(256) kstar_mean_i8_kernel(const double* __rest
     }
 }
 
-// rowscale[r] = sf2 * 2^(e_r) with 2^(e_r) > max_k |Linv[r,k]|  (one warp per row)
+// rowscale[r] = sf2 * 2^(e_r) with 0.98 * 2^(e_r) >= max_k |Linv[r,k]|  (one warp per row)
 __global__ void __launch_bounds__(256) linv_rowscale_kernel(const double* __restrict__ Linv, int NP,
                                                             tb200_kernel_spec spec, const double* __restrict__ theta,
                                                             double* __restrict__ rowscale) {
@@ -299,7 +301,8 @@ __global__ void __launch_bounds__(256) linv_rowscale_kernel(const double* __rest
     for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
     if (lane == 0) {
         int e = 0;
-        frexp(mx, &e);  // mx = f * 2^e, f in [0.5, 1)  ->  |Linv / 2^e| < 1
+        const double f = frexp(mx, &e);  // mx = f * 2^e, f in [0.5, 1)
+        if (f > 0.98) ++e;               // |Linv / 2^e| <= 0.98: the leading balanced digit stays within s8
         rowscale[NP + r] = (double)e;  // second half of the buffer keeps the exponent for the slicing kernel
         rowscale[r] = unpack_hyper(spec, theta).sf2 * ldexp(1.0, e);
     }

@@ -43,7 +43,7 @@ __global__ void reference_kernel(const i8::Params p, int ct0, int nct, double* o
                 a[s] = p.candS[(size_t)s * p.candSliceStride + ((size_t)ct * p.kblks + kb) * i8::A_TILE + i8::tile_offset(c, k)];
                 const uint8_t bv =
                     p.linvS[(size_t)s * p.linvSliceStride + ((size_t)rt * p.kblks + kb) * i8::B_TILE + i8::tile_offset(rr, k)];
-                b[s] = s == 0 ? (int)(int8_t)bv : (int)bv;
+                b[s] = (int)(int8_t)bv;  // balanced digits: every Linv slice is s8
             }
             for (int i = 1; i <= i8::S; ++i)
                 for (int j = 1; j <= i8::S; ++j)

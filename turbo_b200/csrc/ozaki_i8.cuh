@@ -6,22 +6,29 @@
 // measured).  The 5th-gen tensor cores do 8192 INT8 MAC/clk/SM with exact INT32 accumulation, so a
 // product of two FP64 matrices can be assembled EXACTLY from byte slices:
 //
-//   Kstar[c,k] / sf2          = sum_{i=1..7} a_i[c,k] * 2^(-8i)              a_i in [0,255]   (u8)
-//   Linv[r,k]  / 2^(e_r)      = b_1[r,k] * 2^-7 + sum_{j=2..7} b_j 2^(1-8j)  b_1 in [-128,127] (s8),
-//                                                                            b_j in [0,255]   (u8)
+//   Kstar[c,k] / sf2          = sum_{i=1..7} a_i[c,k] * 2^(-8i)      a_i in [0,255]     (u8)
+//   Linv[r,k]  / 2^(e_r)      = sum_{j=1..7} b_j[r,k] * 2^(1-8j)     b_j in [-128,127]  (s8, balanced digits)
 //   V[c,r] = sf2 * 2^(e_r) * sum_g 2^(1-8g) * G_g[c,r],   G_g = sum_{i+j=g} sum_k a_i[c,k] b_j[r,k]
 //
-// Every G_g is an integer matrix product accumulated exactly in INT32 TMEM (7 pairs * 4096 * 255^2
-// < 2^31, hence n <= 4096 per accumulation pass).  Pairs with i+j > GMAX are dropped: GMAX = 8 keeps 28
+// Every G_g is an integer matrix product accumulated exactly in INT32 TMEM (7 pairs * 8192 * 255*128
+// < 2^31, hence n <= 8192 per accumulation pass).  Pairs with i+j > GMAX are dropped: GMAX = 8 keeps 28
 // products and truncates at ~2^-54 of (row max * sf2) per term; GMAX = 9 keeps 34 and is
-// indistinguishable from an FP64 GEMM (tests/test_gpu_i8.py, profiles/r1_ozaki_accuracy.md).
+// indistinguishable from an FP64 GEMM (tests/test_gpu_i8.py).
 //
-// Kernel shape: one CTA per (64 Linv rows) x (128 candidates) tile.  A-operand (M = 128) = candidate
-// slices, B-operand (N = 64) = Linv-row slices, both K-major in the canonical no-swizzle core-matrix
-// layout, pre-tiled in global memory so that one k-block (64 bytes of K) of one slice is ONE contiguous
-// bulk-async copy (cp.async.bulk, the TMA engine, no tensor map needed).  Warp 0 = copy producer,
-// warp 1 = MMA issuer (one elected lane) + TMEM owner, warps 2-5 = epilogue: each thread owns one
-// candidate (TMEM lane) and reduces its 64 columns in registers, so no cross-thread reduction.
+// Kernel shape: one CTA per (64 Linv rows) x (128 candidates) tile.  A-operand (M = 128) = one candidate
+// slice, B-operand = the Linv-row slices j = 1..GMAX-i STACKED along N (all digits are s8, so one
+// instruction descriptor serves every slice; the 64-row slice tiles are adjacent in shared memory, so the
+// stack is one canonical K-major operand of N = 64*(GMAX-i) rows).  One tcgen05.mma therefore produces the
+// products of a_i with several b_j at once and lands them in the accumulators of groups g = i+1 .. GMAX,
+// which are adjacent TMEM column blocks: 10 MMAs of N = 64..224 per K = 32 step instead of 28 of N = 64.
+// That matters because an M128 x N64 MMA re-reads 6 KB of operands from shared memory for 32 cycles of
+// tensor work and the shared-memory pipe, not the tensor pipe, was the limiter (profiles/r1_i8_ncu_full.md:
+// L1/TEX 78 %, tensor 73 %); stacking cuts operand reads per K step from 168 KB to 96 KB.
+// Both operands are K-major in the canonical no-swizzle core-matrix layout, pre-tiled in global memory so
+// that one k-block (64 bytes of K) of one slice is ONE contiguous bulk-async copy (cp.async.bulk, the TMA
+// engine, no tensor map needed).  Warp 0 = copy producer, warp 1 = MMA issuer (one elected lane) + TMEM
+// owner, warps 2-5 = epilogue: each thread owns one candidate (TMEM lane) and reduces its 64 columns in
+// registers, so no cross-thread reduction.
 #pragma once
 #include "common.cuh"
 
@@ -115,10 +122,25 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8]) {
                  : "r"(taddr));
 }
 
-// instruction descriptor: D = S32 (c_format 2 @4), A u8 (0 @7), B u8/s8 (@10), K-major both,
+// instruction descriptor: D = S32 (c_format 2 @4), A u8 (0 @7), B s8 (1 @10), K-major both,
 // N>>3 @17, M>>4 @24
-__host__ __device__ constexpr uint32_t idesc(int b_signed) {
-    return (2u << 4) | (0u << 7) | ((uint32_t)b_signed << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+__host__ __device__ constexpr uint32_t idesc(int n_cols) {
+    return (2u << 4) | (0u << 7) | (1u << 10) | ((uint32_t)(n_cols >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+}
+
+// MMAs of candidate slice tile `a_addr` against rows [n_lo, n_hi) of the stacked Linv slices at `b_addr`
+// -> TMEM columns d_tmem + [n_lo, n_hi); split into balanced chunks of <= 256 columns (multiples of 16)
+__device__ __forceinline__ void issue_stacked(uint32_t d_tmem, uint32_t a_addr, uint32_t b_addr, int n_lo, int n_hi,
+                                              uint32_t accumulate) {
+    const int width = n_hi - n_lo;
+    if (width <= 0) return;
+    const int nchunks = (width + 255) / 256;
+    const int chunk = ((width / nchunks) + 15) & ~15;
+    const uint64_t ad = make_desc(a_addr);
+    for (int n0 = n_lo; n0 < n_hi; n0 += chunk) {
+        const int nc = min(chunk, n_hi - n0);
+        umma_i8(d_tmem + n0, ad, make_desc(b_addr + (n0 >> 3) * SBO), idesc(nc), accumulate);
+    }
 }
 
 template <int GMAX>
@@ -177,7 +199,6 @@ __global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p)
     } else if (warp == 1) {
         if (lane == 0) {
             // ===== MMA issuer =====
-            uint32_t started = 0;  // bit g set once group g has received its first (overwriting) MMA
             for (int kb = 0; kb < nkb; ++kb) {
                 const int s = kb % STAGES;
                 mbar_wait(&full_bar[s], (kb / STAGES) & 1);
@@ -186,16 +207,23 @@ __global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p)
                 const uint32_t b0 = a0 + S * A_TILE;
 #pragma unroll
                 for (int ks = 0; ks < KB / 32; ++ks) {
+                    const bool first = (kb == 0 && ks == 0);
+                    int covered = 0;  // accumulator groups [0, covered) already hold a product (first step only)
 #pragma unroll
                     for (int i = 1; i <= S; ++i) {
-#pragma unroll
-                        for (int j = 1; j <= S; ++j) {
-                            if (i + j > GMAX) continue;
-                            const int g = i + j - 2;
-                            const uint64_t ad = make_desc(a0 + (i - 1) * A_TILE + ks * 2 * LBO);
-                            const uint64_t bd = make_desc(b0 + (j - 1) * B_TILE + ks * 2 * LBO);
-                            umma_i8(tmem_base + g * TN, ad, bd, idesc(j == 1 ? 1 : 0), (started >> g) & 1u);
-                            started |= 1u << g;
+                        const int J = (GMAX - i < S) ? GMAX - i : S;  // Linv slices j = 1..J pair with a_i
+                        if (J <= 0) continue;
+                        // a_i * b_j lands in group i+j-2: columns (i-1)*TN + (j-1)*TN of the accumulator block
+                        const uint32_t d = tmem_base + (i - 1) * TN;
+                        const uint32_t aa = a0 + (i - 1) * A_TILE + ks * 2 * LBO;
+                        const uint32_t bb = b0 + ks * 2 * LBO;
+                        if (!first) {
+                            issue_stacked(d, aa, bb, 0, J * TN, 1u);
+                        } else {
+                            const int split = (covered - (i - 1)) * TN;  // columns below `split` are initialised
+                            issue_stacked(d, aa, bb, 0, split < J * TN ? split : J * TN, 1u);
+                            issue_stacked(d, aa, bb, split > 0 ? split : 0, J * TN, 0u);
+                            if (i - 1 + J > covered) covered = i - 1 + J;
                         }
                     }
                 }
