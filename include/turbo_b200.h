@@ -130,6 +130,11 @@ int tb200_fp64_peak(double ms, double* dmma_tflops_host, double* dfma_tflops_hos
  * stream the kernel is launched on.  enable(1) starts collecting; read() synchronises, returns the
  * summed duration and the number of timed launches, and clears the record. */
 int tb200_timing_enable(int on);
+/* Diagnostic trace: one CUDA event before/after every kernel of tb200_acquire(_i8) on the stream it runs on,
+ * keeping the two-stream schedule.  tag = slot*16 + {0: before K*, 4: after K*, 1: before variance kernel,
+ * 2: after it, 3: after the epilogue}.  tb200_trace_read returns the number of records (times in ms from the first). */
+int tb200_trace_enable(int on);
+int tb200_trace_read(double* t_ms_host, int* tags_host, int cap);
 int tb200_timing_read(double* gemm_ms_host, int64_t* gemm_launches_host);
 
 /* plain C = alpha*op(A)*op(B) + beta*C on the library's DMMA GEMM (testing / roofline runs);

@@ -59,6 +59,8 @@ _SIGNATURES = {
     "tb200_generate_candidates": (C.c_int, [C.POINTER(CandSpecC), C.c_int, C.c_int64, C.c_int64, _P, _P]),
     "tb200_fp64_peak": (C.c_int, [C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "tb200_timing_enable": (C.c_int, [C.c_int]),
+    "tb200_trace_enable": (C.c_int, [C.c_int]),
+    "tb200_trace_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_int), C.c_int]),
     "tb200_timing_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "tb200_dgemm": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, _P, C.c_int, _P, C.c_int,
                               C.c_double, _P, C.c_int, _P]),

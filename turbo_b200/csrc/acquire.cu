@@ -176,17 +176,13 @@ __global__ void __launch_bounds__(256) kstar_mean_kernel(const double* __restric
 // ---------------------------------------------------------------------------------------------
 // INT8 engine (ozaki_i8.cuh): byte slicing of the two operands
 // ---------------------------------------------------------------------------------------------
-// digits of b in [0,1]:  b ~= sum_{s=1..7} u_s 2^(-8s), u_s in [0,255]; exact arithmetic (scaling by 256,
-// floor and the subtraction are error-free in FP64); the last digit is rounded
+// digits of b in [0,1]:  b ~= sum_{s=1..7} u_s 2^(-8s), u_s in [0,255]: b is rounded to 56-bit fixed point (one
+// exact power-of-two scaling + one conversion) and the digits are its bytes; b = 1 maps to 1 - 2^-56
 __device__ __forceinline__ void slice_unsigned(double t, uint8_t (&u)[i8::S]) {
+    unsigned long long x = __double2ull_rn(t * 72057594037927936.0);  // 2^56
+    x = min(x, 72057594037927935ull);
 #pragma unroll
-    for (int s = 0; s < i8::S; ++s) {
-        t *= 256.0;
-        int q = (s == i8::S - 1) ? __double2int_rd(t + 0.5) : __double2int_rd(t);
-        q = min(q, 255);
-        u[s] = (uint8_t)q;
-        t -= (double)q;
-    }
+    for (int s = 0; s < i8::S; ++s) u[s] = (uint8_t)(x >> (48 - 8 * s));
 }
 // balanced digits of a, |a| <= 0.98:  a = sum_{s=1..7} b_s 2^(1-8s), b_s in [-128,127].  Every step is exact in
 // FP64 (power-of-two scaling, integer subtraction).  Invariant: the remainder stays in [-128/255, 127/255], so the
@@ -206,86 +202,108 @@ __device__ __forceinline__ void slice_signed(double a, uint8_t (&u)[i8::S]) {
     }
 }
 
-// K* rows of CPB candidates as byte slices in the tiled layout ozaki_i8 reads, plus the predictive mean.
-// One CTA = 8 candidates (one core-matrix row group) x jchunk training points; 16 consecutive j of the 8
-// candidates form one contiguous 128-byte core matrix per slice, staged in shared memory and written
-// with 16-byte stores.
-__global__ void __launch_bounds__(256) kstar_mean_i8_kernel(const double* __restrict__ Xc, int64_t m_valid,
-                                                            const double* __restrict__ XsT, int n, int NP,
-                                                            tb200_kernel_spec spec, const double* __restrict__ theta,
-                                                            const double* __restrict__ alpha,
-                                                            uint8_t* __restrict__ KsS, long slice_stride,
-                                                            double* __restrict__ mean, int jchunk, long mean_stride) {
-    extern __shared__ double sh[];  // xc[CPB][d], red[8][CPB], then bytes[S][16 chunks][CPB][16]
+// K* rows of 8 candidates as byte slices in the tiled layout ozaki_i8 reads, plus the predictive mean.
+// Thread = (candidate c = tid & 7, group of 16 consecutive training points): its 16 values of one slice are exactly
+// one 16-byte row of a core matrix, and the 8 candidates of the CTA (one core-matrix row group) make the 128-byte core
+// matrix contiguous, so every slice is written with one 16-byte store per thread straight from registers -- no
+// shared-memory staging, no barriers in the loop, the candidate's coordinates are the only shared-memory reads.
+// (v1 walked one training point x 8 candidates per thread and staged single bytes through shared memory: 223
+// instructions per pair, 64 of them FP64 -- profiles/r1_kstar_ncu.md.)  KIND is a template parameter so the
+// 16-way unrolled body carries one kernel family.
+constexpr int KS_THREADS = 128;  // 16 point groups x 8 candidates; small CTAs share an SM with a variance CTA
+constexpr int KS_JG = 16;        // training points per thread and pass
+constexpr int KS_CTAS_PER_SM = 3;  // persistent grid: 3 x 128 threads x 88 registers fit beside one variance CTA
+
+template <int KIND>
+__global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_kernel(
+    const double* __restrict__ Xc, int64_t m_valid, const double* __restrict__ XsT, int n, int NP,
+    tb200_kernel_spec spec, const double* __restrict__ theta, const double* __restrict__ alpha,
+    uint8_t* __restrict__ KsS, long slice_stride, double* __restrict__ mean, int jchunk, long mean_stride, int ngroups,
+    int ksplit) {
+    extern __shared__ double sh[];  // xc[d][CPB] scaled candidates, red[4][CPB]
     const int d = spec.d;
     double* xc = sh;
     double* red = sh + CPB * d;
-    uint8_t* stage = reinterpret_cast<uint8_t*>(red + 8 * CPB);
-    const int64_t c0 = (int64_t)blockIdx.x * CPB;
-    for (int e = threadIdx.x; e < CPB * d; e += blockDim.x) {
-        const int c = e / d, k = e - c * d;
-        const int64_t ci = c0 + c;
-        xc[e] = (ci < m_valid) ? Xc[ci * d + k] / length_scale(spec, theta, k) : 0.0;
-    }
-    __syncthreads();
-    const Hyper h = unpack_hyper(spec, theta);
+    const double sf2 = unpack_hyper(spec, theta).sf2;
+    const int c = threadIdx.x & 7, jg = threadIdx.x >> 3;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int kblks = NP / i8::KB;
-    const int ct = (int)(c0 / i8::TM), rg = (int)((c0 % i8::TM) >> 3);
-    double msum[CPB];
+    // persistent: a few CTAs per SM walk the (candidate group, point split) items.  The block scheduler places a
+    // later grid only after every CTA of the grids ahead of it; a small grid is placed at once next to the resident
+    // variance CTAs instead of holding back (or being held back by) the 1024-CTA variance grid.
+    for (int item = blockIdx.x; item < ngroups * ksplit; item += gridDim.x) {
+        const int grp = item / ksplit, split = item - grp * ksplit;
+        const int64_t c0 = (int64_t)grp * CPB;
+        __syncthreads();  // previous item's xc / red are no longer read
+        for (int e = threadIdx.x; e < CPB * d; e += KS_THREADS) {
+            const int k = e / CPB, cc = e - k * CPB;
+            const int64_t ci = c0 + cc;
+            // sklearn divides the points by the length scale before cdist (kernels.py:1566, :1720)
+            xc[e] = (ci < m_valid) ? Xc[ci * d + k] / length_scale(spec, theta, k) : 0.0;
+        }
+        __syncthreads();
+        const int ct = (int)(c0 / i8::TM), rg = (int)((c0 % i8::TM) >> 3);
+        uint8_t* const tile_base = KsS + (size_t)ct * kblks * i8::A_TILE + (size_t)rg * i8::SBO + c * 16;
+        double msum = 0.0;
+        const int jlo = split * jchunk, jhi = min(NP, jlo + jchunk);
+        for (int j0 = jlo + jg * KS_JG; j0 < jhi; j0 += (KS_THREADS / 8) * KS_JG) {
+            double r2[KS_JG];
 #pragma unroll
-    for (int c = 0; c < CPB; ++c) msum[c] = 0.0;
-    const int jlo = blockIdx.y * jchunk, jhi = min(NP, jlo + jchunk);
-    for (int jb = jlo; jb < jhi; jb += 256) {
-        const int j = jb + threadIdx.x;
-        if (j < jhi) {
-            double r2[CPB];
-#pragma unroll
-            for (int c = 0; c < CPB; ++c) r2[c] = 0.0;
+            for (int q = 0; q < KS_JG; ++q) r2[q] = 0.0;
             for (int k = 0; k < d; ++k) {
-                const double xt = XsT[(long)k * NP + j];
+                const double xk = xc[k * CPB + c];
+                const double2* xt = reinterpret_cast<const double2*>(XsT + (long)k * NP + j0);
 #pragma unroll
-                for (int c = 0; c < CPB; ++c) {
-                    const double df = xc[c * d + k] - xt;
-                    r2[c] += df * df;
+                for (int q = 0; q < KS_JG / 2; ++q) {
+                    const double2 v = __ldg(xt + q);
+                    const double d0 = xk - v.x, d1 = xk - v.y;
+                    r2[2 * q] = fma(d0, d0, r2[2 * q]);
+                    r2[2 * q + 1] = fma(d1, d1, r2[2 * q + 1]);
                 }
             }
-            const double a = alpha[j];
-            const bool live = j < n;
+            uint32_t lo[KS_JG], hi[KS_JG];
+            const double2* al = reinterpret_cast<const double2*>(alpha + j0);
 #pragma unroll
-            for (int c = 0; c < CPB; ++c) {
-                const double g = live ? shape_fn(spec.kind, r2[c]) : 0.0;
-                msum[c] += (h.sf2 * g) * a;
-                uint8_t u[i8::S];
-                slice_unsigned(g, u);
+            for (int q = 0; q < KS_JG; q += 2) {
+                const double2 a = __ldg(al + (q >> 1));
+                const double g0 = (j0 + q < n) ? shape_fn(KIND, r2[q]) : 0.0;
+                const double g1 = (j0 + q + 1 < n) ? shape_fn(KIND, r2[q + 1]) : 0.0;
+                msum = fma(sf2 * g0, a.x, msum);
+                msum = fma(sf2 * g1, a.y, msum);
+                // 56-bit fixed point of g in [0,1] (see slice_unsigned): its bytes are the 7 digits
+                unsigned long long x0 = __double2ull_rn(g0 * 72057594037927936.0);
+                unsigned long long x1 = __double2ull_rn(g1 * 72057594037927936.0);
+                x0 = min(x0, 72057594037927935ull);
+                x1 = min(x1, 72057594037927935ull);
+                lo[q] = (uint32_t)x0; hi[q] = (uint32_t)(x0 >> 32);
+                lo[q + 1] = (uint32_t)x1; hi[q + 1] = (uint32_t)(x1 >> 32);
+            }
+            uint8_t* dst = tile_base + (size_t)(j0 / i8::KB) * i8::A_TILE + ((j0 % i8::KB) >> 4) * i8::LBO;
 #pragma unroll
-                for (int s = 0; s < i8::S; ++s)
-                    stage[((s * 16 + (threadIdx.x >> 4)) * CPB + c) * 16 + (threadIdx.x & 15)] = u[s];
+            for (int sl = 0; sl < i8::S; ++sl) {
+                // digit sl = byte (6 - sl) of the fixed-point value: bytes 2,1,0 of hi, then 3,2,1,0 of lo
+                const int byte = (sl < 3) ? 2 - sl : 6 - sl;
+                uint32_t w[4];
+#pragma unroll
+                for (int v = 0; v < 4; ++v) {
+                    const uint32_t* src = (sl < 3) ? hi : lo;
+                    const uint32_t p01 = __byte_perm(src[4 * v], src[4 * v + 1], byte | ((4 + byte) << 4));
+                    const uint32_t p23 = __byte_perm(src[4 * v + 2], src[4 * v + 3], byte | ((4 + byte) << 4));
+                    w[v] = __byte_perm(p01, p23, 0x5410);
+                }
+                *reinterpret_cast<uint4*>(dst + (size_t)sl * slice_stride) = make_uint4(w[0], w[1], w[2], w[3]);
             }
         }
+        // lanes with the same candidate (lane & 7) hold partial means: fold lane bits 3 and 4, then the 4 warps in order
+        msum += __shfl_xor_sync(0xffffffffu, msum, 8);
+        msum += __shfl_xor_sync(0xffffffffu, msum, 16);
+        if (lane < CPB) red[warp * CPB + lane] = msum;
         __syncthreads();
-        // 7 slices x (up to 16) core matrices of 128 B -> global, 16 B per thread
-        const int nchunks = min(16, (jhi - jb) >> 4);
-        for (int e = threadIdx.x; e < i8::S * nchunks * CPB; e += 256) {
-            const int row = e % CPB, jc = (e / CPB) % nchunks, sl = e / (CPB * nchunks);
-            const int jj = jb + jc * 16;
-            const size_t off = (size_t)sl * slice_stride + ((size_t)ct * kblks + jj / i8::KB) * i8::A_TILE +
-                               (size_t)rg * i8::SBO + ((jj % i8::KB) >> 4) * i8::LBO + row * 16;
-            *reinterpret_cast<uint4*>(KsS + off) =
-                *reinterpret_cast<const uint4*>(stage + ((sl * 16 + jc) * CPB + row) * 16);
+        if (threadIdx.x < CPB) {
+            double t = 0.0;
+            for (int w = 0; w < KS_THREADS / 32; ++w) t += red[w * CPB + threadIdx.x];
+            mean[split * mean_stride + c0 + threadIdx.x] = t;  // partial mean; the epilogue adds the splits in order
         }
-        __syncthreads();
-    }
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-    for (int c = 0; c < CPB; ++c) {
-        const double v = warp_sum(msum[c]);
-        if (lane == 0) red[warp * CPB + c] = v;
-    }
-    __syncthreads();
-    if (threadIdx.x < CPB) {
-        double t = 0.0;
-        for (int w = 0; w < 8; ++w) t += red[w * CPB + threadIdx.x];
-        mean[blockIdx.y * mean_stride + c0 + threadIdx.x] = t;
     }
 }
 
@@ -348,27 +366,48 @@ __device__ __forceinline__ bool better(double v, int64_t i, double bv, int64_t b
     return v > bv || (v == bv && i < bi);
 }
 
-__global__ void __launch_bounds__(1024) acquire_epilogue_kernel(
+// One CTA of 128 threads per 128 candidates: small enough to share an SM with a resident variance-kernel CTA
+// (a single 1024-thread CTA could not, and stalled the two-stream schedule until the other slot's GEMM had
+// drained).  CTA b keeps its own running best in best_val[b] / best_idx[b]: launches of one slot are ordered by
+// their stream, so the read-modify-write needs no atomics and the result is deterministic.
+constexpr int EPI_THREADS = 128;
+
+__global__ void __launch_bounds__(EPI_THREADS) acquire_epilogue_kernel(
     const double* __restrict__ mean, int nsplit, const double* __restrict__ partial, int ntiles, long ldp, int64_t batch,
     int64_t m_valid, int64_t local_base, int64_t index_base, tb200_kernel_spec spec,
     const double* __restrict__ theta, tb200_acq_spec acq,
     double* __restrict__ mu_out, double* __restrict__ sigma_out, double* __restrict__ acq_out,
     double* __restrict__ best_val, int64_t* __restrict__ best_idx) {
-    __shared__ double sv[32];
-    __shared__ int64_t si[32];
+    __shared__ double sv[EPI_THREADS / 32];
+    __shared__ int64_t si[EPI_THREADS / 32];
     double bv = -INFINITY;
     int64_t bi = -1;
     const Hyper hy = unpack_hyper(spec, theta);
     const double prior_var = hy.sf2 + hy.noise;  // kernel_.diag(X): const*1 + white (kernels.py:1315, :1438)
-    for (int64_t c = threadIdx.x; c < batch && c < m_valid; c += blockDim.x) {
-        double vv = 0.0;
-        for (int t = 0; t < ntiles; ++t) vv += partial[(long)t * ldp + c];
+    const int64_t c = (int64_t)blockIdx.x * EPI_THREADS + threadIdx.x;
+    if (c < batch && c < m_valid) {
+        // 4 independent chains over the row tiles, combined in a fixed order
+        double v4[4] = {0.0, 0.0, 0.0, 0.0};
+        int t = 0;
+        for (; t + 16 <= ntiles; t += 16) {  // 16 loads in flight
+            double ld[16];
+#pragma unroll
+            for (int u = 0; u < 16; ++u) ld[u] = partial[(long)(t + u) * ldp + c];
+#pragma unroll
+            for (int u = 0; u < 16; ++u) v4[u & 3] += ld[u];
+        }
+        for (; t + 4 <= ntiles; t += 4) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) v4[u] += partial[(long)(t + u) * ldp + c];
+        }
+        for (; t < ntiles; ++t) v4[0] += partial[(long)t * ldp + c];
+        const double vv = (v4[0] + v4[1]) + (v4[2] + v4[3]);
         double var = prior_var - vv;                // kernel_.diag(X) - einsum(V.T, V)
         if (var < 0.0) var = 0.0;                   // sklearn:_gpr.py:485-491
         var = var * (acq.y_std * acq.y_std);        // :494
         const double sigma = sqrt(var);
         double ms = 0.0;
-        for (int t = 0; t < nsplit; ++t) ms += mean[(long)t * ldp + c];
+        for (int u = 0; u < nsplit; ++u) ms += mean[(long)u * ldp + c];
         const double mu = acq.y_std * ms + acq.y_mean;  // :450
         double a;
         if (acq.acq == TB200_UCB) {
@@ -397,18 +436,20 @@ __global__ void __launch_bounds__(1024) acquire_epilogue_kernel(
     if (lane == 0) { sv[warp] = bv; si[warp] = bi; }
     __syncthreads();
     if (threadIdx.x == 0) {
-        double gv = *best_val;
-        int64_t gi = *best_idx;
-        for (int w = 0; w < (int)(blockDim.x >> 5); ++w)
+        double gv = best_val[blockIdx.x];
+        int64_t gi = best_idx[blockIdx.x];
+        for (int w = 0; w < EPI_THREADS / 32; ++w)
             if (si[w] >= 0 && better(sv[w], si[w], gv, gi)) { gv = sv[w]; gi = si[w]; }
-        *best_val = gv;
-        *best_idx = gi;
+        best_val[blockIdx.x] = gv;
+        best_idx[blockIdx.x] = gi;
     }
 }
 
-__global__ void best_reset_kernel(double* best_val, int64_t* best_idx) {
-    *best_val = -INFINITY;
-    *best_idx = -1;
+__global__ void best_reset_kernel(double* best_val, int64_t* best_idx, int count) {
+    for (int i = threadIdx.x; i < count; i += blockDim.x) {
+        best_val[i] = -INFINITY;
+        best_idx[i] = -1;
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -458,6 +499,19 @@ static cudaEvent_t next_event() {
     return g_events[g_events_used++];
 }
 
+// diagnostic trace (tb200_trace_enable): an event before and after every kernel of tb200_acquire, on the
+// stream it is launched on, WITHOUT changing the two-stream schedule -- shows what actually overlaps
+static bool g_trace = false;
+struct TraceRec { cudaEvent_t e; int tag; };
+static std::vector<TraceRec> g_trace_recs;
+static void trace_mark(int tag, cudaStream_t st) {
+    if (!g_trace || g_trace_recs.size() >= 4096) return;
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    cudaEventRecord(e, st);
+    g_trace_recs.push_back({e, tag});
+}
+
 struct AcqBuffers {
     double* cand;     // [batch][d]   generated candidates
     double* Ks;       // [batch][NP]
@@ -469,9 +523,15 @@ struct AcqBuffers {
 
 static size_t a256(size_t b) { return (b + 255) / 256 * 256; }
 
-// Two slots: consecutive candidate batches alternate between two internal streams so that the tail
-// of one batch's triangular GEMM, its epilogue and the next batch's K* kernel overlap.
-constexpr int ACQ_SLOTS = 2;
+// Two buffer slots and two internal streams split BY ROLE: a high-priority stream runs the small kernels (candidate
+// generation, K* + mean, epilogue) and a low-priority stream runs the variance kernels back to back.  The block
+// scheduler dispatches a later grid only once every CTA of the earlier grids has been placed, so with one stream
+// per slot the small kernels of batch b+1 queued behind the 1024-CTA variance grid of batch b and nothing overlapped
+// (tools/trace_acquire.py); with the priority split their CTAs are placed first and share the SMs with the resident
+// variance CTAs (tensor pipe vs FP64 pipe).  Order in the high-priority stream: K*_0 K*_1 [G_0] E_0 K*_2 [G_1] E_1 ...
+// ([G_b] = wait for the variance kernel of batch b), which also protects the slot buffers: K*_{b+2} overwrites
+// Ks/mean of slot b%2 only after G_b and E_b, and G_{b+2} (which waits for K*_{b+2}) overwrites `partial` after E_b.
+constexpr int ACQ_SLOTS = 3;
 constexpr int KSPLIT_MAX = 8;  // K* kernel: training points split over up to 8 CTAs per candidate group
 
 static size_t acquire_layout(int n, int d, int64_t batch, AcqBuffers* ab, char* base, bool use_i8 = false) {
@@ -488,30 +548,43 @@ static size_t acquire_layout(int n, int d, int64_t batch, AcqBuffers* ab, char* 
         double* Ks = take(use_i8 ? (size_t)i8::S * batch * NP : sizeof(double) * batch * NP);
         double* mean = take(sizeof(double) * KSPLIT_MAX * batch);
         double* partial = take(sizeof(double) * (use_i8 ? NP / i8::TN : NB) * batch);
-        double* bv = take(sizeof(double));
-        int64_t* bi = reinterpret_cast<int64_t*>(take(sizeof(int64_t)));
-        if (ab) { ab[s].cand = cand; ab[s].Ks = Ks; ab[s].mean = mean; ab[s].partial = partial;
-                  ab[s].best_val = bv; ab[s].best_idx = bi; }
+        if (ab) { ab[s].cand = cand; ab[s].Ks = Ks; ab[s].mean = mean; ab[s].partial = partial; }
     }
+    // running best per epilogue CTA, all slots contiguous (one reset, one merge)
+    const size_t nb = (size_t)(batch / EPI_THREADS);
+    double* bv = take(sizeof(double) * ACQ_SLOTS * nb);
+    int64_t* bi = reinterpret_cast<int64_t*>(take(sizeof(int64_t) * ACQ_SLOTS * nb));
+    if (ab)
+        for (int s = 0; s < ACQ_SLOTS; ++s) { ab[s].best_val = bv + s * nb; ab[s].best_idx = bi + s * nb; }
     return off;
 }
 
-// merge the per-slot bests into the caller's running best (read-modify-write, single thread)
-__global__ void best_merge_kernel(const double* v0, const int64_t* i0, const double* v1, const int64_t* i1,
-                                  double* best_val, int64_t* best_idx) {
-    double gv = *best_val;
-    int64_t gi = *best_idx;
-    if (*i0 >= 0 && better(*v0, *i0, gv, gi)) { gv = *v0; gi = *i0; }
-    if (v1 && *i1 >= 0 && better(*v1, *i1, gv, gi)) { gv = *v1; gi = *i1; }
-    *best_val = gv;
-    *best_idx = gi;
+// merge the per-CTA bests of the slots into the caller's running best (read-modify-write, one warp; the
+// (value, lowest index) order makes the result independent of how the entries are visited)
+__global__ void best_merge_kernel(const double* v, const int64_t* idx, int count, double* best_val,
+                                  int64_t* best_idx) {
+    double bv = -INFINITY;
+    int64_t bi = -1;
+    for (int e = threadIdx.x; e < count; e += 32)
+        if (idx[e] >= 0 && better(v[e], idx[e], bv, bi)) { bv = v[e]; bi = idx[e]; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double ov = __shfl_xor_sync(0xffffffffu, bv, o);
+        const int64_t oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (oi >= 0 && better(ov, oi, bv, bi)) { bv = ov; bi = oi; }
+    }
+    if (threadIdx.x == 0 && bi >= 0 && better(bv, bi, *best_val, *best_idx)) {
+        *best_val = bv;
+        *best_idx = bi;
+    }
 }
 
 // internal streams / events, one set per device, created on first use
 struct AcqStreams {
     bool ready = false;
-    cudaStream_t s[ACQ_SLOTS];
-    cudaEvent_t fork, join[ACQ_SLOTS];
+    cudaStream_t small, var;                       // high priority: K*/epilogue; low priority: variance kernels
+    cudaEvent_t fork, join_small, join_var;
+    cudaEvent_t kdone[ACQ_SLOTS], vdone[ACQ_SLOTS];
 };
 static AcqStreams g_streams[64];
 static int g_acq_streams = -1;  // -1: read TB200_ACQ_STREAMS on first use
@@ -522,14 +595,48 @@ static int acq_streams_for_device(AcqStreams** out) {
     TB_CHECK(dev >= 0 && dev < 64, "device ordinal out of range");
     AcqStreams& a = g_streams[dev];
     if (!a.ready) {
+        int lo = 0, hi = 0;  // numerically lower = higher priority
+        TB_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        // the small kernels get the high priority: their few CTAs are placed at once and the variance grid keeps
+        // filling the rest of each SM (TB200_ACQ_PRIORITY=var flips it, for experiments)
+        const char* flip = getenv("TB200_ACQ_PRIORITY");
+        const bool small_high = !(flip && flip[0] == 'v');
+        TB_CUDA(cudaStreamCreateWithPriority(&a.small, cudaStreamNonBlocking, small_high ? hi : lo));
+        TB_CUDA(cudaStreamCreateWithPriority(&a.var, cudaStreamNonBlocking, small_high ? lo : hi));
         for (int i = 0; i < ACQ_SLOTS; ++i) {
-            TB_CUDA(cudaStreamCreateWithFlags(&a.s[i], cudaStreamNonBlocking));
-            TB_CUDA(cudaEventCreateWithFlags(&a.join[i], cudaEventDisableTiming));
+            TB_CUDA(cudaEventCreateWithFlags(&a.kdone[i], cudaEventDisableTiming));
+            TB_CUDA(cudaEventCreateWithFlags(&a.vdone[i], cudaEventDisableTiming));
         }
         TB_CUDA(cudaEventCreateWithFlags(&a.fork, cudaEventDisableTiming));
+        TB_CUDA(cudaEventCreateWithFlags(&a.join_small, cudaEventDisableTiming));
+        TB_CUDA(cudaEventCreateWithFlags(&a.join_var, cudaEventDisableTiming));
         a.ready = true;
     }
     *out = &a;
+    return 0;
+}
+
+// All kernels that share the SMs with the variance kernel ask for the same (maximum) shared-memory carve-out: an SM
+// whose resident CTAs were launched with a small carve-out cannot take a 174 KB variance CTA until it has drained and
+// been reconfigured, which serialised the "concurrent" K* and variance kernels (tools/trace_acquire.py).
+static bool g_carveout_set[64] = {};
+static int g_sm_count = 148;
+static int configure_carveout() {
+    int dev = 0;
+    TB_CUDA(cudaGetDevice(&dev));
+    TB_CHECK(dev >= 0 && dev < 64, "device ordinal out of range");
+    if (g_carveout_set[dev]) return 0;
+    TB_CUDA(cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev));
+    const int mx = (int)cudaSharedmemCarveoutMaxShared;
+    TB_CUDA(cudaFuncSetAttribute(kstar_mean_i8_kernel<TB200_RBF>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
+    TB_CUDA(cudaFuncSetAttribute(kstar_mean_i8_kernel<TB200_MATERN12>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
+    TB_CUDA(cudaFuncSetAttribute(kstar_mean_i8_kernel<TB200_MATERN32>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
+    TB_CUDA(cudaFuncSetAttribute(kstar_mean_i8_kernel<TB200_MATERN52>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
+    TB_CUDA(cudaFuncSetAttribute(kstar_mean_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
+    TB_CUDA(cudaFuncSetAttribute(acquire_epilogue_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
+    TB_CUDA(cudaFuncSetAttribute(generate_candidates_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
+    TB_CUDA(cudaFuncSetAttribute(best_reset_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
+    g_carveout_set[dev] = true;
     return 0;
 }
 
@@ -559,7 +666,7 @@ size_t tb200_acquire_workspace_bytes(int n, int d, int64_t batch) {
 
 int tb200_best_reset(double* best_val, int64_t* best_idx, void* stream) {
     TB_CHECK(best_val && best_idx, "NULL pointer argument");
-    TB_LAUNCH(best_reset_kernel, dim3(1), dim3(1), 0, (cudaStream_t)stream, best_val, best_idx);
+    TB_LAUNCH(best_reset_kernel, dim3(1), dim3(1), 0, (cudaStream_t)stream, best_val, best_idx, 1);
     return 0;
 }
 
@@ -614,48 +721,84 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
 
     if (g_acq_streams < 0) {
         const char* e = getenv("TB200_ACQ_STREAMS");
-        g_acq_streams = (e && atoi(e) == 1) ? 1 : ACQ_SLOTS;
+        g_acq_streams = e ? atoi(e) : ACQ_SLOTS;  // number of buffer slots in flight (1 = serial)
+        if (g_acq_streams < 1) g_acq_streams = 1;
+        if (g_acq_streams > ACQ_SLOTS) g_acq_streams = ACQ_SLOTS;
     }
     // one batch, serial mode, or GEMM timing requested: everything on the caller's stream
     const int64_t nbatches = (m + batch - 1) / batch;
     const int slots = (nbatches < 2 || g_time_gemm) ? 1 : g_acq_streams;
+    if (configure_carveout()) return -1;
     AcqStreams* as = nullptr;
-    cudaStream_t ss[ACQ_SLOTS] = {st, st};
+    cudaStream_t s_small = st, s_var = st;
     if (slots > 1) {
         if (acq_streams_for_device(&as)) return -1;
+        s_small = as->small;
+        s_var = as->var;
         TB_CUDA(cudaEventRecord(as->fork, st));
-        for (int i = 0; i < slots; ++i) {
-            ss[i] = as->s[i];
-            TB_CUDA(cudaStreamWaitEvent(ss[i], as->fork, 0));
-        }
+        TB_CUDA(cudaStreamWaitEvent(s_small, as->fork, 0));
+        TB_CUDA(cudaStreamWaitEvent(s_var, as->fork, 0));
     }
-    for (int i = 0; i < slots; ++i)
-        TB_LAUNCH(best_reset_kernel, dim3(1), dim3(1), 0, ss[i], ab[i].best_val, ab[i].best_idx);
+    TB_LAUNCH(best_reset_kernel, dim3(1), dim3(64), 0, s_small, ab[0].best_val, ab[0].best_idx,
+              (int)(ACQ_SLOTS * (batch / EPI_THREADS)));
 
     const size_t ksm = sizeof(double) * (CPB * d + 8 * CPB);
     // split the training points so one K* launch is ~2k CTAs (3 resident per SM): NB/ksplit tiles each
     int ksplit = NB < KSPLIT_MAX ? NB : KSPLIT_MAX;
     const int jchunk = (NB + ksplit - 1) / ksplit * TILE;
     ksplit = (NP + jchunk - 1) / jchunk;
-    int64_t bno = 0;
-    for (int64_t off = 0; off < m; off += batch, ++bno) {
-        const int sl = (int)(bno % slots);
-        const AcqBuffers& w = ab[sl];
-        cudaStream_t cs = ss[sl];
-        const int64_t mb = (m - off < batch) ? (m - off) : batch;          // valid candidates
-        const int64_t mbp = (mb + 127) / 128 * 128;                          // padded to GEMM tiles
-        const double* xc = Xc ? Xc + off * d : nullptr;
+
+    struct Batch { int sl; int64_t off, mb, mbp; };
+    auto batch_of = [&](int64_t bno) {
+        Batch q;
+        q.sl = (int)(bno % slots);
+        q.off = bno * batch;
+        q.mb = (m - q.off < batch) ? (m - q.off) : batch;  // valid candidates
+        q.mbp = (q.mb + 127) / 128 * 128;                  // padded to GEMM tiles
+        return q;
+    };
+    // candidates (optional) + K* rows + mean of one batch, on the small-kernel stream
+    auto front = [&](int64_t bno) -> int {
+        const Batch q = batch_of(bno);
+        const AcqBuffers& w = ab[q.sl];
+        const double* xc = Xc ? Xc + q.off * d : nullptr;
         if (mode != TB200_CAND_GIVEN) {
             const CandGen g = make_gen(*cand, d);
-            const int64_t total = mb * d;
-            TB_LAUNCH(generate_candidates_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, cs, g, d,
-                      index_base + off, mb, w.cand);
+            const int64_t total = q.mb * d;
+            TB_LAUNCH(generate_candidates_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, s_small, g, d,
+                      index_base + q.off, q.mb, w.cand);
             xc = w.cand;
         }
+        trace_mark(q.sl * 16 + 0, s_small);
         if (use_i8) {
-            const size_t ksm8 = ksm + (size_t)i8::S * 16 * CPB * 16;
-            TB_LAUNCH(kstar_mean_i8_kernel, dim3((unsigned)(mbp / CPB), ksplit), dim3(256), ksm8, cs, xc, mb, XsT, n, NP,
-                      *spec, theta, alpha, reinterpret_cast<uint8_t*>(w.Ks), slice_stride, w.mean, jchunk, (long)batch);
+            const size_t ksm8 = sizeof(double) * (CPB * d + (KS_THREADS / 32) * CPB);
+            const int ngroups = (int)(q.mbp / CPB);
+            const int kctas = g_sm_count * KS_CTAS_PER_SM;
+            const dim3 kgrid((unsigned)(ngroups * ksplit < kctas ? ngroups * ksplit : kctas));
+#define TB_KSTAR_I8(KIND)                                                                                             \
+    TB_LAUNCH(kstar_mean_i8_kernel<KIND>, kgrid, dim3(KS_THREADS), ksm8, s_small, xc, q.mb, XsT, n, NP, *spec, theta, \
+              alpha, reinterpret_cast<uint8_t*>(w.Ks), slice_stride, w.mean, jchunk, (long)batch, ngroups, ksplit)
+            switch (spec->kind) {
+                case TB200_RBF: TB_KSTAR_I8(TB200_RBF); break;
+                case TB200_MATERN12: TB_KSTAR_I8(TB200_MATERN12); break;
+                case TB200_MATERN32: TB_KSTAR_I8(TB200_MATERN32); break;
+                default: TB_KSTAR_I8(TB200_MATERN52); break;
+            }
+#undef TB_KSTAR_I8
+        } else {
+            TB_LAUNCH(kstar_mean_kernel, dim3((unsigned)(q.mbp / CPB), ksplit), dim3(256), ksm, s_small, xc, q.mb, XsT, n,
+                      NP, *spec, theta, alpha, w.Ks, w.mean, jchunk, (long)batch);
+        }
+        trace_mark(q.sl * 16 + 4, s_small);
+        return 0;
+    };
+    // the variance contraction of one batch, on the variance stream
+    auto variance = [&](int64_t bno) -> int {
+        const Batch q = batch_of(bno);
+        const AcqBuffers& w = ab[q.sl];
+        if (g_time_gemm) TB_CUDA(cudaEventRecord(next_event(), s_var));
+        trace_mark(q.sl * 16 + 1, s_var);
+        if (use_i8) {
             i8::Params ip;
             ip.candS = reinterpret_cast<const uint8_t*>(w.Ks);
             ip.linvS = f8.linvS;
@@ -666,34 +809,57 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
             ip.linvSliceStride = (long)NP * NP;
             ip.kblks = NP / i8::KB;
             ip.rowTiles = NP / i8::TN;
-            ip.candTiles = (int)(mbp / i8::TM);
-            if (g_time_gemm) TB_CUDA(cudaEventRecord(next_event(), cs));
-            if (f8.gmax == 8 ? i8::launch_colsumsq_i8<8>(ip, cs) : i8::launch_colsumsq_i8<9>(ip, cs)) return -1;
-            if (g_time_gemm) TB_CUDA(cudaEventRecord(next_event(), cs));
+            ip.candTiles = (int)(q.mbp / i8::TM);
+            if (f8.gmax == 8 ? i8::launch_colsumsq_i8<8>(ip, s_var) : i8::launch_colsumsq_i8<9>(ip, s_var)) return -1;
         } else {
-            TB_LAUNCH(kstar_mean_kernel, dim3((unsigned)(mbp / CPB), ksplit), dim3(256), ksm, cs, xc, mb, XsT, n, NP,
-                      *spec, theta, alpha, w.Ks, w.mean, jchunk, (long)batch);
-            GemmParams gp = gemm_params(Linv, NP, w.Ks, NP, w.partial, batch, NB, (int)(mbp / 128), NP, 1.0, 0.0);
+            GemmParams gp = gemm_params(Linv, NP, w.Ks, NP, w.partial, batch, NB, (int)(q.mbp / 128), NP, 1.0, 0.0);
             gp.order = ORDER_RECT_HEAVY_LAST_ROW_FIRST;
             gp.khi_mode = KHI_BY_TI;
             gp.a_tri_diag = 1;  // Linv is lower triangular
             gp.epi = EPI_COLSUMSQ;
-            if (g_time_gemm) TB_CUDA(cudaEventRecord(next_event(), cs));
-            if (launch_gemm<false, true>(gp, 1, 1, cs)) return -1;
-            if (g_time_gemm) TB_CUDA(cudaEventRecord(next_event(), cs));
+            if (launch_gemm<false, true>(gp, 1, 1, s_var)) return -1;
         }
-        TB_LAUNCH(acquire_epilogue_kernel, dim3(1), dim3(1024), 0, cs, w.mean, ksplit, w.partial, ntiles, (long)batch, mbp, mb,
-                  off, index_base, *spec, theta, *acq, mu_out, sigma_out, acq_out, w.best_val, w.best_idx);
-    }
-    if (slots > 1) {
-        for (int i = 0; i < slots; ++i) {
-            TB_CUDA(cudaEventRecord(as->join[i], ss[i]));
-            TB_CUDA(cudaStreamWaitEvent(st, as->join[i], 0));
+        trace_mark(q.sl * 16 + 2, s_var);
+        if (g_time_gemm) TB_CUDA(cudaEventRecord(next_event(), s_var));
+        return 0;
+    };
+    auto epilogue = [&](int64_t bno) -> int {
+        const Batch q = batch_of(bno);
+        const AcqBuffers& w = ab[q.sl];
+        TB_LAUNCH(acquire_epilogue_kernel, dim3((unsigned)(q.mbp / EPI_THREADS)), dim3(EPI_THREADS), 0, s_small, w.mean,
+                  ksplit, w.partial, ntiles, (long)batch, q.mbp, q.mb, q.off, index_base, *spec, theta, *acq, mu_out,
+                  sigma_out, acq_out, w.best_val, w.best_idx);
+        trace_mark(q.sl * 16 + 3, s_small);
+        return 0;
+    };
+
+    if (slots == 1) {
+        for (int64_t bno = 0; bno < nbatches; ++bno)
+            if (front(bno) || variance(bno) || epilogue(bno)) return -1;
+    } else {
+        for (int64_t bno = 0; bno < slots && bno < nbatches; ++bno) {
+            if (front(bno)) return -1;
+            TB_CUDA(cudaEventRecord(as->kdone[bno % slots], s_small));
         }
+        for (int64_t bno = 0; bno < nbatches; ++bno) {
+            const int sl = (int)(bno % slots);
+            TB_CUDA(cudaStreamWaitEvent(s_var, as->kdone[sl], 0));
+            if (variance(bno)) return -1;
+            TB_CUDA(cudaEventRecord(as->vdone[sl], s_var));
+            TB_CUDA(cudaStreamWaitEvent(s_small, as->vdone[sl], 0));
+            if (epilogue(bno)) return -1;
+            if (bno + slots < nbatches) {
+                if (front(bno + slots)) return -1;
+                TB_CUDA(cudaEventRecord(as->kdone[sl], s_small));
+            }
+        }
+        TB_CUDA(cudaEventRecord(as->join_small, s_small));
+        TB_CUDA(cudaEventRecord(as->join_var, s_var));
+        TB_CUDA(cudaStreamWaitEvent(st, as->join_small, 0));
+        TB_CUDA(cudaStreamWaitEvent(st, as->join_var, 0));
     }
-    TB_LAUNCH(best_merge_kernel, dim3(1), dim3(1), 0, st, ab[0].best_val, ab[0].best_idx,
-              slots > 1 ? ab[1].best_val : (const double*)nullptr, slots > 1 ? ab[1].best_idx : (const int64_t*)nullptr,
-              best_val, best_idx);
+    TB_LAUNCH(best_merge_kernel, dim3(1), dim3(32), 0, st, ab[0].best_val, ab[0].best_idx,
+              (int)(ACQ_SLOTS * (batch / EPI_THREADS)), best_val, best_idx);
     return 0;
 }
 
@@ -735,6 +901,26 @@ int tb200_i8_prepare(const double* Linv, int n, const tb200_kernel_spec* spec, c
     TB_LAUNCH(linv_slice_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, st, Linv, NP, rowscale, linvS,
               (long)NP * NP);
     return 0;
+}
+
+int tb200_trace_enable(int on) {
+    g_trace = on != 0;
+    for (auto& r : g_trace_recs) cudaEventDestroy(r.e);
+    g_trace_recs.clear();
+    return 0;
+}
+
+int tb200_trace_read(double* t_ms, int* tags, int cap) {
+    TB_CHECK(t_ms && tags, "NULL pointer argument");
+    int k = 0;
+    for (size_t i = 0; i < g_trace_recs.size() && k < cap; ++i, ++k) {
+        TB_CUDA(cudaEventSynchronize(g_trace_recs[i].e));
+        float t = 0.f;
+        TB_CUDA(cudaEventElapsedTime(&t, g_trace_recs[0].e, g_trace_recs[i].e));
+        t_ms[k] = t;
+        tags[k] = g_trace_recs[i].tag;
+    }
+    return k;
 }
 
 int tb200_timing_enable(int on) {

@@ -80,7 +80,7 @@ __device__ __forceinline__ double shape_fn(int kind, double r2) {
         return (1.0 + t) * exp(-t);
     }
     const double t = r * 2.23606797749979;  // math.sqrt(5)
-    return (1.0 + t + t * t / 3.0) * exp(-t);
+    return (1.0 + t + t * t * (1.0 / 3.0)) * exp(-t);  // sklearn divides by 3.0: <= 1 ulp apart
 }
 
 // h(r2) with dK/dlog(l_k) = sf2 * h * D_k, D_k = ((x_k - x'_k)/l_k)^2 (sklearn:kernels.py:1581-1584,

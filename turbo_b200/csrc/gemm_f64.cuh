@@ -249,6 +249,8 @@ inline int launch_gemm(const GemmParams& p, int batch1, int batch2, cudaStream_t
     if (!configured) {
         TB_CUDA(cudaFuncSetAttribute(gemm_f64_kernel<TA, TB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)G_SMEM_BYTES));
+        TB_CUDA(cudaFuncSetAttribute(gemm_f64_kernel<TA, TB>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                     (int)cudaSharedmemCarveoutMaxShared));
         configured = true;
     }
     const long tiles = (p.order == ORDER_LOWER) ? (long)p.tilesM * (p.tilesM + 1) / 2 : (long)p.tilesM * p.tilesN;

@@ -128,18 +128,56 @@ __host__ __device__ constexpr uint32_t idesc(int n_cols) {
     return (2u << 4) | (0u << 7) | (1u << 10) | ((uint32_t)(n_cols >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
 }
 
-// MMAs of candidate slice tile `a_addr` against rows [n_lo, n_hi) of the stacked Linv slices at `b_addr`
-// -> TMEM columns d_tmem + [n_lo, n_hi); split into balanced chunks of <= 256 columns (multiples of 16)
-__device__ __forceinline__ void issue_stacked(uint32_t d_tmem, uint32_t a_addr, uint32_t b_addr, int n_lo, int n_hi,
-                                              uint32_t accumulate) {
-    const int width = n_hi - n_lo;
-    if (width <= 0) return;
-    const int nchunks = (width + 255) / 256;
-    const int chunk = ((width / nchunks) + 15) & ~15;
-    const uint64_t ad = make_desc(a_addr);
-    for (int n0 = n_lo; n0 < n_hi; n0 += chunk) {
-        const int nc = min(chunk, n_hi - n0);
-        umma_i8(d_tmem + n0, ad, make_desc(b_addr + (n0 >> 3) * SBO), idesc(nc), accumulate);
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
+}
+
+// MMAs of one candidate-slice tile (descriptor `ad`) against rows [N_LO, N_HI) of the stacked Linv slices (descriptor
+// of row 0 = `bd0`; 8 rows further = +SBO bytes = +SBO/16 in the descriptor's address field) -> TMEM columns
+// d_tmem + [N_LO, N_HI).  Balanced chunks of <= 256 columns (multiples of 16), all resolved at compile time so the
+// issuing lane executes a handful of uniform-register adds per MMA.
+template <int N_LO, int N_HI, int ACC>
+__device__ __forceinline__ void issue_range(uint32_t d_tmem, uint64_t ad, uint64_t bd0) {
+    if constexpr (N_HI > N_LO) {
+        constexpr int width = N_HI - N_LO;
+        constexpr int nchunks = (width + 255) / 256;
+        constexpr int chunk = ((width / nchunks) + 15) & ~15;
+        constexpr int nc = chunk < width ? chunk : width;
+        umma_i8(d_tmem + N_LO, ad, bd0 + (uint64_t)((N_LO >> 3) * (SBO >> 4)), idesc(nc), (uint32_t)ACC);
+        issue_range<N_LO + nc, N_HI, ACC>(d_tmem, ad, bd0);
+    }
+}
+
+// all slice products of one K = 32 step.  FIRST: no accumulator holds a value yet -- groups [0, COVERED) have been
+// written by earlier slices of this step, the rest are overwritten (accumulate = 0).
+template <int GMAX, int I, bool FIRST, int COVERED>
+__device__ __forceinline__ void issue_step(uint32_t tmem_base, uint64_t ad0, uint64_t bd0) {
+    if constexpr (I <= S) {
+        constexpr int J = (GMAX - I < S) ? GMAX - I : S;  // Linv slices j = 1..J pair with a_I
+        if constexpr (J > 0) {
+            // a_I * b_j lands in group I+j-2: columns (I-1)*TN + (j-1)*TN of the accumulator block
+            const uint32_t d = tmem_base + (I - 1) * TN;
+            const uint64_t ad = ad0 + (uint64_t)((I - 1) * (A_TILE >> 4));
+            if constexpr (!FIRST) {
+                issue_range<0, J * TN, 1>(d, ad, bd0);
+                issue_step<GMAX, I + 1, false, 0>(tmem_base, ad0, bd0);
+            } else {
+                constexpr int split0 = (COVERED - (I - 1)) * TN;  // columns below `split` are initialised
+                constexpr int split = split0 < 0 ? 0 : (split0 > J * TN ? J * TN : split0);
+                issue_range<0, split, 1>(d, ad, bd0);
+                issue_range<split, J * TN, 0>(d, ad, bd0);
+                constexpr int cov = (I - 1 + J > COVERED) ? I - 1 + J : COVERED;
+                issue_step<GMAX, I + 1, true, cov>(tmem_base, ad0, bd0);
+            }
+        } else {
+            issue_step<GMAX, I + 1, FIRST, COVERED>(tmem_base, ad0, bd0);
+        }
     }
 }
 
@@ -178,13 +216,13 @@ __global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p)
     const uint32_t tmem_base = tmem_base_s;
 
     if (warp == 0) {
-        if (lane == 0) {
-            // ===== producer: 14 bulk copies per k-block =====
-            const uint8_t* a_src = p.candS + ((size_t)ct * p.kblks) * A_TILE;
-            const uint8_t* b_src = p.linvS + ((size_t)rt * p.kblks) * B_TILE;
-            for (int kb = 0; kb < nkb; ++kb) {
-                const int s = kb % STAGES;
-                if (kb >= STAGES) mbar_wait(&empty_bar[s], ((kb / STAGES) - 1) & 1);
+        // ===== producer: 14 bulk copies per k-block, issued by one elected lane of a converged warp =====
+        const uint8_t* a_src = p.candS + ((size_t)ct * p.kblks) * A_TILE;
+        const uint8_t* b_src = p.linvS + ((size_t)rt * p.kblks) * B_TILE;
+        for (int kb = 0; kb < nkb; ++kb) {
+            const int s = kb % STAGES;
+            if (kb >= STAGES) mbar_wait(&empty_bar[s], ((kb / STAGES) - 1) & 1);
+            if (elect_one()) {
                 uint8_t* st = smem + (size_t)s * STAGE_BYTES;
                 mbar_expect_tx(&full_bar[s], STAGE_BYTES);
 #pragma unroll
@@ -195,41 +233,29 @@ __global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p)
                              B_TILE, &full_bar[s]);
                 }
             }
+            __syncwarp();
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ===== MMA issuer =====
-            for (int kb = 0; kb < nkb; ++kb) {
-                const int s = kb % STAGES;
-                mbar_wait(&full_bar[s], (kb / STAGES) & 1);
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t a0 = smem_u32(smem + (size_t)s * STAGE_BYTES);
-                const uint32_t b0 = a0 + S * A_TILE;
-#pragma unroll
-                for (int ks = 0; ks < KB / 32; ++ks) {
-                    const bool first = (kb == 0 && ks == 0);
-                    int covered = 0;  // accumulator groups [0, covered) already hold a product (first step only)
-#pragma unroll
-                    for (int i = 1; i <= S; ++i) {
-                        const int J = (GMAX - i < S) ? GMAX - i : S;  // Linv slices j = 1..J pair with a_i
-                        if (J <= 0) continue;
-                        // a_i * b_j lands in group i+j-2: columns (i-1)*TN + (j-1)*TN of the accumulator block
-                        const uint32_t d = tmem_base + (i - 1) * TN;
-                        const uint32_t aa = a0 + (i - 1) * A_TILE + ks * 2 * LBO;
-                        const uint32_t bb = b0 + ks * 2 * LBO;
-                        if (!first) {
-                            issue_stacked(d, aa, bb, 0, J * TN, 1u);
-                        } else {
-                            const int split = (covered - (i - 1)) * TN;  // columns below `split` are initialised
-                            issue_stacked(d, aa, bb, 0, split < J * TN ? split : J * TN, 1u);
-                            issue_stacked(d, aa, bb, split > 0 ? split : 0, J * TN, 0u);
-                            if (i - 1 + J > covered) covered = i - 1 + J;
-                        }
-                    }
+        // ===== MMA issuer: the warp stays converged, one elected lane issues =====
+        for (int kb = 0; kb < nkb; ++kb) {
+            const int s = kb % STAGES;
+            mbar_wait(&full_bar[s], (kb / STAGES) & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t a0 = smem_u32(smem + (size_t)s * STAGE_BYTES);
+            const uint64_t ad0 = make_desc(a0);
+            const uint64_t bd0 = make_desc(a0 + S * A_TILE);
+            if (elect_one()) {
+                // K = 32 per MMA: the second half of the 64-byte k-block is 2 LBO further (descriptor units of 16 B)
+                if (kb == 0) {
+                    issue_step<GMAX, 1, true, 0>(tmem_base, ad0, bd0);
+                } else {
+                    issue_step<GMAX, 1, false, 0>(tmem_base, ad0, bd0);
                 }
+                issue_step<GMAX, 1, false, 0>(tmem_base, ad0 + (uint64_t)((2 * LBO) >> 4), bd0 + (uint64_t)((2 * LBO) >> 4));
                 umma_commit(&empty_bar[s]);  // frees the stage once these MMAs have read it
+                if (kb == nkb - 1) umma_commit(&done_bar);
             }
-            umma_commit(&done_bar);
+            __syncwarp();
         }
     } else {
         // ===== epilogue: thread = candidate (TMEM lane), 64 columns = Linv rows of this tile =====
@@ -269,6 +295,10 @@ inline int launch_colsumsq_i8(const Params& p, cudaStream_t stream) {
     if (!configured) {
         TB_CUDA(cudaFuncSetAttribute(colsumsq_i8_kernel<GMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)SMEM_BYTES));
+        // same (maximum) carve-out as the small kernels that share the SMs with it: CTAs launched under different
+        // shared-memory configurations cannot be resident on one SM at the same time
+        TB_CUDA(cudaFuncSetAttribute(colsumsq_i8_kernel<GMAX>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                     (int)cudaSharedmemCarveoutMaxShared));
         configured = true;
     }
     TB_LAUNCH((colsumsq_i8_kernel<GMAX>), dim3((unsigned)(p.rowTiles * p.candTiles)), dim3(THREADS), SMEM_BYTES, stream,
