@@ -105,8 +105,10 @@ int tb200_best_reset(double* best_val, int64_t* best_idx, void* stream);
  *   tb200_i8_prepare: slice the inverse factor once per model.  linvS: tb200_i8_factor_bytes(n) bytes;
  *     rowscale: 2*NP doubles (scale sf2*2^e_r per row, then the exponents e_r).
  *   gmax = 8: 28 slice products (truncation ~2^-54 of row-max*sf2 per term, >= 40x inside the parity floor);
- *   gmax = 9: 34 products, indistinguishable from an FP64 GEMM.  n <= TB200_I8_MAX_N (INT32 exactness). */
-#define TB200_I8_MAX_N 4096
+ *   gmax = 9: 34 products, indistinguishable from an FP64 GEMM.  INT32 accumulation is exact for 8192 training
+ *   points per pass (balanced s8 digits of L^-1); rows longer than that are accumulated in several passes that are
+ *   summed in FP64 before squaring.  n <= TB200_I8_MAX_N (workspace sizing only). */
+#define TB200_I8_MAX_N 32768
 size_t tb200_i8_factor_bytes(int n);
 int tb200_i8_prepare(const double* Linv, int n, const tb200_kernel_spec* spec_host, const double* theta,
                      uint8_t* linvS, double* rowscale, void* stream);

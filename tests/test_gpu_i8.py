@@ -49,7 +49,9 @@ def test_i8_predict_and_acquisition_match_reference(golden, engine):
         np.testing.assert_array_equal(x[0], g["Xc"][idx])
 
 
-@pytest.mark.parametrize("n,d,kind,noise", [(1000, 6, 3, 1e-6), (2048, 3, 0, 1e-8), (4096, 10, 3, 1e-4)])
+# 8200 -> NP = 8320 = 130 row tiles: more than one INT32 accumulation pass (PASS_KB = 128 k-blocks) for the last rows
+@pytest.mark.parametrize("n,d,kind,noise", [(1000, 6, 3, 1e-6), (2048, 3, 0, 1e-8), (4096, 10, 3, 1e-4),
+                                            (8200, 8, 3, 1e-4)])
 def test_i8_matches_dmma_at_size(n, d, kind, noise):
     """full-size, including an ill-conditioned factor (large rows of L^-1): the three engines agree on the
     variance to the parity floor, and on the selected candidate"""
@@ -91,5 +93,5 @@ def test_i8_matches_dmma_at_size(n, d, kind, noise):
 def test_i8_rejects_large_n():
     from turbo_b200 import device
     with pytest.raises(ValueError):
-        device.resolve_engine("i8", 8192)
-    assert device.resolve_engine("auto", 8192) == "dmma" and device.resolve_engine("auto", 4096) == "i8"
+        device.resolve_engine("i8", 65536)
+    assert device.resolve_engine("auto", 65536) == "dmma" and device.resolve_engine("auto", 16384) == "i8"

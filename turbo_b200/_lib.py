@@ -12,7 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("TB200_LIB") or os.path.join(_HERE, "libturbo_b200.so")  # TB200_LIB: A/B builds
 MAX_D = 64
-I8_MAX_N = 4096  # TB200_I8_MAX_N
+I8_MAX_N = 32768  # TB200_I8_MAX_N
 
 KIND_RBF, KIND_MATERN12, KIND_MATERN32, KIND_MATERN52 = 0, 1, 2, 3
 ACQ_EI, ACQ_PI, ACQ_UCB = 0, 1, 2

@@ -703,7 +703,7 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
     TB_CHECK(spec->d >= 1 && spec->d <= TB200_MAX_D, "d out of range (1..64)");
     TB_CHECK(acq->acq >= TB200_EI && acq->acq <= TB200_UCB, "unknown acquisition function");
     TB_CHECK(!use_i8 || (f8.gmax == 8 || f8.gmax == 9), "i8 engine: gmax must be 8 or 9");
-    TB_CHECK(!use_i8 || pad_n(n) <= TB200_I8_MAX_N, "i8 engine: n > 4096 would overflow the INT32 accumulators");
+    TB_CHECK(!use_i8 || pad_n(n) <= TB200_I8_MAX_N, "i8 engine: n above TB200_I8_MAX_N");
     const int mode = cand ? cand->mode : TB200_CAND_GIVEN;
     if (m <= 0) return 0;
     TB_CHECK(mode != TB200_CAND_GIVEN || Xc, "Xc is NULL and no generator given");
@@ -894,7 +894,7 @@ int tb200_i8_prepare(const double* Linv, int n, const tb200_kernel_spec* spec, c
                      double* rowscale, void* stream) {
     TB_CHECK(Linv && spec && theta && linvS && rowscale, "NULL pointer argument");
     const int NP = pad_n(n);
-    TB_CHECK(NP <= TB200_I8_MAX_N, "i8 engine: n > 4096 would overflow the INT32 accumulators");
+    TB_CHECK(NP <= TB200_I8_MAX_N, "i8 engine: n above TB200_I8_MAX_N");
     cudaStream_t st = (cudaStream_t)stream;
     TB_LAUNCH(linv_rowscale_kernel, dim3(NP / 8), dim3(256), 0, st, Linv, NP, *spec, theta, rowscale);
     const long total = (long)NP * (NP / 16);

@@ -181,13 +181,23 @@ __device__ __forceinline__ void issue_step(uint32_t tmem_base, uint64_t ad0, uin
     }
 }
 
-template <int GMAX>
+// MULTI = false: the whole k-range of a tile (<= PASS_KB k-blocks, n <= 8192) is one exact INT32 accumulation pass.
+// MULTI = true : longer k-ranges are cut into passes of PASS_KB k-blocks; after each pass the epilogue threads drain the
+// accumulators into 64 FP64 registers per thread (the rows of V must be complete before they are squared) and hand
+// TMEM back to the MMA warp.  One drain costs ~3k cycles against ~230k cycles of MMAs per pass.
+constexpr int PASS_KB = 128;  // 8192 of K: 7 pairs * 8192 * 255 * 128 < 2^31
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+template <int GMAX, bool MULTI>
 __global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p) {
     constexpr int NG = GMAX - 1;  // groups g = 2..GMAX, one 64-column INT32 accumulator each
     static_assert(NG * TN <= TMEM_COLS, "accumulators exceed TMEM");
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], done_bar;
+    __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], done_bar, tfree_bar;
     __shared__ uint32_t tmem_base_s;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -202,6 +212,7 @@ __global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p)
             mbar_init(&empty_bar[s], 1);
         }
         mbar_init(&done_bar, 1);
+        mbar_init(&tfree_bar, TM);  // every epilogue thread arrives once it has drained its TMEM lane
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -239,6 +250,11 @@ __global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p)
         // ===== MMA issuer: the warp stays converged, one elected lane issues =====
         for (int kb = 0; kb < nkb; ++kb) {
             const int s = kb % STAGES;
+            const bool pass_start = MULTI ? (kb % PASS_KB == 0) : (kb == 0);
+            if (MULTI && pass_start && kb > 0) {
+                mbar_wait(&tfree_bar, ((kb / PASS_KB) - 1) & 1);  // accumulators of the previous pass drained
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            }
             mbar_wait(&full_bar[s], (kb / STAGES) & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t a0 = smem_u32(smem + (size_t)s * STAGE_BYTES);
@@ -246,37 +262,69 @@ __global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p)
             const uint64_t bd0 = make_desc(a0 + S * A_TILE);
             if (elect_one()) {
                 // K = 32 per MMA: the second half of the 64-byte k-block is 2 LBO further (descriptor units of 16 B)
-                if (kb == 0) {
+                if (pass_start) {
                     issue_step<GMAX, 1, true, 0>(tmem_base, ad0, bd0);
                 } else {
                     issue_step<GMAX, 1, false, 0>(tmem_base, ad0, bd0);
                 }
                 issue_step<GMAX, 1, false, 0>(tmem_base, ad0 + (uint64_t)((2 * LBO) >> 4), bd0 + (uint64_t)((2 * LBO) >> 4));
                 umma_commit(&empty_bar[s]);  // frees the stage once these MMAs have read it
-                if (kb == nkb - 1) umma_commit(&done_bar);
+                if (kb == nkb - 1 || (MULTI && (kb + 1) % PASS_KB == 0)) umma_commit(&done_bar);
             }
             __syncwarp();
         }
     } else {
         // ===== epilogue: thread = candidate (TMEM lane), 64 columns = Linv rows of this tile =====
         const int q = warp & 3;  // TMEM lane quarter this warp may access
-        mbar_wait(&done_bar, 0);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
         double acc = 0.0;
+        if constexpr (!MULTI) {
+            mbar_wait(&done_bar, 0);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll 1
-        for (int cc = 0; cc < TN / 8; ++cc) {
-            uint32_t r[NG][8];
+            for (int cc = 0; cc < TN / 8; ++cc) {
+                uint32_t r[NG][8];
 #pragma unroll
-            for (int g = 0; g < NG; ++g) tmem_ld8(lane_base + g * TN + cc * 8, r[g]);
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                for (int g = 0; g < NG; ++g) tmem_ld8(lane_base + g * TN + cc * 8, r[g]);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                // sum_g 2^(1-8(g+2)) G_g, smallest weight first
-                double v = 0.0;
+                for (int c = 0; c < 8; ++c) {
+                    // sum_g 2^(1-8(g+2)) G_g, smallest weight first
+                    double v = 0.0;
 #pragma unroll
-                for (int g = NG - 1; g >= 0; --g) v = fma((double)(int)r[g][c], ldexp(1.0, 1 - 8 * (g + 2)), v);
-                v *= __ldg(p.rowscale + rt * TN + cc * 8 + c);
+                    for (int g = NG - 1; g >= 0; --g) v = fma((double)(int)r[g][c], ldexp(1.0, 1 - 8 * (g + 2)), v);
+                    v *= __ldg(p.rowscale + rt * TN + cc * 8 + c);
+                    acc = fma(v, v, acc);
+                }
+            }
+        } else {
+            double vrow[TN];  // V[candidate, 64 rows] / rowscale, summed over the passes (registers: fully unrolled)
+            const int npass = (nkb + PASS_KB - 1) / PASS_KB;
+            for (int pass = 0; pass < npass; ++pass) {
+                mbar_wait(&done_bar, pass & 1);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+                for (int cc = 0; cc < TN / 8; ++cc) {
+                    uint32_t r[NG][8];
+#pragma unroll
+                    for (int g = 0; g < NG; ++g) tmem_ld8(lane_base + g * TN + cc * 8, r[g]);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) {
+                        double v = 0.0;
+#pragma unroll
+                        for (int g = NG - 1; g >= 0; --g) v = fma((double)(int)r[g][c], ldexp(1.0, 1 - 8 * (g + 2)), v);
+                        vrow[cc * 8 + c] = (pass == 0) ? v : vrow[cc * 8 + c] + v;
+                    }
+                }
+                if (pass + 1 < npass) {
+                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                    mbar_arrive(&tfree_bar);
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < TN; ++c) {
+                const double v = vrow[c] * __ldg(p.rowscale + rt * TN + c);
                 acc = fma(v, v, acc);
             }
         }
@@ -289,21 +337,28 @@ __global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p)
     }
 }
 
-template <int GMAX>
-inline int launch_colsumsq_i8(const Params& p, cudaStream_t stream) {
+template <int GMAX, bool MULTI>
+inline int launch_colsumsq_i8_impl(const Params& p, cudaStream_t stream) {
     static bool configured = false;
     if (!configured) {
-        TB_CUDA(cudaFuncSetAttribute(colsumsq_i8_kernel<GMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        TB_CUDA(cudaFuncSetAttribute(colsumsq_i8_kernel<GMAX, MULTI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)SMEM_BYTES));
         // same (maximum) carve-out as the small kernels that share the SMs with it: CTAs launched under different
         // shared-memory configurations cannot be resident on one SM at the same time
-        TB_CUDA(cudaFuncSetAttribute(colsumsq_i8_kernel<GMAX>, cudaFuncAttributePreferredSharedMemoryCarveout,
+        TB_CUDA(cudaFuncSetAttribute(colsumsq_i8_kernel<GMAX, MULTI>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                      (int)cudaSharedmemCarveoutMaxShared));
         configured = true;
     }
-    TB_LAUNCH((colsumsq_i8_kernel<GMAX>), dim3((unsigned)(p.rowTiles * p.candTiles)), dim3(THREADS), SMEM_BYTES, stream,
-              p);
+    TB_LAUNCH((colsumsq_i8_kernel<GMAX, MULTI>), dim3((unsigned)(p.rowTiles * p.candTiles)), dim3(THREADS), SMEM_BYTES,
+              stream, p);
     return 0;
+}
+
+template <int GMAX>
+inline int launch_colsumsq_i8(const Params& p, cudaStream_t stream) {
+    // the heaviest tile spans rowTiles k-blocks
+    return p.rowTiles <= PASS_KB ? launch_colsumsq_i8_impl<GMAX, false>(p, stream)
+                                 : launch_colsumsq_i8_impl<GMAX, true>(p, stream);
 }
 
 }  // namespace i8

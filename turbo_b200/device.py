@@ -108,13 +108,13 @@ class Factor:
 
 
 def resolve_engine(engine, NP):
-    """'auto' -> the INT8 tensor-core engine whenever its INT32 accumulation is exact (n <= 4096)"""
+    """'auto' -> the INT8 tensor-core engine for n <= I8_MAX_N (INT32 accumulation is exact per pass of 8192 training points; longer rows take several passes)"""
     engine = (engine or os.environ.get("TB200_ENGINE") or "auto").lower()
     if engine == "auto":
         engine = "i8" if NP <= _lib.I8_MAX_N else "dmma"
     if engine in ("i8", "i8x"):
         if NP > _lib.I8_MAX_N:
-            raise ValueError("the i8 variance engine needs n <= %d (INT32 exactness); use engine='dmma'" % _lib.I8_MAX_N)
+            raise ValueError("the i8 variance engine needs n <= %d; use engine='dmma'" % _lib.I8_MAX_N)
         return engine
     if engine != "dmma":
         raise ValueError("unknown variance engine %r (auto | dmma | i8 | i8x)" % engine)
@@ -124,7 +124,7 @@ def resolve_engine(engine, NP):
 class Acquirer:
     """runs tb200_acquire / tb200_acquire_i8 over device candidates or a generated set, keeping the running
     best on device.  engine: 'dmma' (FP64 tensor-core GEMM), 'i8' (INT8 tensor cores, 28 slice products),
-    'i8x' (34 slice products), 'auto' (i8 when n <= 4096)."""
+    'i8x' (34 slice products), 'auto' (i8 when n <= I8_MAX_N = 32768)."""
 
     def __init__(self, factor, acq_c, batch=0, engine=None):
         lib = _lib.load()
