@@ -9,7 +9,10 @@
 //   K^-1  : Linv^T Linv, one triangular GEMM;
 //   grad  : 0.5 * sum_ij (alpha alpha^T - K^-1)_ij dK_ij/dtheta with dK recomputed on the fly
 //           (sklearn materialises an (n,n,p) tensor: kernels.py:1753-1771).
+#include <stdlib.h>
+
 #include "gemm_f64.cuh"
+#include "ozaki_gemm.cuh"
 
 namespace tb200 {
 
@@ -366,6 +369,95 @@ __global__ void pad_vector_kernel(const double* __restrict__ y, int n, int NP, d
 }
 
 // ---------------------------------------------------------------------------------------------
+// INT8 engine of the batched fit (ozaki_gemm.cuh): scales and byte slicing of L and L^-1
+// ---------------------------------------------------------------------------------------------
+// balanced s8 digits of a, |a| <= 0.98 (same construction as slice_signed in acquire.cu)
+__device__ __forceinline__ void fit_slice_signed(double a, uint8_t (&u)[i8::S]) {
+    double t = a * 128.0;
+#pragma unroll
+    for (int s = 0; s < i8::S; ++s) {
+        if (s > 0) t *= 256.0;
+        int q = __double2int_rn(t);
+        q = max(q, -128);
+        q = min(q, 127);
+        double rem = t - (double)q;
+        if (s < i8::S - 1 && rem > 127.0 / 255.0 && q < 127) { q += 1; rem -= 1.0; }
+        u[s] = (uint8_t)(int8_t)q;
+        t = rem;
+    }
+}
+
+__device__ __forceinline__ double pow2_cover(double mx) {
+    if (!(mx > 0.0) || isinf(mx)) return 1.0;  // empty / failed member: any scale
+    int e = 0;
+    const double f = frexp(mx, &e);
+    if (f > 0.98) ++e;
+    return ldexp(1.0, e);
+}
+
+// rows of L: |L[r,k]| <= sqrt(K[r,r]) (sum_k L[r,k]^2 = K[r,r]), known from the Gram diagonal before factoring
+__global__ void rowscale_from_diag_kernel(const double* __restrict__ K, int NP, double* __restrict__ scale) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x, rs = blockIdx.y;
+    if (r >= NP) return;
+    const double dg = K[(size_t)rs * NP * NP + (size_t)r * NP + r];
+    scale[(size_t)rs * NP + r] = pow2_cover(sqrt(fabs(dg)));
+}
+
+// columns of the lower-triangular X = L^-1: max_{r >= c} |X[r,c]|  (threads of a warp read adjacent columns)
+__global__ void colscale_kernel(const double* __restrict__ X, int NP, double* __restrict__ scale) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x, rs = blockIdx.y;
+    if (c >= NP) return;
+    const double* x = X + (size_t)rs * NP * NP + c;
+    double m0 = 0.0, m1 = 0.0, m2 = 0.0, m3 = 0.0;
+    int r = c;
+    for (; r + 4 <= NP; r += 4) {
+        m0 = fmax(m0, fabs(x[(size_t)r * NP]));
+        m1 = fmax(m1, fabs(x[(size_t)(r + 1) * NP]));
+        m2 = fmax(m2, fabs(x[(size_t)(r + 2) * NP]));
+        m3 = fmax(m3, fabs(x[(size_t)(r + 3) * NP]));
+    }
+    for (; r < NP; ++r) m0 = fmax(m0, fabs(x[(size_t)r * NP]));
+    scale[(size_t)rs * NP + c] = pow2_cover(fmax(fmax(m0, m1), fmax(m2, m3)));
+}
+
+// One warp = one (8 operand rows) x (64 of K) piece = 4 core matrices per slice, written as 128 contiguous bytes
+// per core matrix.  TRANSPOSED = false: operand row = matrix row, K = matrix column (rows of L);
+// TRANSPOSED = true: operand row = matrix column, K = matrix row (columns of L^-1).
+// Pieces are enumerated over operand row groups [rg0, rg1) x k-blocks [kb0, kb1); with `lower` set, pieces whose
+// k-block lies entirely before the 128-row block of the operand rows are skipped (never read by the tri GEMM).
+template <bool TRANSPOSED>
+__global__ void __launch_bounds__(256) slice_operand_kernel(const double* __restrict__ M, int NP, long mStride,
+                                                            const double* __restrict__ scale, int rg0, int rg1, int kb0,
+                                                            int kb1, int lower, uint8_t* __restrict__ out, long sliceStride,
+                                                            long restartStride, int kblks) {
+    const int lane = threadIdx.x & 31;
+    const long piece = (long)blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int nkb = kb1 - kb0;
+    if (piece >= (long)(rg1 - rg0) * nkb) return;
+    const int rg = rg0 + (int)(piece / nkb), kb = kb0 + (int)(piece % nkb);
+    if (lower && kb < 2 * (rg / 16)) return;
+    const int rs = blockIdx.y;
+    const int orow = rg * 8 + (lane & 7);       // operand row
+    const int k0 = kb * 64 + (lane >> 3) * 16;  // first of this lane's 16 K indices
+    const double* src = M + (size_t)rs * mStride;
+    const double inv = 1.0 / scale[(size_t)rs * NP + orow];  // exact: power of two
+    __align__(16) uint8_t bytes[i8::S][16];
+#pragma unroll
+    for (int q = 0; q < 16; ++q) {
+        const double v = TRANSPOSED ? src[(size_t)(k0 + q) * NP + orow] : src[(size_t)orow * NP + k0 + q];
+        uint8_t u[i8::S];
+        fit_slice_signed(v * inv, u);
+#pragma unroll
+        for (int s = 0; s < i8::S; ++s) bytes[s][q] = u[s];
+    }
+    const size_t off = (size_t)rs * restartStride + ((size_t)(orow / 64) * kblks + kb) * i8::B_TILE +
+                       (size_t)((orow % 64) >> 3) * i8::SBO + (lane >> 3) * i8::LBO + (lane & 7) * 16;
+#pragma unroll
+    for (int s = 0; s < i8::S; ++s)
+        *reinterpret_cast<uint4*>(out + (size_t)s * sliceStride + off) = *reinterpret_cast<const uint4*>(bytes[s]);
+}
+
+// ---------------------------------------------------------------------------------------------
 // host drivers
 // ---------------------------------------------------------------------------------------------
 struct FitBuffers {
@@ -378,9 +470,26 @@ struct FitBuffers {
     double* alpha;   // [R][NP]
     double* logdet;  // [R]
     double* partial; // [R][ntiles64][p]
+    uint8_t* sliced; // [R][7][NP/64][NP/64][4096]  byte slices of L rows, then of L^-1 columns (INT8 engine)
+    double* scale;   // [R][NP] power-of-two row / column scales of the sliced operand
 };
 
+constexpr int FIT_GMAX = 9;  // 34 slice products: as accurate as the FP64 GEMM it replaces
+
 static size_t align256(size_t b) { return (b + 255) / 256 * 256; }
+
+static bool use_left_looking(int NB, int R) { return (long)R * NB >= 4 * 148; }
+
+// The batched (left-looking) schedule runs its long-K products on the INT8 tensor cores when one INT32 pass covers
+// the k-range (NP <= 8192).  TB200_FIT_ENGINE=dmma keeps everything on the FP64 DMMA GEMM.
+static bool fit_uses_i8(int NP, int R) {
+    static int forced = -1;
+    if (forced < 0) {
+        const char* e = getenv("TB200_FIT_ENGINE");
+        forced = (e && e[0] == 'd') ? 1 : 0;
+    }
+    return !forced && NP <= 8192 && use_left_looking(NP / TILE, R);
+}
 
 size_t fit_workspace_layout(int n, int d, int R, int p, bool own_linv, bool own_xst, bool own_alpha, FitBuffers* fb,
                             char* base) {
@@ -401,7 +510,14 @@ size_t fit_workspace_layout(int n, int d, int R, int p, bool own_linv, bool own_
     double* alpha = own_alpha ? take(sizeof(double) * R * NP) : nullptr;
     double* logdet = take(sizeof(double) * R);
     double* partial = take(sizeof(double) * R * nt64 * (p > 0 ? p : 1));
+    uint8_t* sliced = nullptr;
+    double* scale = nullptr;
+    if (fit_uses_i8((int)NP, R)) {
+        sliced = reinterpret_cast<uint8_t*>(take((size_t)i8::S * R * NP * NP));
+        scale = take(sizeof(double) * R * NP);
+    }
     if (fb) {
+        fb->sliced = sliced; fb->scale = scale;
         fb->K = K; fb->Linv = Linv; fb->Dinv = Dinv; fb->XsT = XsT; fb->ypad = ypad; fb->z = z;
         fb->alpha = alpha; fb->logdet = logdet; fb->partial = partial;
     }
@@ -414,7 +530,6 @@ size_t fit_workspace_layout(int n, int d, int R, int p, bool own_linv, bool own_
 //    each tile of C is read/written O(1) times instead of once per 128-wide step;
 //  * few matrices (the final factor, n large): RIGHT-looking, which exposes (NB-k)^2/2 tiles per
 //    step to fill 148 SMs from a single matrix.
-static bool use_left_looking(int NB, int R) { return (long)R * NB >= 4 * 148; }
 
 static int launch_diag(const FitBuffers& fb, int NP, int R, int k, int* info, cudaStream_t st) {
     const int NB = NP / TILE;
@@ -444,8 +559,21 @@ static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStr
     const int NB = NP / TILE;
     const long sK = (long)NP * NP;
     const bool left = use_left_looking(NB, R);
+    const bool i8fit = fit_uses_i8(NP, R) && fb.sliced != nullptr;
+    if (i8fit)
+        TB_LAUNCH(rowscale_from_diag_kernel, dim3((NP + 255) / 256, R), dim3(256), 0, st, fb.K, NP, fb.scale);
     for (int k = 0; k < NB; ++k) {
-        if (left && k > 0) {
+        if (i8fit && k > 0) {
+            // same block-column update on the INT8 tensor cores: rows of L are already sliced up to column k*128
+            i8::GemmI8Params g{};
+            g.S = fb.sliced; g.restartStride = (long)i8::S * sK; g.sliceStride = sK;
+            g.scale = fb.scale; g.scaleStride = NP;
+            g.C = fb.K; g.ldc = NP; g.cStride = sK;
+            g.kblks = NP / i8::KB; g.tri = 0;
+            g.rowTile0 = k; g.colTile0 = 2 * k; g.nColTiles = 2; g.kbLo = 0; g.kbHi = 2 * k;
+            g.alpha = -1.0; g.beta = 1.0;
+            if (i8::launch_gemm_i8<FIT_GMAX>(g, (NB - k) * 2, R, st)) return -1;
+        } else if (left && k > 0) {
             // block column k: A[i,k] -= L[i,0:k] L[k,0:k]^T  (i >= k), K = k*128 accumulated in registers
             const double* rows = fb.K + (long)k * TILE * NP;
             double* col = fb.K + (long)k * TILE * NP + (long)k * TILE;
@@ -457,6 +585,13 @@ static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStr
         const int rem = NB - k - 1;
         if (rem == 0) break;
         if (launch_panel(fb, NP, R, k, st)) return -1;
+        if (i8fit) {
+            // slice the finished panel L[(k+1)*128:, k*128:(k+1)*128] (k-blocks 2k, 2k+1 of those rows)
+            const int rg0 = (k + 1) * (TILE / 8), rg1 = NP / 8;
+            const long pieces = (long)(rg1 - rg0) * 2;
+            TB_LAUNCH(slice_operand_kernel<false>, dim3((unsigned)((pieces + 7) / 8), R), dim3(256), 0, st, fb.K, NP, sK,
+                      fb.scale, rg0, rg1, 2 * k, 2 * k + 2, 0, fb.sliced, sK, (long)i8::S * sK, NP / i8::KB);
+        }
         if (!left) {
             // trailing: A[i,j] -= A[i,k] A[j,k]^T  (k < j <= i)
             const double* panel = fb.K + (long)(k + 1) * TILE * NP + (long)k * TILE;
@@ -550,11 +685,28 @@ static int fit_pipeline(const double* X, const double* y_n, int n, const tb200_k
     TB_LAUNCH(lml_kernel, dim3(R), dim3(256), 0, st, fb.ypad, 0L, alpha, NP, n, fb.logdet, info, lml);
     if (with_grad) {
         // K^-1 (lower tiles) = Linv^T Linv, written over L
-        GemmParams q = gemm_params(Linv, NP, Linv, NP, fb.K, NP, NP / TILE, NP / TILE, NP, 1.0, 0.0);
-        q.order = ORDER_LOWER;
-        q.klo_mode = KLO_BY_TI;
-        q.sA1 = q.sB1 = q.sC1 = (long)NP * NP;
-        if (launch_gemm<true, false>(q, R, 1, st)) return -1;
+        if (fit_uses_i8(NP, R) && fb.sliced != nullptr) {
+            // INT8 tensor cores: operand rows = columns of Linv (K index = row), per-column power-of-two scales
+            const long sK = (long)NP * NP;
+            const int NB = NP / TILE;
+            TB_LAUNCH(colscale_kernel, dim3((NP + 127) / 128, R), dim3(128), 0, st, Linv, NP, fb.scale);
+            const long pieces = (long)(NP / 8) * (NP / i8::KB);
+            TB_LAUNCH(slice_operand_kernel<true>, dim3((unsigned)((pieces + 7) / 8), R), dim3(256), 0, st, Linv, NP, sK,
+                      fb.scale, 0, NP / 8, 0, NP / i8::KB, 1, fb.sliced, sK, (long)i8::S * sK, NP / i8::KB);
+            i8::GemmI8Params g{};
+            g.S = fb.sliced; g.restartStride = (long)i8::S * sK; g.sliceStride = sK;
+            g.scale = fb.scale; g.scaleStride = NP;
+            g.C = fb.K; g.ldc = NP; g.cStride = sK;
+            g.kblks = NP / i8::KB; g.tri = 1;
+            g.alpha = 1.0; g.beta = 0.0;
+            if (i8::launch_gemm_i8<FIT_GMAX>(g, NB * (NB + 1), R, st)) return -1;
+        } else {
+            GemmParams q = gemm_params(Linv, NP, Linv, NP, fb.K, NP, NP / TILE, NP / TILE, NP, 1.0, 0.0);
+            q.order = ORDER_LOWER;
+            q.klo_mode = KLO_BY_TI;
+            q.sA1 = q.sB1 = q.sC1 = (long)NP * NP;
+            if (launch_gemm<true, false>(q, R, 1, st)) return -1;
+        }
         const size_t sm = sizeof(double) * (2 * d * GT + 8 * p);
         TB_LAUNCH(lml_grad_kernel, dim3(nt64, R), dim3(256), sm, st, XsT, n, NP, spec, theta, p, fb.K, alpha,
                   fb.partial, nt64);

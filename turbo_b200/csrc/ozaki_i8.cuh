@@ -124,8 +124,9 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8]) {
 
 // instruction descriptor: D = S32 (c_format 2 @4), A u8 (0 @7), B s8 (1 @10), K-major both,
 // N>>3 @17, M>>4 @24
-__host__ __device__ constexpr uint32_t idesc(int n_cols) {
-    return (2u << 4) | (0u << 7) | (1u << 10) | ((uint32_t)(n_cols >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+__host__ __device__ constexpr uint32_t idesc(int n_cols, int a_signed = 0) {
+    return (2u << 4) | ((uint32_t)a_signed << 7) | (1u << 10) | ((uint32_t)(n_cols >> 3) << 17) |
+           ((uint32_t)(TM >> 4) << 24);
 }
 
 __device__ __forceinline__ bool elect_one() {
@@ -142,21 +143,21 @@ __device__ __forceinline__ bool elect_one() {
 // of row 0 = `bd0`; 8 rows further = +SBO bytes = +SBO/16 in the descriptor's address field) -> TMEM columns
 // d_tmem + [N_LO, N_HI).  Balanced chunks of <= 256 columns (multiples of 16), all resolved at compile time so the
 // issuing lane executes a handful of uniform-register adds per MMA.
-template <int N_LO, int N_HI, int ACC>
+template <int N_LO, int N_HI, int ACC, int ASGN = 0>
 __device__ __forceinline__ void issue_range(uint32_t d_tmem, uint64_t ad, uint64_t bd0) {
     if constexpr (N_HI > N_LO) {
         constexpr int width = N_HI - N_LO;
         constexpr int nchunks = (width + 255) / 256;
         constexpr int chunk = ((width / nchunks) + 15) & ~15;
         constexpr int nc = chunk < width ? chunk : width;
-        umma_i8(d_tmem + N_LO, ad, bd0 + (uint64_t)((N_LO >> 3) * (SBO >> 4)), idesc(nc), (uint32_t)ACC);
-        issue_range<N_LO + nc, N_HI, ACC>(d_tmem, ad, bd0);
+        umma_i8(d_tmem + N_LO, ad, bd0 + (uint64_t)((N_LO >> 3) * (SBO >> 4)), idesc(nc, ASGN), (uint32_t)ACC);
+        issue_range<N_LO + nc, N_HI, ACC, ASGN>(d_tmem, ad, bd0);
     }
 }
 
 // all slice products of one K = 32 step.  FIRST: no accumulator holds a value yet -- groups [0, COVERED) have been
 // written by earlier slices of this step, the rest are overwritten (accumulate = 0).
-template <int GMAX, int I, bool FIRST, int COVERED>
+template <int GMAX, int I, bool FIRST, int COVERED, int ASGN = 0>
 __device__ __forceinline__ void issue_step(uint32_t tmem_base, uint64_t ad0, uint64_t bd0) {
     if constexpr (I <= S) {
         constexpr int J = (GMAX - I < S) ? GMAX - I : S;  // Linv slices j = 1..J pair with a_I
@@ -165,18 +166,18 @@ __device__ __forceinline__ void issue_step(uint32_t tmem_base, uint64_t ad0, uin
             const uint32_t d = tmem_base + (I - 1) * TN;
             const uint64_t ad = ad0 + (uint64_t)((I - 1) * (A_TILE >> 4));
             if constexpr (!FIRST) {
-                issue_range<0, J * TN, 1>(d, ad, bd0);
-                issue_step<GMAX, I + 1, false, 0>(tmem_base, ad0, bd0);
+                issue_range<0, J * TN, 1, ASGN>(d, ad, bd0);
+                issue_step<GMAX, I + 1, false, 0, ASGN>(tmem_base, ad0, bd0);
             } else {
                 constexpr int split0 = (COVERED - (I - 1)) * TN;  // columns below `split` are initialised
                 constexpr int split = split0 < 0 ? 0 : (split0 > J * TN ? J * TN : split0);
-                issue_range<0, split, 1>(d, ad, bd0);
-                issue_range<split, J * TN, 0>(d, ad, bd0);
+                issue_range<0, split, 1, ASGN>(d, ad, bd0);
+                issue_range<split, J * TN, 0, ASGN>(d, ad, bd0);
                 constexpr int cov = (I - 1 + J > COVERED) ? I - 1 + J : COVERED;
-                issue_step<GMAX, I + 1, true, cov>(tmem_base, ad0, bd0);
+                issue_step<GMAX, I + 1, true, cov, ASGN>(tmem_base, ad0, bd0);
             }
         } else {
-            issue_step<GMAX, I + 1, FIRST, COVERED>(tmem_base, ad0, bd0);
+            issue_step<GMAX, I + 1, FIRST, COVERED, ASGN>(tmem_base, ad0, bd0);
         }
     }
 }
