@@ -420,16 +420,40 @@ __global__ void colscale_kernel(const double* __restrict__ X, int NP, double* __
     scale[(size_t)rs * NP + c] = pow2_cover(fmax(fmax(m0, m1), fmax(m2, m3)));
 }
 
+// column maxima of |M[r, c] * kmul(r)| for columns [col0, col0+128) over rows [row0, NP), kept as the bit pattern of a
+// non-negative double (order-preserving as an integer, so atomicMax works); `out` must be zero beforehand.
+// kmax != NULL: row r is weighted by the power-of-two cover of kmax[r] (the X column scale t_r of the trtri recurrence).
+__global__ void __launch_bounds__(128) colmax_bits_kernel(const double* __restrict__ M, int NP, long mStride, int col0,
+                                                          int row0, const unsigned long long* __restrict__ kmax,
+                                                          unsigned long long* __restrict__ out) {
+    const int rs = blockIdx.y, c = col0 + threadIdx.x;
+    const int r_lo = row0 + blockIdx.x * 128, r_hi = min(NP, r_lo + 128);
+    const double* x = M + (size_t)rs * mStride + c;
+    double m = 0.0;
+    for (int r = r_lo; r < r_hi; ++r) {
+        double v = fabs(x[(size_t)r * NP]);
+        if (kmax) v *= pow2_cover(__longlong_as_double((long long)kmax[(size_t)rs * NP + r]));
+        if (v > m) m = v;  // NaN never enters
+    }
+    if (m > 0.0) atomicMax(out + (size_t)rs * NP + c, (unsigned long long)__double_as_longlong(m));
+}
+
 // One warp = one (8 operand rows) x (64 of K) piece = 4 core matrices per slice, written as 128 contiguous bytes
-// per core matrix.  TRANSPOSED = false: operand row = matrix row, K = matrix column (rows of L);
-// TRANSPOSED = true: operand row = matrix column, K = matrix row (columns of L^-1).
+// per core matrix.  TRANSPOSED = false: operand row = matrix row, K = matrix column (rows of L / of X = L^-1);
+// TRANSPOSED = true: operand row = matrix column, K = matrix row (columns of L^-1, columns of an L panel).
 // Pieces are enumerated over operand row groups [rg0, rg1) x k-blocks [kb0, kb1); with `lower` set, pieces whose
 // k-block lies entirely before the 128-row block of the operand rows are skipped (never read by the tri GEMM).
+// Operand-row scale: `scale` (doubles) or the cover of `opmax` (bits) or 1.  K-index weight: kmode 1 multiplies by the
+// cover of kmax[k], kmode 2 divides by it (both exact: powers of two).  tileRow0: operand row of tile 0 of `out`
+// (a panel buffer holds only its own two 64-row tiles).  scale_out (optional): the operand-row scale as a double.
 template <bool TRANSPOSED>
 __global__ void __launch_bounds__(256) slice_operand_kernel(const double* __restrict__ M, int NP, long mStride,
-                                                            const double* __restrict__ scale, int rg0, int rg1, int kb0,
-                                                            int kb1, int lower, uint8_t* __restrict__ out, long sliceStride,
-                                                            long restartStride, int kblks) {
+                                                            const double* __restrict__ scale,
+                                                            const unsigned long long* __restrict__ opmax,
+                                                            const unsigned long long* __restrict__ kmax, int kmode,
+                                                            int rg0, int rg1, int kb0, int kb1, int lower, int tileRow0,
+                                                            uint8_t* __restrict__ out, long sliceStride,
+                                                            long restartStride, int kblks, double* __restrict__ scale_out) {
     const int lane = threadIdx.x & 31;
     const long piece = (long)blockIdx.x * 8 + (threadIdx.x >> 5);
     const int nkb = kb1 - kb0;
@@ -440,17 +464,25 @@ __global__ void __launch_bounds__(256) slice_operand_kernel(const double* __rest
     const int orow = rg * 8 + (lane & 7);       // operand row
     const int k0 = kb * 64 + (lane >> 3) * 16;  // first of this lane's 16 K indices
     const double* src = M + (size_t)rs * mStride;
-    const double inv = 1.0 / scale[(size_t)rs * NP + orow];  // exact: power of two
+    double osc = 1.0;
+    if (scale) osc = scale[(size_t)rs * NP + orow];
+    else if (opmax) osc = pow2_cover(__longlong_as_double((long long)opmax[(size_t)rs * NP + orow]));
+    if (scale_out && kb == kb0 && (lane >> 3) == 0) scale_out[(size_t)rs * NP + orow] = osc;
+    const double inv = 1.0 / osc;  // exact: power of two
     __align__(16) uint8_t bytes[i8::S][16];
 #pragma unroll
     for (int q = 0; q < 16; ++q) {
-        const double v = TRANSPOSED ? src[(size_t)(k0 + q) * NP + orow] : src[(size_t)orow * NP + k0 + q];
+        double v = TRANSPOSED ? src[(size_t)(k0 + q) * NP + orow] : src[(size_t)orow * NP + k0 + q];
+        if (kmode) {
+            const double t = pow2_cover(__longlong_as_double((long long)kmax[(size_t)rs * NP + k0 + q]));
+            v = (kmode == 1) ? v * t : v / t;
+        }
         uint8_t u[i8::S];
         fit_slice_signed(v * inv, u);
 #pragma unroll
         for (int s = 0; s < i8::S; ++s) bytes[s][q] = u[s];
     }
-    const size_t off = (size_t)rs * restartStride + ((size_t)(orow / 64) * kblks + kb) * i8::B_TILE +
+    const size_t off = (size_t)rs * restartStride + ((size_t)((orow - tileRow0) / 64) * kblks + kb) * i8::B_TILE +
                        (size_t)((orow % 64) >> 3) * i8::SBO + (lane >> 3) * i8::LBO + (lane & 7) * 16;
 #pragma unroll
     for (int s = 0; s < i8::S; ++s)
@@ -472,6 +504,10 @@ struct FitBuffers {
     double* partial; // [R][ntiles64][p]
     uint8_t* sliced; // [R][7][NP/64][NP/64][4096]  byte slices of L rows, then of L^-1 columns (INT8 engine)
     double* scale;   // [R][NP] power-of-two row / column scales of the sliced operand
+    unsigned long long* tmax;  // [R][NP] column maxima of X = L^-1 (bits of a double), trtri recurrence
+    unsigned long long* smax;  // [R][NP] column maxima of the weighted L panels
+    double* sigma;   // [R][NP] power-of-two scales of the weighted L panels
+    uint8_t* bpanel; // [R][7][2][NP/64][4096] byte slices of one weighted L panel (B operand of the trtri step)
 };
 
 constexpr int FIT_GMAX = 9;  // 34 slice products: as accurate as the FP64 GEMM it replaces
@@ -512,12 +548,20 @@ size_t fit_workspace_layout(int n, int d, int R, int p, bool own_linv, bool own_
     double* partial = take(sizeof(double) * R * nt64 * (p > 0 ? p : 1));
     uint8_t* sliced = nullptr;
     double* scale = nullptr;
-    if (fit_uses_i8((int)NP, R)) {
+    const bool i8fit = fit_uses_i8((int)NP, R);
+    if (i8fit) {
         sliced = reinterpret_cast<uint8_t*>(take((size_t)i8::S * R * NP * NP));
         scale = take(sizeof(double) * R * NP);
     }
+    unsigned long long* tmax = nullptr; unsigned long long* smax = nullptr; double* sigma = nullptr; uint8_t* bpanel = nullptr;
+    if (i8fit) {
+        tmax = reinterpret_cast<unsigned long long*>(take(sizeof(double) * R * NP));
+        smax = reinterpret_cast<unsigned long long*>(take(sizeof(double) * R * NP));
+        sigma = take(sizeof(double) * R * NP);
+        bpanel = reinterpret_cast<uint8_t*>(take((size_t)i8::S * R * 2 * (NP / i8::KB) * i8::B_TILE));
+    }
     if (fb) {
-        fb->sliced = sliced; fb->scale = scale;
+        fb->sliced = sliced; fb->scale = scale; fb->tmax = tmax; fb->smax = smax; fb->sigma = sigma; fb->bpanel = bpanel;
         fb->K = K; fb->Linv = Linv; fb->Dinv = Dinv; fb->XsT = XsT; fb->ypad = ypad; fb->z = z;
         fb->alpha = alpha; fb->logdet = logdet; fb->partial = partial;
     }
@@ -590,7 +634,8 @@ static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStr
             const int rg0 = (k + 1) * (TILE / 8), rg1 = NP / 8;
             const long pieces = (long)(rg1 - rg0) * 2;
             TB_LAUNCH(slice_operand_kernel<false>, dim3((unsigned)((pieces + 7) / 8), R), dim3(256), 0, st, fb.K, NP, sK,
-                      fb.scale, rg0, rg1, 2 * k, 2 * k + 2, 0, fb.sliced, sK, (long)i8::S * sK, NP / i8::KB);
+                      fb.scale, (const unsigned long long*)nullptr, (const unsigned long long*)nullptr, 0, rg0, rg1, 2 * k,
+                      2 * k + 2, 0, 0, fb.sliced, sK, (long)i8::S * sK, NP / i8::KB, (double*)nullptr);
         }
         if (!left) {
             // trailing: A[i,j] -= A[i,k] A[j,k]^T  (k < j <= i)
@@ -617,10 +662,70 @@ __global__ void __launch_bounds__(256) place_diag_blocks_kernel(const double* __
     }
 }
 
+// Linv = L^-1 on the INT8 tensor cores, block column by block column from the right:
+//   X[i,c] = -( sum_{k=c+1..i} X[i,k] L[k,c] ) Dinv_c      (i > c; X[c,c] = Dinv_c)
+// Every X block column to the right of c is complete, so its column maxima t_k are known: the A operand is
+// X[i,k] / t_k (|.| <= 0.98, sliced once per block column as it completes) and the weight moves into the B operand
+// L[k,c] * t_k, a 128-column panel that is sliced (transposed, with its own column scales sigma) per step.
+// All scalings are powers of two, so the product is exact to the kept slice pairs as in ozaki_gemm.cuh.
+static int trtri_batched_i8(const FitBuffers& fb, double* Linv, int NP, int R, cudaStream_t st) {
+    const int NB = NP / TILE, kblks = NP / i8::KB;
+    const long sK = (long)NP * NP, sD = (long)NB * TILE * TILE;
+    const long bSlice = (long)2 * kblks * i8::B_TILE, bRestart = (long)i8::S * bSlice;
+    TB_CUDA(cudaMemsetAsync(Linv, 0, sizeof(double) * (size_t)R * NP * NP, st));
+    TB_LAUNCH(place_diag_blocks_kernel, dim3(NB, R), dim3(256), 0, st, fb.Dinv, sD, Linv, NP);
+    TB_CUDA(cudaMemsetAsync(fb.tmax, 0, sizeof(double) * (size_t)R * NP, st));
+    TB_CUDA(cudaMemsetAsync(fb.smax, 0, sizeof(double) * (size_t)R * NP, st));
+    const unsigned long long* none = nullptr;
+    for (int c = NB - 2; c >= 0; --c) {
+        const int c1 = c + 1, rem = NB - c1;
+        // column scales of the finished block column c1 of X, then its byte slices (rows >= c1*128, k-blocks 2c1, 2c1+1)
+        TB_LAUNCH(colmax_bits_kernel, dim3(rem, R), dim3(128), 0, st, Linv, NP, sK, c1 * TILE, c1 * TILE, none, fb.tmax);
+        {
+            const int rg0 = c1 * (TILE / 8), rg1 = NP / 8;
+            const long pieces = (long)(rg1 - rg0) * 2;
+            TB_LAUNCH(slice_operand_kernel<false>, dim3((unsigned)((pieces + 7) / 8), R), dim3(256), 0, st, Linv, NP, sK,
+                      (const double*)nullptr, none, (const unsigned long long*)fb.tmax, 2, rg0, rg1, 2 * c1, 2 * c1 + 2, 0,
+                      0, fb.sliced, sK, (long)i8::S * sK, kblks, (double*)nullptr);
+        }
+        // weighted panel L[k, c-block] * t_k (k >= c1*128): column scales, then transposed byte slices
+        TB_LAUNCH(colmax_bits_kernel, dim3(rem, R), dim3(128), 0, st, fb.K, NP, sK, c * TILE, c1 * TILE,
+                  (const unsigned long long*)fb.tmax, fb.smax);
+        {
+            const int rg0 = c * (TILE / 8), rg1 = rg0 + TILE / 8;
+            const long pieces = (long)(rg1 - rg0) * (kblks - 2 * c1);
+            TB_LAUNCH(slice_operand_kernel<true>, dim3((unsigned)((pieces + 7) / 8), R), dim3(256), 0, st, fb.K, NP, sK,
+                      (const double*)nullptr, (const unsigned long long*)fb.smax, (const unsigned long long*)fb.tmax, 1, rg0,
+                      rg1, 2 * c1, kblks, 0, c * TILE, fb.bpanel, bSlice, bRestart, kblks, fb.sigma);
+        }
+        // T[i, c-block] = -sum_k (X[i,k]/t_k) (L[k,c] t_k), rows of block rows c1.., k-blocks [2c1, 2(it+1))
+        {
+            i8::GemmI8Params g{};
+            g.S = fb.sliced; g.restartStride = (long)i8::S * sK; g.sliceStride = sK;
+            g.scale = nullptr; g.scaleStride = NP;
+            g.SB = fb.bpanel; g.restartStrideB = bRestart; g.sliceStrideB = bSlice; g.scaleB = fb.sigma;
+            g.C = Linv; g.ldc = NP; g.cStride = sK;
+            g.kblks = kblks; g.tri = 0;
+            g.rowTile0 = c1; g.colTile0 = 2 * c; g.nColTiles = 2; g.kbLo = 2 * c1; g.kbHi = kblks; g.kbHiByRow = 1;
+            g.alpha = -1.0; g.beta = 0.0;
+            if (i8::launch_gemm_i8<FIT_GMAX>(g, rem * 2, R, st)) return -1;
+        }
+        // X[i, c-block] = T[i, c-block] * Dinv_c  (in place, 128-deep DMMA GEMM)
+        {
+            double* col = Linv + (long)c1 * TILE * NP + (long)c * TILE;
+            GemmParams p = gemm_params(col, NP, fb.Dinv + (long)c * TILE * TILE, TILE, col, NP, rem, 1, TILE, 1.0, 0.0);
+            p.sA1 = sK; p.sB1 = sD; p.sC1 = sK;
+            if (launch_gemm<false, false>(p, R, 1, st)) return -1;
+        }
+    }
+    return 0;
+}
+
 // Linv = L^-1 for R factors, from the inverted diagonal blocks; GEMM only
 static int trtri_batched(const FitBuffers& fb, double* Linv, int NP, int R, cudaStream_t st) {
     const int NB = NP / TILE;
     const long sK = (long)NP * NP, sD = (long)NB * TILE * TILE;
+    if (fit_uses_i8(NP, R) && fb.sliced != nullptr && !getenv("TB200_TRTRI_DMMA")) return trtri_batched_i8(fb, Linv, NP, R, st);
     if (use_left_looking(NB, R)) {
         // row block i:  X[i,c] = -Dinv_i * sum_{k=c}^{i-1} L[i,k] X[k,c]  (c < i),  X[i,i] = Dinv_i
         TB_CUDA(cudaMemsetAsync(Linv, 0, sizeof(double) * (size_t)R * NP * NP, st));
@@ -692,7 +797,8 @@ static int fit_pipeline(const double* X, const double* y_n, int n, const tb200_k
             TB_LAUNCH(colscale_kernel, dim3((NP + 127) / 128, R), dim3(128), 0, st, Linv, NP, fb.scale);
             const long pieces = (long)(NP / 8) * (NP / i8::KB);
             TB_LAUNCH(slice_operand_kernel<true>, dim3((unsigned)((pieces + 7) / 8), R), dim3(256), 0, st, Linv, NP, sK,
-                      fb.scale, 0, NP / 8, 0, NP / i8::KB, 1, fb.sliced, sK, (long)i8::S * sK, NP / i8::KB);
+                      fb.scale, (const unsigned long long*)nullptr, (const unsigned long long*)nullptr, 0, 0, NP / 8, 0,
+                      NP / i8::KB, 1, 0, fb.sliced, sK, (long)i8::S * sK, NP / i8::KB, (double*)nullptr);
             i8::GemmI8Params g{};
             g.S = fb.sliced; g.restartStride = (long)i8::S * sK; g.sliceStride = sK;
             g.scale = fb.scale; g.scaleStride = NP;

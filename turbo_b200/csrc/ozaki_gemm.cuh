@@ -13,11 +13,14 @@ namespace tb200 {
 namespace i8 {
 
 struct GemmI8Params {
-    const uint8_t* S;      // sliced operand
+    const uint8_t* S;      // sliced A operand (and B operand unless SB is set)
     long restartStride;    // bytes between restarts
     long sliceStride;      // bytes between slices of one restart
-    const double* scale;   // [restart][rows]: 2^(e_r), |x[r,k]| <= 0.98 * 2^(e_r)
+    const double* scale;   // [restart][rows]: 2^(e_r), |x[r,k]| <= 0.98 * 2^(e_r); NULL = 1 (A side)
     long scaleStride;
+    const uint8_t* SB;     // optional separate B operand (a panel buffer): tile index = jt - colTile0
+    long restartStrideB, sliceStrideB;
+    const double* scaleB;  // scales of the B rows, indexed by absolute output column; NULL = `scale`
     double* C;             // FP64 output, row-major
     long ldc, cStride;
     int kblks;             // k-blocks per 64-row tile (= K extent of the buffer / 64)
@@ -25,6 +28,7 @@ struct GemmI8Params {
                            // 0: rectangle rowTile0.. x colTile0.., k-blocks [kbLo, kbHi)
     int rowTile0, colTile0, nColTiles;  // 128-row tiles / 64-col tiles (rectangle mode)
     int kbLo, kbHi;
+    int kbHiByRow;         // rectangle mode: k-blocks [kbLo, 2*(it+1)) (A is lower triangular: X[i,k] = 0 for k > i)
     double alpha, beta;
 };
 
@@ -51,7 +55,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_i8_kernel(const GemmI8Params 
         it = p.rowTile0 + (int)blockIdx.x / p.nColTiles;
         jt = p.colTile0 + (int)blockIdx.x % p.nColTiles;
         kb_lo = p.kbLo;
-        kb_hi = p.kbHi;
+        kb_hi = p.kbHiByRow ? 2 * (it + 1) : p.kbHi;
     }
     const int nkb = kb_hi - kb_lo;
     const int rs = (int)blockIdx.y;  // restart
@@ -80,7 +84,9 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_i8_kernel(const GemmI8Params 
         const uint8_t* base = p.S + (size_t)rs * p.restartStride;
         const uint8_t* a0_src = base + ((size_t)(2 * it) * p.kblks) * B_TILE;
         const uint8_t* a1_src = base + ((size_t)(2 * it + 1) * p.kblks) * B_TILE;
-        const uint8_t* b_src = base + ((size_t)jt * p.kblks) * B_TILE;
+        const uint8_t* b_src = p.SB ? p.SB + (size_t)rs * p.restartStrideB + ((size_t)(jt - p.colTile0) * p.kblks) * B_TILE
+                                    : base + ((size_t)jt * p.kblks) * B_TILE;
+        const long b_slice = p.SB ? p.sliceStrideB : p.sliceStride;
         for (int i = 0; i < nkb; ++i) {
             const int s = i % STAGES;
             const size_t kb = (size_t)(kb_lo + i);
@@ -93,7 +99,8 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_i8_kernel(const GemmI8Params 
                     const size_t so = (size_t)sl * p.sliceStride + kb * B_TILE;
                     bulk_g2s(st + sl * A_TILE, a0_src + so, B_TILE, &full_bar[s]);
                     bulk_g2s(st + sl * A_TILE + B_TILE, a1_src + so, B_TILE, &full_bar[s]);
-                    bulk_g2s(st + S * A_TILE + sl * B_TILE, b_src + so, B_TILE, &full_bar[s]);
+                    bulk_g2s(st + S * A_TILE + sl * B_TILE, b_src + (size_t)sl * b_slice + kb * B_TILE, B_TILE,
+                             &full_bar[s]);
                 }
             }
             __syncwarp();
@@ -125,10 +132,9 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_i8_kernel(const GemmI8Params 
         const int q = warp & 3;
         const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
         const int row = it * TM + q * 32 + lane;
-        const double* sc = p.scale + (size_t)rs * p.scaleStride;
-        const double srow = p.alpha * sc[row];
+        const double srow = p.alpha * (p.scale ? p.scale[(size_t)rs * p.scaleStride + row] : 1.0);
         double* crow = p.C + (size_t)rs * p.cStride + (size_t)row * p.ldc + (size_t)jt * TN;
-        const double* scol = sc + jt * TN;
+        const double* scol = (p.scaleB ? p.scaleB : p.scale) + (size_t)rs * p.scaleStride + jt * TN;
         mbar_wait(&done_bar, 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll 1
