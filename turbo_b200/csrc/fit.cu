@@ -268,6 +268,32 @@ __global__ void lml_kernel(const double* __restrict__ y, long strideY, const dou
 // ---------------------------------------------------------------------------------------------
 // gradient trace: partial[r][tile][q] over lower 64x64 tiles of W = alpha alpha^T - K^-1
 // ---------------------------------------------------------------------------------------------
+// g(r2) and h(r2) of common.cuh's shape_fn / shape_grad_fn from ONE sqrt and ONE exp
+template <int KIND>
+__device__ __forceinline__ void shape_pair(double r2, double& g, double& h) {
+    if (KIND == TB200_RBF) {
+        g = h = exp(-0.5 * r2);
+    } else if (KIND == TB200_MATERN12) {
+        const double r = sqrt(r2);
+        g = exp(-r);
+        h = r != 0.0 ? g / r : 0.0;
+    } else if (KIND == TB200_MATERN32) {
+        const double t = sqrt(3.0 * r2);  // shape_grad_fn's form; shape_fn's r*sqrt(3) differs by <= 1 ulp
+        const double e = exp(-t);
+        g = (1.0 + t) * e;
+        h = 3.0 * e;
+    } else {
+        const double t = sqrt(5.0 * r2);
+        const double e = exp(-t);
+        g = (1.0 + t + t * t * (1.0 / 3.0)) * e;
+        h = 5.0 / 3.0 * (t + 1.0) * e;
+    }
+}
+
+// Each thread owns a 4x4 block of pairs.  Pass 1: r2 and the pair weights f = 2 w sf2 h(r2) stay in registers;
+// pass 2 walks the dimensions ONCE MORE as the outer loop, so the per-dimension sums never live in a dynamically
+// indexed (= local-memory) array: one scalar per dimension is reduced over the warp and parked in shared memory.
+template <int KIND>
 __global__ void __launch_bounds__(256) lml_grad_kernel(const double* __restrict__ XsT, int n, int NP,
                                                        tb200_kernel_spec spec, const double* __restrict__ theta,
                                                        int p, const double* __restrict__ Kinv,
@@ -288,61 +314,97 @@ __global__ void __launch_bounds__(256) lml_grad_kernel(const double* __restrict_
         xj[e] = xs[(long)k * NP + tj * GT + c];
     }
     __syncthreads();
-    const Hyper h = unpack_hyper(spec, theta + (long)r * p);
+    const Hyper hy = unpack_hyper(spec, theta + (long)r * p);
     const double* Kr = Kinv + (long)r * NP * NP;
     const double* al = alpha + (long)r * NP;
     const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nl = spec.ard ? d : 1;
     const int off_ls = spec.has_const ? 1 : 0;
-    double g_const = 0.0, g_noise = 0.0;
-    double g_ls[TB200_MAX_D];
-    for (int k = 0; k < nl; ++k) g_ls[k] = 0.0;
+    const int i0 = ti * GT + ty * 4, j0 = tj * GT + tx * 4;
 
+    // w = alpha_i alpha_j - Kinv_ij for the valid lower pairs (loads first: they overlap the distance loop)
+    double w[4][4];
+#pragma unroll
     for (int a = 0; a < 4; ++a) {
-        const int i = ti * GT + ty * 4 + a;
-        if (i >= n) continue;
-        const double ai = al[i];
+        const int i = i0 + a;
+        const double ai = i < n ? al[i] : 0.0;
+#pragma unroll
         for (int b = 0; b < 4; ++b) {
-            const int j = tj * GT + tx * 4 + b;
-            if (j > i || j >= n) continue;
-            const double w = ai * al[j] - Kr[(long)i * NP + j];
-            if (i == j) {
-                g_const += w * h.sf2;  // dK/dlog(const) on the diagonal = sf2 * 1
-                g_noise += w * h.noise;
-                continue;
-            }
-            double r2 = 0.0;
-            for (int k = 0; k < d; ++k) {
-                const double df = xi[k * GT + ty * 4 + a] - xj[k * GT + tx * 4 + b];
-                r2 += df * df;
-            }
-            const double w2 = 2.0 * w;  // (i,j) and (j,i)
-            g_const += w2 * h.sf2 * shape_fn(spec.kind, r2);
-            const double f = w2 * h.sf2 * shape_grad_fn(spec.kind, r2);
-            if (spec.ard) {
-                for (int k = 0; k < d; ++k) {
-                    const double df = xi[k * GT + ty * 4 + a] - xj[k * GT + tx * 4 + b];
-                    g_ls[k] += f * (df * df);
-                }
-            } else {
-                g_ls[0] += f * r2;
-            }
+            const int j = j0 + b;
+            w[a][b] = (i < n && j <= i) ? ai * al[j] - Kr[(long)i * NP + j] : 0.0;
         }
     }
-    // block reduction of p values, fixed order
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int q = 0; q < p; ++q) {
-        double v;
-        if (spec.has_const && q == 0) v = g_const;
-        else if (q < off_ls + nl) v = g_ls[q - off_ls];
-        else v = g_noise;
-        v = warp_sum(v);
-        if (lane == 0) red[warp * p + q] = v;
+    double r2[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) r2[a][b] = 0.0;
+    for (int k = 0; k < d; ++k) {
+        double xa[4], xb[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) { xa[a] = xi[k * GT + ty * 4 + a]; xb[a] = xj[k * GT + tx * 4 + a]; }
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                const double df = xa[a] - xb[b];
+                r2[a][b] += df * df;
+            }
+    }
+    double g_const = 0.0, g_noise = 0.0, g_iso = 0.0;
+    double f[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const int i = i0 + a, j = j0 + b;
+            f[a][b] = 0.0;
+            if (!(i < n && j <= i)) continue;
+            if (i == j) {
+                g_const += w[a][b] * hy.sf2;  // dK/dlog(const) on the diagonal = sf2 * 1
+                g_noise += w[a][b] * hy.noise;
+                continue;
+            }
+            double g, h;
+            shape_pair<KIND>(r2[a][b], g, h);
+            const double w2 = 2.0 * w[a][b];  // (i,j) and (j,i)
+            g_const += w2 * hy.sf2 * g;
+            f[a][b] = w2 * hy.sf2 * h;
+            g_iso += f[a][b] * r2[a][b];
+        }
+    // warp sums in a fixed order, one slot per (warp, hyper-parameter)
+    {
+        const double vc = warp_sum(g_const), vn = warp_sum(g_noise);
+        if (lane == 0) {
+            if (spec.has_const) red[warp * p] = vc;
+            if (spec.has_white) red[warp * p + off_ls + nl] = vn;
+        }
+    }
+    if (spec.ard) {
+        for (int k = 0; k < d; ++k) {
+            double xa[4], xb[4];
+#pragma unroll
+            for (int a = 0; a < 4; ++a) { xa[a] = xi[k * GT + ty * 4 + a]; xb[a] = xj[k * GT + tx * 4 + a]; }
+            double acc = 0.0;
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b) {
+                    const double df = xa[a] - xb[b];
+                    acc += f[a][b] * (df * df);
+                }
+            acc = warp_sum(acc);
+            if (lane == 0) red[warp * p + off_ls + k] = acc;
+        }
+    } else {
+        const double v = warp_sum(g_iso);
+        if (lane == 0) red[warp * p + off_ls] = v;
     }
     __syncthreads();
     if (threadIdx.x < p) {
         double t = 0.0;
-        for (int w = 0; w < 8; ++w) t += red[w * p + threadIdx.x];
+        for (int wq = 0; wq < 8; ++wq) t += red[wq * p + threadIdx.x];
         partial[((long)r * ntiles + blockIdx.x) * p + threadIdx.x] = t;
     }
 }
@@ -510,7 +572,19 @@ struct FitBuffers {
     uint8_t* bpanel; // [R][7][2][NP/64][4096] byte slices of one weighted L panel (B operand of the trtri step)
 };
 
-constexpr int FIT_GMAX = 9;  // 34 slice products: as accurate as the FP64 GEMM it replaces
+// slice products kept by the fit GEMMs: 9 (34 products, as accurate as the FP64 GEMM it replaces; default) or
+// 8 (28 products, TB200_FIT_GMAX=8)
+static int fit_gmax() {
+    static int g = 0;
+    if (!g) {
+        const char* e = getenv("TB200_FIT_GMAX");
+        g = (e && atoi(e) == 8) ? 8 : 9;
+    }
+    return g;
+}
+static int launch_fit_gemm_i8(const i8::GemmI8Params& g, int ntiles, int R, cudaStream_t st) {
+    return fit_gmax() == 8 ? i8::launch_gemm_i8<8>(g, ntiles, R, st) : i8::launch_gemm_i8<9>(g, ntiles, R, st);
+}
 
 static size_t align256(size_t b) { return (b + 255) / 256 * 256; }
 
@@ -616,7 +690,7 @@ static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStr
             g.kblks = NP / i8::KB; g.tri = 0;
             g.rowTile0 = k; g.colTile0 = 2 * k; g.nColTiles = 2; g.kbLo = 0; g.kbHi = 2 * k;
             g.alpha = -1.0; g.beta = 1.0;
-            if (i8::launch_gemm_i8<FIT_GMAX>(g, (NB - k) * 2, R, st)) return -1;
+            if (launch_fit_gemm_i8(g, (NB - k) * 2, R, st)) return -1;
         } else if (left && k > 0) {
             // block column k: A[i,k] -= L[i,0:k] L[k,0:k]^T  (i >= k), K = k*128 accumulated in registers
             const double* rows = fb.K + (long)k * TILE * NP;
@@ -708,7 +782,7 @@ static int trtri_batched_i8(const FitBuffers& fb, double* Linv, int NP, int R, c
             g.kblks = kblks; g.tri = 0;
             g.rowTile0 = c1; g.colTile0 = 2 * c; g.nColTiles = 2; g.kbLo = 2 * c1; g.kbHi = kblks; g.kbHiByRow = 1;
             g.alpha = -1.0; g.beta = 0.0;
-            if (i8::launch_gemm_i8<FIT_GMAX>(g, rem * 2, R, st)) return -1;
+            if (launch_fit_gemm_i8(g, rem * 2, R, st)) return -1;
         }
         // X[i, c-block] = T[i, c-block] * Dinv_c  (in place, 128-deep DMMA GEMM)
         {
@@ -805,7 +879,7 @@ static int fit_pipeline(const double* X, const double* y_n, int n, const tb200_k
             g.C = fb.K; g.ldc = NP; g.cStride = sK;
             g.kblks = NP / i8::KB; g.tri = 1;
             g.alpha = 1.0; g.beta = 0.0;
-            if (i8::launch_gemm_i8<FIT_GMAX>(g, NB * (NB + 1), R, st)) return -1;
+            if (launch_fit_gemm_i8(g, NB * (NB + 1), R, st)) return -1;
         } else {
             GemmParams q = gemm_params(Linv, NP, Linv, NP, fb.K, NP, NP / TILE, NP / TILE, NP, 1.0, 0.0);
             q.order = ORDER_LOWER;
@@ -814,8 +888,16 @@ static int fit_pipeline(const double* X, const double* y_n, int n, const tb200_k
             if (launch_gemm<true, false>(q, R, 1, st)) return -1;
         }
         const size_t sm = sizeof(double) * (2 * d * GT + 8 * p);
-        TB_LAUNCH(lml_grad_kernel, dim3(nt64, R), dim3(256), sm, st, XsT, n, NP, spec, theta, p, fb.K, alpha,
-                  fb.partial, nt64);
+#define TB_LML_GRAD(KIND)                                                                                     \
+    TB_LAUNCH(lml_grad_kernel<KIND>, dim3(nt64, R), dim3(256), sm, st, XsT, n, NP, spec, theta, p, fb.K, alpha, \
+              fb.partial, nt64)
+        switch (spec.kind) {
+            case TB200_RBF: TB_LML_GRAD(TB200_RBF); break;
+            case TB200_MATERN12: TB_LML_GRAD(TB200_MATERN12); break;
+            case TB200_MATERN32: TB_LML_GRAD(TB200_MATERN32); break;
+            default: TB_LML_GRAD(TB200_MATERN52); break;
+        }
+#undef TB_LML_GRAD
         TB_LAUNCH(lml_grad_reduce_kernel, dim3(R, p), dim3(256), 0, st, fb.partial, nt64, p, info, grad);
     }
     return 0;
