@@ -11,8 +11,10 @@ on a GP with n_train=4096, d=10, ARD Matern-5/2 + white noise at fixed hyper-par
   value     : candidates/s, candidates already resident in HBM (device-timed, max over ranks)
   e2e       : same metric through the plugin call acq.argmax_over(host candidates): pinned host
               buffer -> chunked H2D inside the timed region -> (value, index) read back
-  roofline  : the variance GEMM (DMMA) -- algorithmic n^2 flop per candidate / CUDA-event duration,
-              against the FP64 tensor peak measured on this device by tb200_fp64_peak
+  roofline  : the variance contraction V = L^-1 k* (n^2 flop per candidate).  Default engine: INT8 tensor cores
+              (tcgen05.mma kind::i8, exact byte-slice products) -- algorithmic INT8 ops / CUDA-event duration against
+              2 x the measured bf16 peak; --engine dmma: FP64 DMMA GEMM against the FP64 tensor peak measured on this
+              device by tb200_fp64_peak
   cpu_baseline : the oracle port (NumPy/SciPy, same LAPACK/BLAS calls as the reference's sklearn path)
               on a bounded sample of the same workload, rank 0, N=1 only
   fit       : GP fit ms -- one batched LML+gradient evaluation over R restarts (R split over ranks)
@@ -37,7 +39,7 @@ if ROOT not in sys.path:
 N_TRAIN, DIM = 4096, 10
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
 # `ncu --set full` captures under profiles/ (None until captured for that engine)
-TRAFFIC = {"dmma": 197.2e6, "i8": None, "i8x": None}
+TRAFFIC = {"dmma": 197.2e6, "i8": 163.9e6, "i8x": None}  # profiles/r1_gemm_ncu_full.md, r1_i8v2_ncu_full.md
 METRIC = "EI candidates/sec (n=4096,d=10)"
 
 
@@ -290,8 +292,9 @@ def run_ours(args):
         roofline = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s (INT8 tensor ops)",
                     "frac": achieved / peak, "traffic": TRAFFIC.get(engine),
                     "kernel": "i8::colsumsq_i8_kernel<%d> (tcgen05.mma kind::i8, %d byte-slice products of V = Linv * "
-                              "Kstar^T accumulated exactly in INT32 TMEM, FP64 sum-of-squares epilogue)"
-                              % (8 if engine == "i8" else 9, pairs),
+                              "Kstar^T accumulated exactly in INT32 TMEM, Linv slices stacked along N: %d MMAs per K=32 "
+                              "step, FP64 sum-of-squares epilogue)"
+                              % (8 if engine == "i8" else 9, pairs, 10 if engine == "i8" else 11),
                     "algorithmic_flop_per_launch": int8_ops, "launches_timed": g_n, "avg_launch_ms": avg_ms,
                     "gemm_share_of_step": g_ms / ms_serial, "timed_in": timed_in,
                     "fp64_equivalent_tflops": fp64_equiv, "fp64_dmma_peak_tflops": dmma_tf,
@@ -324,6 +327,8 @@ def run_ours(args):
     e1.record()
     torch.cuda.synchronize()
     fit = {"lml_grad_batched_ms": min(fit_ms[1:]), "restarts": R, "restarts_per_gpu": Rl,
+           "engine": "i8 (potrf column updates, trtri, K^-1 on tcgen05 kind::i8, 34 slice products) when the batch is "
+                     "large enough for the left-looking schedule, else FP64 DMMA; TB200_FIT_ENGINE=dmma forces DMMA",
            "flop_per_evaluation": float(n) ** 3 + float(n) ** 2 * (3 * d + 42),
            "tflops": Rl * (float(n) ** 3 + float(n) ** 2 * (3 * d + 42)) / (min(fit_ms[1:]) * 1e-3) / 1e12,
            "final_factor_ms": e0.elapsed_time(e1), "all_finite": bool(np.isfinite(lml).all())}
