@@ -29,8 +29,10 @@ import time
 
 import numpy as np
 
-if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-    os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
+# rank 0 prints ONE JSON line on stdout: NCCL's "NCCL version ..." banner (printed at VERSION and at WARN level) goes
+# to a file unless the caller asked for INFO/TRACE output explicitly
+if os.environ.get("NCCL_DEBUG", "VERSION").upper() in ("VERSION", "WARN"):
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/null")
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
