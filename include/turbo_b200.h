@@ -128,6 +128,23 @@ int tb200_generate_candidates(const tb200_cand_spec* cand_host, int d, int64_t i
  * runs register-resident DMMA.8x8x4 / DFMA loops on every SM for ~`ms` milliseconds each. */
 int tb200_fp64_peak(double ms, double* dmma_tflops_host, double* dfma_tflops_host);
 
+/* Per-epilogue-CTA running bests (value, global index; index -1 = unused) of the last tb200_acquire(_i8) call that
+ * used `work`: tb200_acquire_local_best_count(batch, n) distinct good candidates, the starting points of the gradient
+ * polish (the reference's `start_from_best` best random samples, auxiliary_optimisers.py:73-75). */
+int tb200_acquire_local_best_count(int64_t batch, int n);
+int tb200_acquire_local_bests(void* work, int n, int d, int64_t batch, int use_i8, double* vals_out, int64_t* idx_out,
+                              void* stream);
+
+/* Acquisition value and its gradient with respect to the point, for P <= 128 points per call: the
+ * analytic counterpart of the numerical gradients SciPy's L-BFGS-B takes of `-acq(x)` in
+ * turbo/modules/auxiliary_optimisers.py:84-93.  val_out[P], grad_out[P][d] (d a / d x in the caller's coordinates);
+ * mu_out / sigma_out optional.  FP64 DMMA path (V = Linv k*, w = Linv^T V). */
+size_t tb200_acquire_grad_workspace_bytes(int n, int d);
+int tb200_acquire_grad(const double* Xp, int P, const double* XsT, const double* Linv, const double* alpha, int n,
+                       const tb200_kernel_spec* spec_host, const double* theta, const tb200_acq_spec* acq_host,
+                       double* val_out, double* grad_out, double* mu_out, double* sigma_out, void* work,
+                       size_t work_bytes, void* stream);
+
 /* CUDA-event timing of the dominant kernel (the variance GEMM inside tb200_acquire), recorded on the
  * stream the kernel is launched on.  enable(1) starts collecting; read() synchronises, returns the
  * summed duration and the number of timed launches, and clears the record. */

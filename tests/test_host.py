@@ -137,6 +137,14 @@ def test_argmax_pair_reduction_rule():
     assert red([-np.inf], [4]) == (-np.inf, 4)                           # a real -inf value is selectable
 
 
+def test_merge_top_rule():
+    from turbo_b200 import dist
+    v, i = dist.merge_top([1.0, 3.0, 3.0, 2.0, np.nan, 9.0], [5, 9, 4, 6, 7, -1], 3)
+    assert v.tolist() == [3.0, 3.0, 2.0] and i.tolist() == [4, 9, 6]      # NaN and index -1 never enter
+    v, i = dist.merge_top([], [], 2)
+    assert len(v) == 0 and len(i) == 0
+
+
 def _gloo_worker(rank, world, port, q):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     import torch.distributed as td
@@ -161,6 +169,10 @@ def _gloo_worker(rank, world, port, q):
             out["all_failed"] = "no error"
         except np.linalg.LinAlgError:
             out["all_failed"] = "LinAlgError"
+        # polish starts: every rank contributes local top candidates, every rank gets the same global top-k
+        tv, ti = [([3.0, 1.0, 2.0], [40, 7, 9]), ([3.0, 2.5], [12, 900])][rank]
+        out["top"] = dist.allgather_top(np.array(tv), np.array(ti), 3, "world")
+        out["top_short"] = dist.allgather_top(np.array(tv[:rank]), np.array(ti[:rank]), 4, "world")
         q.put((rank, out))
     finally:
         td.destroy_process_group()
@@ -188,6 +200,8 @@ def test_world_size_2_reductions_over_gloo():
         theta, f = o["best_none_local"]
         assert f == 4.0 and np.array_equal(theta, [1.0, 2.0, 3.0])
         assert o["all_failed"] == "LinAlgError"
+        assert o["top"][0].tolist() == [3.0, 3.0, 2.5] and o["top"][1].tolist() == [12, 40, 900]
+        assert o["top_short"][0].tolist() == [3.0] and o["top_short"][1].tolist() == [12]
 
 
 def test_host_candidate_mirror_properties():

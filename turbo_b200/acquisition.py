@@ -39,8 +39,13 @@ class _DeviceFunction:
         a.run(device.to_device(X), m, 0, None, acq=out)
         return out.cpu().numpy()
 
+    def value_and_grad(self, X):
+        """acquisition values (P,) and analytic gradients (P,d) at host points X (tb200_acquire_grad): what the
+        L-BFGS-B stage of RandomAndQuasiNewton needs (auxiliary_optimisers.py:84-93 uses numerical gradients)"""
+        return device.acquisition_value_and_grad(self.model.factor, self._spec_c(), X)
+
     def argmax_over(self, candidates=None, generator=None, m=None, lo=None, hi=None, seed=0, group=None,
-                    chunk=1 << 18, batch=0, engine=None):
+                    chunk=1 << 18, batch=0, engine=None, keep_top=0):
         """argmax of the acquisition function over a candidate set.
 
         candidates: (m,d) host array (every rank passes the same full set when ``group`` is given), or
@@ -48,6 +53,8 @@ class _DeviceFunction:
                     from the global index, so the result does not depend on how ranks split the range.
         Returns (value, global index, x (1,d)); (-inf, -1, None) if no candidate is selectable.
         Ties keep the lowest index; NaN never wins (auxiliary_optimisers.py:63-66 picks argsort's first).
+        keep_top > 0: additionally returns (values, indices, X) of up to keep_top distinct good candidates, best
+        first (the winner, then per-CTA running bests merged over chunks and ranks) as a 4th element.
         """
         import torch
         from . import dist
@@ -70,6 +77,7 @@ class _DeviceFunction:
             copy_stream = torch.cuda.Stream()
             main = torch.cuda.current_stream()
             pending = None
+            tops = []
             for off in range(0, hi_i - lo_i, chunk):
                 cnt = min(chunk, hi_i - lo_i - off)
                 with torch.cuda.stream(copy_stream):
@@ -78,6 +86,8 @@ class _DeviceFunction:
                     ev.record(copy_stream)
                 main.wait_event(ev)
                 a.run(buf, cnt, lo_i + off, None)
+                if keep_top:
+                    tops.append(a.local_bests())
                 buf.record_stream(main)
                 pending = buf
             del pending
@@ -86,17 +96,28 @@ class _DeviceFunction:
             mode = {'uniform': _lib.CAND_UNIFORM, 'lhs': _lib.CAND_LHS}[generator]
             cand_c = _lib.cand_spec(mode, seed, m, lo, hi)
             lo_i, hi_i = dist.shard_range(m, rank, world)
+            tops = []
             if hi_i > lo_i:
                 a.run(None, hi_i - lo_i, lo_i, cand_c)
+                if keep_top:
+                    tops.append(a.local_bests())
         val, idx = a.best()
         val, idx = dist.allreduce_argmax(val, idx, group)
         if idx < 0:
-            return -math.inf, -1, None
-        if candidates is not None:
-            x = X[idx:idx + 1].copy()
-        else:
-            x = _lib.host_candidates(cand_c.mode, seed, m, lo, hi, [idx])
-        return val, idx, x
+            return (-math.inf, -1, None, None) if keep_top else (-math.inf, -1, None)
+
+        def rows(ids):
+            if candidates is not None:
+                return X[np.asarray(ids, dtype=np.int64)].copy()
+            return _lib.host_candidates(cand_c.mode, seed, m, lo, hi, [int(i) for i in ids])
+
+        x = rows([idx])
+        if not keep_top:
+            return val, idx, x
+        tv = np.concatenate([t[0] for t in tops]) if tops else np.zeros(0)
+        ti = np.concatenate([t[1] for t in tops]) if tops else np.zeros(0, dtype=np.int64)
+        tv, ti = dist.allgather_top(tv, ti, keep_top, group)
+        return val, idx, x, (tv, ti, rows(ti))
 
 
 class GpuUCB(UCB):

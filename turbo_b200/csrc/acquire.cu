@@ -445,6 +445,112 @@ __global__ void __launch_bounds__(EPI_THREADS) acquire_epilogue_kernel(
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// acquisition value AND gradient w.r.t. the point (analytic replacement for the numerical
+// gradients of the L-BFGS-B stage of auxiliary_optimisers.py:69-112).  One CTA per point p:
+//   dk_j/dx = -sf2 h(r2_j) (x/l - x_j/l) / l          (h = shape_grad_fn, dK/dlog l_k = sf2 h D_k)
+//   dmu/dx  = y_std sum_j alpha_j dk_j/dx,   dvar_n/dx = -2 sum_j w_j dk_j/dx,  w = Linv^T (Linv k*)
+// written as xs*SA - sum_j A_j xs_j with A_j = alpha_j sf2 h_j (B_j = w_j sf2 h_j) so that no thread keeps
+// per-dimension accumulators.  V = Linv K*^T and W = Linv^T V come from the DMMA GEMM (NP x 128, ld 128).
+// ---------------------------------------------------------------------------------------------
+constexpr int GRAD_PMAX = 128;  // points per call (one GEMM column tile)
+
+__global__ void __launch_bounds__(256) acq_grad_kernel(
+    const double* __restrict__ Xp, int P, const double* __restrict__ XsT, int n, int NP, tb200_kernel_spec spec,
+    const double* __restrict__ theta, const double* __restrict__ alpha, const double* __restrict__ mean, int nsplit,
+    long mean_stride, const double* __restrict__ V, const double* __restrict__ W, double* __restrict__ Ag,
+    double* __restrict__ Bg, tb200_acq_spec acq, double* __restrict__ val_out, double* __restrict__ grad_out,
+    double* __restrict__ mu_out, double* __restrict__ sigma_out) {
+    extern __shared__ double sh[];  // xs[d], red[4][8], res[8], dsum[2][d]
+    const int d = spec.d, p = blockIdx.x;
+    double* xs = sh;
+    double* red = sh + d;
+    double* res = red + 32;
+    double* dsum = res + 8;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int k = threadIdx.x; k < d; k += blockDim.x) xs[k] = Xp[(long)p * d + k] / length_scale(spec, theta, k);
+    __syncthreads();
+    const Hyper hy = unpack_hyper(spec, theta);
+    double vv = 0.0, sa = 0.0, sb = 0.0;
+    for (int j = threadIdx.x; j < NP; j += blockDim.x) {
+        const double v = V[(long)j * GRAD_PMAX + p];
+        vv = fma(v, v, vv);
+        double r2 = 0.0;
+        for (int k = 0; k < d; ++k) {
+            const double df = xs[k] - XsT[(long)k * NP + j];
+            r2 += df * df;
+        }
+        const double h = (j < n) ? hy.sf2 * shape_grad_fn(spec.kind, r2) : 0.0;
+        const double a = alpha[j] * h, b = W[(long)j * GRAD_PMAX + p] * h;
+        Ag[(long)p * NP + j] = a;
+        Bg[(long)p * NP + j] = b;
+        sa += a;
+        sb += b;
+    }
+    vv = warp_sum(vv); sa = warp_sum(sa); sb = warp_sum(sb);
+    if (lane == 0) { red[warp] = vv; red[8 + warp] = sa; red[16 + warp] = sb; }
+    __syncthreads();  // also orders this CTA's Ag/Bg writes before the reads below
+    if (threadIdx.x == 0) {
+        double t0 = 0.0, t1 = 0.0, t2 = 0.0;
+        for (int w = 0; w < 8; ++w) { t0 += red[w]; t1 += red[8 + w]; t2 += red[16 + w]; }
+        double ms = 0.0;
+        for (int t = 0; t < nsplit; ++t) ms += mean[(long)t * mean_stride + p];
+        res[0] = t0; res[1] = t1; res[2] = t2; res[3] = ms;
+    }
+    __syncthreads();
+    // per-dimension dot products sum_j A_j xs_j[k], sum_j B_j xs_j[k]: one warp per dimension (strided)
+    for (int k = warp; k < d; k += 8) {
+        double da = 0.0, db = 0.0;
+        for (int j = lane; j < NP; j += 32) {
+            const double xt = XsT[(long)k * NP + j];
+            da = fma(Ag[(long)p * NP + j], xt, da);
+            db = fma(Bg[(long)p * NP + j], xt, db);
+        }
+        da = warp_sum(da); db = warp_sum(db);
+        if (lane == 0) { dsum[k] = da; dsum[d + k] = db; }
+    }
+    __syncthreads();
+    const double prior_var = hy.sf2 + hy.noise;
+    double var = prior_var - res[0];
+    const bool clamped = var <= 0.0;
+    if (var < 0.0) var = 0.0;
+    var *= acq.y_std * acq.y_std;
+    const double sigma = sqrt(var);
+    const double mu = acq.y_std * res[3] + acq.y_mean;
+    double a, cm, cs;  // value, d a / d mu, d a / d sigma
+    if (acq.acq == TB200_UCB) {
+        if (isinf(acq.param)) { a = sigma; cm = 0.0; cs = 1.0; }
+        else { a = acq.sign * mu + acq.param * sigma; cm = acq.sign; cs = acq.param; }
+    } else if (sigma != 0.0) {
+        const double diff = acq.sign * (mu - acq.incumbent) - acq.param;
+        const double Z = diff / sigma;
+        if (acq.acq == TB200_PI) {
+            a = norm_cdf(Z);
+            cm = norm_pdf(Z) * acq.sign / sigma;
+            cs = -norm_pdf(Z) * diff / (sigma * sigma);
+        } else {
+            a = diff * norm_cdf(Z) + sigma * norm_pdf(Z);
+            cm = norm_cdf(Z) * acq.sign;  // dEI/dmu = s Phi(Z), dEI/dsigma = phi(Z)
+            cs = norm_pdf(Z);
+        }
+    } else {
+        a = 0.0; cm = 0.0; cs = 0.0;
+    }
+    if (threadIdx.x == 0) {
+        val_out[p] = a;
+        if (mu_out) mu_out[p] = mu;
+        if (sigma_out) sigma_out[p] = sigma;
+    }
+    for (int k = threadIdx.x; k < d; k += blockDim.x) {
+        const double il = 1.0 / length_scale(spec, theta, k);
+        const double dm = -(xs[k] * res[1] - dsum[k]) * il;              // d(mean_n)/dx_k
+        const double dvn = 2.0 * (xs[k] * res[2] - dsum[d + k]) * il;     // d(var_n)/dx_k
+        const double dmu = acq.y_std * dm;
+        const double dsig = (clamped || sigma == 0.0) ? 0.0 : acq.y_std * acq.y_std * dvn / (2.0 * sigma);
+        grad_out[(long)p * d + k] = cm * dmu + cs * dsig;
+    }
+}
+
 __global__ void best_reset_kernel(double* best_val, int64_t* best_idx, int count) {
     for (int i = threadIdx.x; i < count; i += blockDim.x) {
         best_val[i] = -INFINITY;
@@ -900,6 +1006,74 @@ int tb200_i8_prepare(const double* Linv, int n, const tb200_kernel_spec* spec, c
     const long total = (long)NP * (NP / 16);
     TB_LAUNCH(linv_slice_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, st, Linv, NP, rowscale, linvS,
               (long)NP * NP);
+    return 0;
+}
+
+// the per-epilogue-CTA running bests of the LAST tb200_acquire(_i8) call on `work` (entry e covers the candidates
+// whose position within their batch is in [128 e', 128 e'+128) of one buffer slot): distinct good candidates, used as
+// starting points of the gradient polish (the reference takes the best `start_from_best` random samples,
+// auxiliary_optimisers.py:73-75).  Unused entries have index -1.
+int tb200_acquire_local_best_count(int64_t batch, int n) {
+    if (batch <= 0) batch = tb200_default_batch(n);
+    return (int)(ACQ_SLOTS * (batch / EPI_THREADS));
+}
+
+int tb200_acquire_local_bests(void* work, int n, int d, int64_t batch, int use_i8, double* vals_out, int64_t* idx_out,
+                              void* stream) {
+    TB_CHECK(work && vals_out && idx_out, "NULL pointer argument");
+    if (batch <= 0) batch = tb200_default_batch(n);
+    AcqBuffers ab[ACQ_SLOTS];
+    acquire_layout(n, d, batch, ab, (char*)work, use_i8 != 0);
+    const size_t cnt = (size_t)ACQ_SLOTS * (batch / EPI_THREADS);
+    TB_CUDA(cudaMemcpyAsync(vals_out, ab[0].best_val, sizeof(double) * cnt, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    TB_CUDA(cudaMemcpyAsync(idx_out, ab[0].best_idx, sizeof(int64_t) * cnt, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return 0;
+}
+
+size_t tb200_acquire_grad_workspace_bytes(int n, int d) {
+    (void)d;
+    const size_t NP = pad_n(n);
+    return a256(sizeof(double) * GRAD_PMAX * NP) * 5 + a256(sizeof(double) * KSPLIT_MAX * GRAD_PMAX);
+}
+
+int tb200_acquire_grad(const double* Xp, int P, const double* XsT, const double* Linv, const double* alpha, int n,
+                       const tb200_kernel_spec* spec, const double* theta, const tb200_acq_spec* acq, double* val_out,
+                       double* grad_out, double* mu_out, double* sigma_out, void* work, size_t work_bytes, void* stream) {
+    TB_CHECK(Xp && XsT && Linv && alpha && spec && theta && acq && val_out && grad_out && work, "NULL pointer argument");
+    TB_CHECK(spec->kind >= TB200_RBF && spec->kind <= TB200_MATERN52, "unknown kernel kind");
+    TB_CHECK(spec->d >= 1 && spec->d <= TB200_MAX_D, "d out of range (1..64)");
+    TB_CHECK(acq->acq >= TB200_EI && acq->acq <= TB200_UCB, "unknown acquisition function");
+    TB_CHECK(P >= 0 && P <= GRAD_PMAX, "at most 128 points per call");
+    if (P == 0) return 0;
+    TB_CHECK(work_bytes >= tb200_acquire_grad_workspace_bytes(n, spec->d), "workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int NP = pad_n(n), NB = NP / TILE, d = spec->d;
+    char* base = (char*)work;
+    const size_t mat = a256(sizeof(double) * GRAD_PMAX * NP);
+    double* Ks = (double*)base;
+    double* V = (double*)(base + mat);
+    double* W = (double*)(base + 2 * mat);
+    double* Ag = (double*)(base + 3 * mat);
+    double* Bg = (double*)(base + 4 * mat);
+    double* mean = (double*)(base + 5 * mat);
+    // K* rows + mean partials of the (padded) 128 points
+    const size_t ksm = sizeof(double) * (CPB * d + 8 * CPB);
+    int ksplit = NB < KSPLIT_MAX ? NB : KSPLIT_MAX;
+    const int jchunk = (NB + ksplit - 1) / ksplit * TILE;
+    ksplit = (NP + jchunk - 1) / jchunk;
+    TB_LAUNCH(kstar_mean_kernel, dim3(GRAD_PMAX / CPB, ksplit), dim3(256), ksm, st, Xp, (int64_t)P, XsT, n, NP, *spec, theta,
+              alpha, Ks, mean, jchunk, (long)GRAD_PMAX);
+    // V = Linv Ks^T (NP x 128), W = Linv^T V
+    GemmParams g1 = gemm_params(Linv, NP, Ks, NP, V, GRAD_PMAX, NB, 1, NP, 1.0, 0.0);
+    g1.khi_mode = KHI_BY_TI;
+    g1.a_tri_diag = 1;
+    if (launch_gemm<false, true>(g1, 1, 1, st)) return -1;
+    GemmParams g2 = gemm_params(Linv, NP, V, GRAD_PMAX, W, GRAD_PMAX, NB, 1, NP, 1.0, 0.0);
+    g2.klo_mode = KLO_BY_TI;
+    if (launch_gemm<true, false>(g2, 1, 1, st)) return -1;
+    const size_t gsm = sizeof(double) * (d + 32 + 8 + 2 * d);
+    TB_LAUNCH(acq_grad_kernel, dim3(P), dim3(256), gsm, st, Xp, P, XsT, n, NP, *spec, theta, alpha, mean, ksplit,
+              (long)GRAD_PMAX, V, W, Ag, Bg, *acq, val_out, grad_out, mu_out, sigma_out);
     return 0;
 }
 

@@ -167,6 +167,46 @@ class Acquirer:
         """(value, global index); index -1 when nothing was selectable (all NaN / empty)"""
         return float(self.best_val.item()), int(self.best_idx.item())
 
+    def local_bests(self):
+        """(values, global indices) of the per-CTA running bests of the LAST run() call (tb200_acquire_local_bests):
+        distinct good candidates, index >= 0 only, best first (ties: lowest index)."""
+        cnt = int(self.lib.tb200_acquire_local_best_count(self.batch, self.f.n))
+        dev = device()
+        v = torch.empty(cnt, dtype=torch.float64, device=dev)
+        i = torch.empty(cnt, dtype=torch.int64, device=dev)
+        _lib.check(self.lib.tb200_acquire_local_bests(_lib.ptr(self.work), self.f.n, self.f.spec.d, self.batch,
+                                                      int(self.engine != "dmma"), _lib.ptr(v), _lib.ptr(i),
+                                                      _lib.stream_ptr()))
+        v, i = v.cpu().numpy(), i.cpu().numpy()
+        keep = (i >= 0) & ~np.isnan(v)
+        v, i = v[keep], i[keep]
+        order = np.lexsort((i, -v))
+        return v[order], i[order]
+
+
+def acquisition_value_and_grad(factor, acq_c, X):
+    """acquisition value (P,) and gradient (P,d) at host points X through tb200_acquire_grad (128 points per call)"""
+    lib = _lib.load()
+    X = np.ascontiguousarray(np.atleast_2d(X), dtype=np.float64)
+    P, d = X.shape
+    assert d == factor.spec.d
+    dev = device()
+    Xd = torch.from_numpy(X).to(dev)
+    val = torch.empty(P, dtype=torch.float64, device=dev)
+    grad = torch.empty((P, d), dtype=torch.float64, device=dev)
+    nbytes = lib.tb200_acquire_grad_workspace_bytes(factor.n, d)
+    work = _workspace(nbytes)
+    cs = factor.spec.to_c()
+    for off in range(0, P, 128):
+        cnt = min(128, P - off)
+        _lib.check(lib.tb200_acquire_grad(_lib.ptr(Xd[off:]), cnt, _lib.ptr(factor.XsT), _lib.ptr(factor.Linv),
+                                          _lib.ptr(factor.alpha), factor.n, C.byref(cs), _lib.ptr(factor.theta),
+                                          C.byref(acq_c), _lib.ptr(val[off:]), _lib.ptr(grad[off:]), None, None,
+                                          _lib.ptr(work), nbytes, _lib.stream_ptr()))
+    out = val.cpu().numpy(), grad.cpu().numpy()
+    del work
+    return out
+
 
 def acq_spec(acq, sign, incumbent, param, y_mean, y_std):
     return _lib.AcqSpecC(int(acq), float(sign), float(incumbent), float(param), float(y_mean), float(y_std))

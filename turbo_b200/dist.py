@@ -71,6 +71,36 @@ def allreduce_argmax(value, index, group=None):
     return reduce_argmax_pairs(vals, pairs[:, 1])
 
 
+def merge_top(values, indices, k):
+    """pure rule: the k best distinct (value, index) pairs, best first, ties -> lowest index"""
+    values, indices = np.asarray(values, dtype=np.float64), np.asarray(indices, dtype=np.int64)
+    keep = (indices >= 0) & ~np.isnan(values)
+    values, indices = values[keep], indices[keep]
+    indices, first = np.unique(indices, return_index=True)
+    values = values[first]
+    order = np.lexsort((indices, -values))[:k]
+    return values[order], indices[order]
+
+
+def allgather_top(values, indices, k, group=None):
+    """every rank contributes its local top candidates; every rank returns the same global top-k"""
+    values, indices = merge_top(values, indices, k)
+    if group is None:
+        return values, indices
+    import torch
+    td = _dist()
+    g = None if group == 'world' else group
+    world = td.get_world_size(g)
+    dev = _comm_device(group)
+    mine = np.full((k, 2), -1, dtype=np.int64)
+    mine[:len(indices), 0] = values.view(np.int64)
+    mine[:len(indices), 1] = indices
+    out = torch.empty(2 * k * world, dtype=torch.int64, device=dev)
+    td.all_gather_into_tensor(out, torch.from_numpy(mine.reshape(-1)).to(dev), group=g)
+    pairs = out.cpu().numpy().reshape(world * k, 2)
+    return merge_top(pairs[:, 0].copy().view(np.float64), pairs[:, 1], k)
+
+
 def select_best_restart(thetas, neg_lmls, p, group):
     """each rank contributes its best local restart; every rank returns the global (theta, -lml).
     Ties -> lowest rank.  Raises LinAlgError if no rank has a finite restart."""
