@@ -484,9 +484,9 @@ __global__ void colscale_kernel(const double* __restrict__ X, int NP, double* __
 
 // column maxima of |M[r, c] * kmul(r)| for columns [col0, col0+128) over rows [row0, NP), kept as the bit pattern of a
 // non-negative double (order-preserving as an integer, so atomicMax works); `out` must be zero beforehand.
-// kmax != NULL: row r is weighted by the power-of-two cover of kmax[r] (the X column scale t_r of the trtri recurrence).
+// kscale != NULL: row r is weighted by kscale[r] (the X column scale t_r of the trtri recurrence).
 __global__ void __launch_bounds__(128) colmax_bits_kernel(const double* __restrict__ M, int NP, long mStride, int col0,
-                                                          int row0, const unsigned long long* __restrict__ kmax,
+                                                          int row0, const double* __restrict__ kscale,
                                                           unsigned long long* __restrict__ out) {
     const int rs = blockIdx.y, c = col0 + threadIdx.x;
     const int r_lo = row0 + blockIdx.x * 128, r_hi = min(NP, r_lo + 128);
@@ -494,10 +494,17 @@ __global__ void __launch_bounds__(128) colmax_bits_kernel(const double* __restri
     double m = 0.0;
     for (int r = r_lo; r < r_hi; ++r) {
         double v = fabs(x[(size_t)r * NP]);
-        if (kmax) v *= pow2_cover(__longlong_as_double((long long)kmax[(size_t)rs * NP + r]));
+        if (kscale) v *= kscale[(size_t)rs * NP + r];
         if (v > m) m = v;  // NaN never enters
     }
     if (m > 0.0) atomicMax(out + (size_t)rs * NP + c, (unsigned long long)__double_as_longlong(m));
+}
+
+// power-of-two covers of 128 column maxima: out[c] = 2^e with 0.98 * 2^e >= max (1 for an all-zero column)
+__global__ void __launch_bounds__(128) cover_kernel(const unsigned long long* __restrict__ bits, int NP, int col0,
+                                                    double* __restrict__ out) {
+    const size_t e = (size_t)blockIdx.x * NP + col0 + threadIdx.x;
+    out[e] = pow2_cover(__longlong_as_double((long long)bits[e]));
 }
 
 // One warp = one (8 operand rows) x (64 of K) piece = 4 core matrices per slice, written as 128 contiguous bytes
@@ -505,17 +512,16 @@ __global__ void __launch_bounds__(128) colmax_bits_kernel(const double* __restri
 // TRANSPOSED = true: operand row = matrix column, K = matrix row (columns of L^-1, columns of an L panel).
 // Pieces are enumerated over operand row groups [rg0, rg1) x k-blocks [kb0, kb1); with `lower` set, pieces whose
 // k-block lies entirely before the 128-row block of the operand rows are skipped (never read by the tri GEMM).
-// Operand-row scale: `scale` (doubles) or the cover of `opmax` (bits) or 1.  K-index weight: kmode 1 multiplies by the
-// cover of kmax[k], kmode 2 divides by it (both exact: powers of two).  tileRow0: operand row of tile 0 of `out`
-// (a panel buffer holds only its own two 64-row tiles).  scale_out (optional): the operand-row scale as a double.
+// Operand-row scale: `scale` (power-of-two doubles) or 1.  K-index weight: kmode 1 multiplies by kscale[k], kmode 2
+// divides by it (both exact: powers of two).  tileRow0: operand row of tile 0 of `out` (a panel buffer holds only its
+// own two 64-row tiles).
 template <bool TRANSPOSED>
 __global__ void __launch_bounds__(256) slice_operand_kernel(const double* __restrict__ M, int NP, long mStride,
                                                             const double* __restrict__ scale,
-                                                            const unsigned long long* __restrict__ opmax,
-                                                            const unsigned long long* __restrict__ kmax, int kmode,
+                                                            const double* __restrict__ kscale, int kmode,
                                                             int rg0, int rg1, int kb0, int kb1, int lower, int tileRow0,
                                                             uint8_t* __restrict__ out, long sliceStride,
-                                                            long restartStride, int kblks, double* __restrict__ scale_out) {
+                                                            long restartStride, int kblks) {
     const int lane = threadIdx.x & 31;
     const long piece = (long)blockIdx.x * 8 + (threadIdx.x >> 5);
     const int nkb = kb1 - kb0;
@@ -526,19 +532,25 @@ __global__ void __launch_bounds__(256) slice_operand_kernel(const double* __rest
     const int orow = rg * 8 + (lane & 7);       // operand row
     const int k0 = kb * 64 + (lane >> 3) * 16;  // first of this lane's 16 K indices
     const double* src = M + (size_t)rs * mStride;
-    double osc = 1.0;
-    if (scale) osc = scale[(size_t)rs * NP + orow];
-    else if (opmax) osc = pow2_cover(__longlong_as_double((long long)opmax[(size_t)rs * NP + orow]));
-    if (scale_out && kb == kb0 && (lane >> 3) == 0) scale_out[(size_t)rs * NP + orow] = osc;
-    const double inv = 1.0 / osc;  // exact: power of two
+    const double inv = scale ? 1.0 / scale[(size_t)rs * NP + orow] : 1.0;  // exact: power of two
+    double kw[16];
+    if (kmode) {
+        const double4* kp = reinterpret_cast<const double4*>(kscale + (size_t)rs * NP + k0);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const double4 t = kp[q];
+            kw[4 * q] = t.x; kw[4 * q + 1] = t.y; kw[4 * q + 2] = t.z; kw[4 * q + 3] = t.w;
+        }
+        if (kmode == 2) {
+#pragma unroll
+            for (int q = 0; q < 16; ++q) kw[q] = 1.0 / kw[q];  // exact
+        }
+    }
     __align__(16) uint8_t bytes[i8::S][16];
 #pragma unroll
     for (int q = 0; q < 16; ++q) {
         double v = TRANSPOSED ? src[(size_t)(k0 + q) * NP + orow] : src[(size_t)orow * NP + k0 + q];
-        if (kmode) {
-            const double t = pow2_cover(__longlong_as_double((long long)kmax[(size_t)rs * NP + k0 + q]));
-            v = (kmode == 1) ? v * t : v / t;
-        }
+        if (kmode) v *= kw[q];
         uint8_t u[i8::S];
         fit_slice_signed(v * inv, u);
 #pragma unroll
@@ -672,6 +684,30 @@ static int launch_panel(const FitBuffers& fb, int NP, int R, int k, cudaStream_t
     return launch_gemm<false, true>(p, R, 1, st);
 }
 
+// high-priority side stream of the batched fit (look-ahead of the diagonal block), one per device
+struct FitStreams {
+    bool ready = false;
+    cudaStream_t side;
+    cudaEvent_t fork, join;
+};
+static FitStreams g_fit_streams[64];
+static int fit_streams_for_device(FitStreams** out) {
+    int dev = 0;
+    TB_CUDA(cudaGetDevice(&dev));
+    TB_CHECK(dev >= 0 && dev < 64, "device ordinal out of range");
+    FitStreams& f = g_fit_streams[dev];
+    if (!f.ready) {
+        int lo = 0, hi = 0;
+        TB_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        TB_CUDA(cudaStreamCreateWithPriority(&f.side, cudaStreamNonBlocking, hi));
+        TB_CUDA(cudaEventCreateWithFlags(&f.fork, cudaEventDisableTiming));
+        TB_CUDA(cudaEventCreateWithFlags(&f.join, cudaEventDisableTiming));
+        f.ready = true;
+    }
+    *out = &f;
+    return 0;
+}
+
 // blocked Cholesky of R matrices in fb.K (lower), Dinv blocks kept for trtri
 static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStream_t st) {
     const int NB = NP / TILE;
@@ -681,8 +717,11 @@ static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStr
     if (i8fit)
         TB_LAUNCH(rowscale_from_diag_kernel, dim3((NP + 255) / 256, R), dim3(256), 0, st, fb.K, NP, fb.scale);
     for (int k = 0; k < NB; ++k) {
+        bool diag_done = false;
         if (i8fit && k > 0) {
-            // same block-column update on the INT8 tensor cores: rows of L are already sliced up to column k*128
+            // same block-column update on the INT8 tensor cores: rows of L are already sliced up to column k*128.
+            // Look-ahead: the diagonal tile's update and its 128x128 factorisation (a latency-bound 64-CTA kernel) run
+            // on a high-priority side stream while the main stream updates the rows below.
             i8::GemmI8Params g{};
             g.S = fb.sliced; g.restartStride = (long)i8::S * sK; g.sliceStride = sK;
             g.scale = fb.scale; g.scaleStride = NP;
@@ -690,7 +729,20 @@ static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStr
             g.kblks = NP / i8::KB; g.tri = 0;
             g.rowTile0 = k; g.colTile0 = 2 * k; g.nColTiles = 2; g.kbLo = 0; g.kbHi = 2 * k;
             g.alpha = -1.0; g.beta = 1.0;
-            if (launch_fit_gemm_i8(g, (NB - k) * 2, R, st)) return -1;
+            FitStreams* fs = nullptr;
+            if (NB - k > 1 && !fit_streams_for_device(&fs)) {
+                TB_CUDA(cudaEventRecord(fs->fork, st));
+                TB_CUDA(cudaStreamWaitEvent(fs->side, fs->fork, 0));
+                if (launch_fit_gemm_i8(g, 2, R, fs->side)) return -1;           // diagonal tile (it = k)
+                if (launch_diag(fb, NP, R, k, info, fs->side)) return -1;
+                TB_CUDA(cudaEventRecord(fs->join, fs->side));
+                g.rowTile0 = k + 1;
+                if (launch_fit_gemm_i8(g, (NB - k - 1) * 2, R, st)) return -1;  // rows below
+                TB_CUDA(cudaStreamWaitEvent(st, fs->join, 0));
+                diag_done = true;
+            } else {
+                if (launch_fit_gemm_i8(g, (NB - k) * 2, R, st)) return -1;
+            }
         } else if (left && k > 0) {
             // block column k: A[i,k] -= L[i,0:k] L[k,0:k]^T  (i >= k), K = k*128 accumulated in registers
             const double* rows = fb.K + (long)k * TILE * NP;
@@ -699,7 +751,7 @@ static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStr
             p.sA1 = sK; p.sB1 = sK; p.sC1 = sK;
             if (launch_gemm<false, true>(p, R, 1, st)) return -1;
         }
-        if (launch_diag(fb, NP, R, k, info, st)) return -1;
+        if (!diag_done && launch_diag(fb, NP, R, k, info, st)) return -1;
         const int rem = NB - k - 1;
         if (rem == 0) break;
         if (launch_panel(fb, NP, R, k, st)) return -1;
@@ -708,8 +760,8 @@ static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStr
             const int rg0 = (k + 1) * (TILE / 8), rg1 = NP / 8;
             const long pieces = (long)(rg1 - rg0) * 2;
             TB_LAUNCH(slice_operand_kernel<false>, dim3((unsigned)((pieces + 7) / 8), R), dim3(256), 0, st, fb.K, NP, sK,
-                      fb.scale, (const unsigned long long*)nullptr, (const unsigned long long*)nullptr, 0, rg0, rg1, 2 * k,
-                      2 * k + 2, 0, 0, fb.sliced, sK, (long)i8::S * sK, NP / i8::KB, (double*)nullptr);
+                      fb.scale, (const double*)nullptr, 0, rg0, rg1, 2 * k, 2 * k + 2, 0, 0, fb.sliced, sK,
+                      (long)i8::S * sK, NP / i8::KB);
         }
         if (!left) {
             // trailing: A[i,j] -= A[i,k] A[j,k]^T  (k < j <= i)
@@ -750,27 +802,30 @@ static int trtri_batched_i8(const FitBuffers& fb, double* Linv, int NP, int R, c
     TB_LAUNCH(place_diag_blocks_kernel, dim3(NB, R), dim3(256), 0, st, fb.Dinv, sD, Linv, NP);
     TB_CUDA(cudaMemsetAsync(fb.tmax, 0, sizeof(double) * (size_t)R * NP, st));
     TB_CUDA(cudaMemsetAsync(fb.smax, 0, sizeof(double) * (size_t)R * NP, st));
-    const unsigned long long* none = nullptr;
+    const double* none = nullptr;
+    double* tsc = fb.scale;  // column scales t_k of X as doubles (fb.scale is free between potrf and the K^-1 step)
     for (int c = NB - 2; c >= 0; --c) {
         const int c1 = c + 1, rem = NB - c1;
         // column scales of the finished block column c1 of X, then its byte slices (rows >= c1*128, k-blocks 2c1, 2c1+1)
         TB_LAUNCH(colmax_bits_kernel, dim3(rem, R), dim3(128), 0, st, Linv, NP, sK, c1 * TILE, c1 * TILE, none, fb.tmax);
+        TB_LAUNCH(cover_kernel, dim3(R), dim3(128), 0, st, fb.tmax, NP, c1 * TILE, tsc);
         {
             const int rg0 = c1 * (TILE / 8), rg1 = NP / 8;
             const long pieces = (long)(rg1 - rg0) * 2;
             TB_LAUNCH(slice_operand_kernel<false>, dim3((unsigned)((pieces + 7) / 8), R), dim3(256), 0, st, Linv, NP, sK,
-                      (const double*)nullptr, none, (const unsigned long long*)fb.tmax, 2, rg0, rg1, 2 * c1, 2 * c1 + 2, 0,
-                      0, fb.sliced, sK, (long)i8::S * sK, kblks, (double*)nullptr);
+                      none, (const double*)tsc, 2, rg0, rg1, 2 * c1, 2 * c1 + 2, 0, 0, fb.sliced, sK, (long)i8::S * sK,
+                      kblks);
         }
         // weighted panel L[k, c-block] * t_k (k >= c1*128): column scales, then transposed byte slices
         TB_LAUNCH(colmax_bits_kernel, dim3(rem, R), dim3(128), 0, st, fb.K, NP, sK, c * TILE, c1 * TILE,
-                  (const unsigned long long*)fb.tmax, fb.smax);
+                  (const double*)tsc, fb.smax);
+        TB_LAUNCH(cover_kernel, dim3(R), dim3(128), 0, st, fb.smax, NP, c * TILE, fb.sigma);
         {
             const int rg0 = c * (TILE / 8), rg1 = rg0 + TILE / 8;
             const long pieces = (long)(rg1 - rg0) * (kblks - 2 * c1);
             TB_LAUNCH(slice_operand_kernel<true>, dim3((unsigned)((pieces + 7) / 8), R), dim3(256), 0, st, fb.K, NP, sK,
-                      (const double*)nullptr, (const unsigned long long*)fb.smax, (const unsigned long long*)fb.tmax, 1, rg0,
-                      rg1, 2 * c1, kblks, 0, c * TILE, fb.bpanel, bSlice, bRestart, kblks, fb.sigma);
+                      (const double*)fb.sigma, (const double*)tsc, 1, rg0, rg1, 2 * c1, kblks, 0, c * TILE, fb.bpanel,
+                      bSlice, bRestart, kblks);
         }
         // T[i, c-block] = -sum_k (X[i,k]/t_k) (L[k,c] t_k), rows of block rows c1.., k-blocks [2c1, 2(it+1))
         {
@@ -871,8 +926,8 @@ static int fit_pipeline(const double* X, const double* y_n, int n, const tb200_k
             TB_LAUNCH(colscale_kernel, dim3((NP + 127) / 128, R), dim3(128), 0, st, Linv, NP, fb.scale);
             const long pieces = (long)(NP / 8) * (NP / i8::KB);
             TB_LAUNCH(slice_operand_kernel<true>, dim3((unsigned)((pieces + 7) / 8), R), dim3(256), 0, st, Linv, NP, sK,
-                      fb.scale, (const unsigned long long*)nullptr, (const unsigned long long*)nullptr, 0, 0, NP / 8, 0,
-                      NP / i8::KB, 1, 0, fb.sliced, sK, (long)i8::S * sK, NP / i8::KB, (double*)nullptr);
+                      fb.scale, (const double*)nullptr, 0, 0, NP / 8, 0, NP / i8::KB, 1, 0, fb.sliced, sK,
+                      (long)i8::S * sK, NP / i8::KB);
             i8::GemmI8Params g{};
             g.S = fb.sliced; g.restartStride = (long)i8::S * sK; g.sliceStride = sK;
             g.scale = fb.scale; g.scaleStride = NP;
