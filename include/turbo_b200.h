@@ -128,6 +128,19 @@ int tb200_generate_candidates(const tb200_cand_spec* cand_host, int d, int64_t i
  * runs register-resident DMMA.8x8x4 / DFMA loops on every SM for ~`ms` milliseconds each. */
 int tb200_fp64_peak(double ms, double* dmma_tflops_host, double* dfma_tflops_host);
 
+/* Incremental refit at fixed hyper-parameters (the reference's `training_iterations` callable returning 0,
+ * turbo/modules/surrogates.py:250-269, :306-310): append ONE training point to the factor in O(n^2).
+ * tb200_factor_append overwrites the padded row n_old of Linv, column n_old of XsT and Ldiag[n_old]; it needs
+ * n_old < tb200_padded_n(n_old) (otherwise rebuild with tb200_factor).  info: 0, or n_old+1 if the new pivot is not
+ * positive (nothing is modified then).  tb200_alpha_lml recomputes alpha = K^-1 y and the log-marginal likelihood
+ * (sklearn:_gpr.py:613-617) for a (re-normalised) target vector from Linv and diag(L). */
+size_t tb200_append_workspace_bytes(int n);
+int tb200_factor_append(const double* x_new, double* XsT, double* Linv, double* Ldiag, int n_old,
+                        const tb200_kernel_spec* spec_host, const double* theta, double jitter, int* info, void* work,
+                        size_t work_bytes, void* stream);
+int tb200_alpha_lml(const double* y_n, int n, const double* Linv, const double* Ldiag, double* alpha, double* lml,
+                    void* work, size_t work_bytes, void* stream);
+
 /* Per-epilogue-CTA running bests (value, global index; index -1 = unused) of the last tb200_acquire(_i8) call that
  * used `work`: tb200_acquire_local_best_count(batch, n) distinct good candidates, the starting points of the gradient
  * polish (the reference's `start_from_best` best random samples, auxiliary_optimisers.py:73-75). */

@@ -270,3 +270,47 @@ def test_gradient_polish_improves_on_random_stage():
     assert info['max_acq'] >= info['random_stage_max_acq']
     assert acq(x)[0] == pytest.approx(info['max_acq'], rel=1e-8, abs=1e-12)
     assert info['polish_starts'] == 6 and info['polish_evaluations'] >= 1
+
+
+def test_incremental_refit_equals_full_refactorisation():
+    """SURVEY 8f-2: trials that append rows at fixed hyper-parameters extend the previous factor (tb200_factor_append);
+    predictions, LML and the selected candidate equal those of a model factorised from scratch"""
+    import turbo_b200 as tb
+    rng = np.random.default_rng(21)
+    n0, d = 250, 5                     # NP = 256: six appends fit the padding, the seventh needs a rebuild
+    X = rng.random((n0 + 8, d))
+    y = np.cos(2 * X).sum(axis=1) + 0.02 * rng.standard_normal(n0 + 8)
+    spec = tb.KernelSpec(3, d, True)
+    theta = np.log(np.r_[0.8, np.full(d, 0.45), 1e-3])
+    mp = dict(kernel=(spec, theta), normalize_y=True)
+    inc = tb.GpuGPSurrogate(model_params=mp, training_iterations=0)
+    Xc = rng.random((3000, d))
+    prev = None
+    for n in (n0, n0 + 1, n0 + 4, n0 + 6, n0 + 8):
+        model, info = inc.construct_model(0, X[:n], y[:n])
+        expect_inc = prev is not None and n <= 256
+        assert bool(info.get('incremental', False)) == expect_inc, (n, info)
+        if prev is not None and expect_inc:
+            assert prev._factor is None  # the factor moved to the new model
+        fresh = tb.GpuGPSurrogate(model_params=mp, training_iterations=0, incremental=False)
+        ref, _ = fresh.construct_model(0, X[:n], y[:n])
+        mu, sd = model.predict(Xc, return_std_dev=True)
+        mu0, sd0 = ref.predict(Xc, return_std_dev=True)
+        np.testing.assert_allclose(mu, mu0, rtol=1e-9, atol=1e-10)
+        np.testing.assert_allclose(sd ** 2, sd0 ** 2, rtol=1e-8, atol=256 * np.finfo(float).eps * n * model.y_std ** 2)
+        assert model.get_log_likelihood() == pytest.approx(ref.get_log_likelihood(), rel=1e-10)
+        a1 = tb.GpuEI(0.01).construct_function(0, model, 'min', float(y[:n].min()))[0]
+        a0 = tb.GpuEI(0.01).construct_function(0, ref, 'min', float(y[:n].min()))[0]
+        assert a1.argmax_over(candidates=Xc)[1] == a0.argmax_over(candidates=Xc)[1]
+        prev = model
+    # the oracle agrees with an incrementally built model as well
+    sur = tb.GpuGPSurrogate(model_params=mp, training_iterations=0)
+    sur.construct_model(0, X[:n0], y[:n0])
+    model, info = sur.construct_model(1, X[:n0 + 5], y[:n0 + 5])
+    assert info['incremental']
+    og = O.FittedGP(O.KernelSpec(3, d, True), theta, X[:n0 + 5], y[:n0 + 5])
+    mu_o, sd_o = og.predict(Xc[:500])
+    mu, sd = model.predict(Xc[:500], return_std_dev=True)
+    np.testing.assert_allclose(mu, mu_o, rtol=1e-8, atol=1e-8 * np.abs(mu_o).max())
+    np.testing.assert_allclose(sd ** 2, sd_o ** 2, rtol=1e-8, atol=256 * np.finfo(float).eps * (n0 + 5) * model.y_std ** 2)
+    assert model.get_log_likelihood() == pytest.approx(og.lml(), rel=1e-8)

@@ -58,6 +58,10 @@ _SIGNATURES = {
                                    _P, C.c_size_t, _P]),
     "tb200_generate_candidates": (C.c_int, [C.POINTER(CandSpecC), C.c_int, C.c_int64, C.c_int64, _P, _P]),
     "tb200_fp64_peak": (C.c_int, [C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "tb200_append_workspace_bytes": (C.c_size_t, [C.c_int]),
+    "tb200_factor_append": (C.c_int, [_P, _P, _P, _P, C.c_int, C.POINTER(KernelSpecC), _P, C.c_double, _P, _P,
+                                      C.c_size_t, _P]),
+    "tb200_alpha_lml": (C.c_int, [_P, C.c_int, _P, _P, _P, _P, _P, C.c_size_t, _P]),
     "tb200_acquire_local_best_count": (C.c_int, [C.c_int64, C.c_int]),
     "tb200_acquire_local_bests": (C.c_int, [_P, C.c_int, C.c_int, C.c_int64, C.c_int, _P, _P, _P]),
     "tb200_acquire_grad_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),

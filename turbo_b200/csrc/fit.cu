@@ -564,6 +564,77 @@ __global__ void __launch_bounds__(256) slice_operand_kernel(const double* __rest
 }
 
 // ---------------------------------------------------------------------------------------------
+// incremental refit: append one training point to a factor at fixed hyper-parameters
+//   L' = [[L, 0], [l^T, lam]],  l = L^-1 k,  lam^2 = k(x,x) + jitter - l.l
+//   L'^-1 = [[L^-1, 0], [-(L^-T l)^T / lam, 1 / lam]]
+// The padded row n_old of Linv (identity) becomes the new row; O(n^2) instead of the O(n^3) refactorisation.
+// ---------------------------------------------------------------------------------------------
+__global__ void kcol_kernel(const double* __restrict__ x_new, const double* __restrict__ XsT, int n, int NP,
+                            tb200_kernel_spec spec, const double* __restrict__ theta, double* __restrict__ kv) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= NP) return;
+    double v = 0.0;
+    if (j < n) {
+        double r2 = 0.0;
+        for (int k = 0; k < spec.d; ++k) {
+            const double df = x_new[k] / length_scale(spec, theta, k) - XsT[(long)k * NP + j];
+            r2 += df * df;
+        }
+        v = unpack_hyper(spec, theta).sf2 * shape_fn(spec.kind, r2);
+    }
+    kv[j] = v;
+}
+
+__global__ void __launch_bounds__(256) append_row_kernel(const double* __restrict__ x_new, const double* __restrict__ l,
+                                                         const double* __restrict__ u, int n_old, int NP,
+                                                         tb200_kernel_spec spec, const double* __restrict__ theta,
+                                                         double jitter, double* __restrict__ XsT,
+                                                         double* __restrict__ Linv, double* __restrict__ Ldiag,
+                                                         int* __restrict__ info) {
+    __shared__ double red[8];
+    __shared__ double lam_s;
+    double s = 0.0;
+    for (int j = threadIdx.x; j < n_old; j += blockDim.x) s = fma(l[j], l[j], s);
+    s = warp_sum(s);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < 8; ++w) t += red[w];
+        const Hyper h = unpack_hyper(spec, theta);
+        const double lam2 = (h.sf2 + h.noise + jitter) - t;  // diagonal of K as gram_train_kernel writes it
+        const bool ok = lam2 > 0.0;                             // false for NaN too
+        lam_s = ok ? sqrt(lam2) : 0.0;
+        *info = ok ? 0 : n_old + 1;                             // first failing pivot, 1-based (LAPACK convention)
+    }
+    __syncthreads();
+    const double lam = lam_s;
+    if (lam == 0.0) return;
+    double* row = Linv + (long)n_old * NP;
+    for (int j = threadIdx.x; j < n_old; j += blockDim.x) row[j] = -u[j] / lam;
+    if (threadIdx.x == 0) {
+        row[n_old] = 1.0 / lam;
+        Ldiag[n_old] = lam;
+    }
+    for (int k = threadIdx.x; k < spec.d; k += blockDim.x)
+        XsT[(long)k * NP + n_old] = x_new[k] / length_scale(spec, theta, k);
+}
+
+__global__ void logdet_from_diag_kernel(const double* __restrict__ Ldiag, int n, double* __restrict__ logdet) {
+    __shared__ double red[32];
+    double s = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) s += log(Ldiag[i]);
+    s = warp_sum(s);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w];
+        *logdet = t;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // host drivers
 // ---------------------------------------------------------------------------------------------
 struct FitBuffers {
@@ -1006,6 +1077,51 @@ int tb200_factor(const double* X, const double* y_n, int n, const tb200_kernel_s
     TB_CHECK(work_bytes >= need, "workspace too small (see tb200_fit_workspace_bytes)");
     return fit_pipeline(X, y_n, n, *spec, theta, 1, jitter, false, fb, XsT, Linv, alpha, Ldiag, lml, nullptr, info,
                         (cudaStream_t)stream);
+}
+
+size_t tb200_append_workspace_bytes(int n) { return align256(sizeof(double) * pad_n(n)) * 4 + 512; }
+
+int tb200_factor_append(const double* x_new, double* XsT, double* Linv, double* Ldiag, int n_old,
+                        const tb200_kernel_spec* spec, const double* theta, double jitter, int* info, void* work,
+                        size_t work_bytes, void* stream) {
+    if (check_spec(spec)) return -1;
+    TB_CHECK(x_new && XsT && Linv && Ldiag && theta && info && work, "NULL pointer argument");
+    TB_CHECK(n_old >= 1, "n_old must be >= 1");
+    const int NP = pad_n(n_old);
+    TB_CHECK(n_old < NP, "no padded row left: rebuild the factor (tb200_factor) for the larger n");
+    TB_CHECK(work_bytes >= tb200_append_workspace_bytes(n_old), "workspace too small (tb200_append_workspace_bytes)");
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t vec = align256(sizeof(double) * NP);
+    double* kv = (double*)work;
+    double* l = (double*)((char*)work + vec);
+    double* u = (double*)((char*)work + 2 * vec);
+    TB_LAUNCH(kcol_kernel, dim3((NP + 255) / 256), dim3(256), 0, st, x_new, XsT, n_old, NP, *spec, theta, kv);
+    TB_LAUNCH(trmv_lower_kernel, dim3(NP / 8, 1), dim3(256), 0, st, Linv, NP, kv, 0L, l);
+    TB_LAUNCH(trmv_lower_t_kernel, dim3(NP / 64, 1), dim3(256), 0, st, Linv, NP, l, u);
+    TB_LAUNCH(append_row_kernel, dim3(1), dim3(256), 0, st, x_new, l, u, n_old, NP, *spec, theta, jitter, XsT, Linv, Ldiag,
+              info);
+    return 0;
+}
+
+int tb200_alpha_lml(const double* y_n, int n, const double* Linv, const double* Ldiag, double* alpha, double* lml,
+                    void* work, size_t work_bytes, void* stream) {
+    TB_CHECK(y_n && Linv && Ldiag && alpha && lml && work, "NULL pointer argument");
+    TB_CHECK(n >= 1, "n must be >= 1");
+    TB_CHECK(work_bytes >= tb200_append_workspace_bytes(n), "workspace too small (tb200_append_workspace_bytes)");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int NP = pad_n(n);
+    const size_t vec = align256(sizeof(double) * NP);
+    double* ypad = (double*)work;
+    double* z = (double*)((char*)work + vec);
+    double* logdet = (double*)((char*)work + 3 * vec);
+    int* info0 = (int*)((char*)work + 3 * vec + 256);
+    TB_CUDA(cudaMemsetAsync(info0, 0, sizeof(int), st));
+    TB_LAUNCH(pad_vector_kernel, dim3((NP + 255) / 256), dim3(256), 0, st, y_n, n, NP, ypad);
+    TB_LAUNCH(trmv_lower_kernel, dim3(NP / 8, 1), dim3(256), 0, st, Linv, NP, ypad, 0L, z);
+    TB_LAUNCH(trmv_lower_t_kernel, dim3(NP / 64, 1), dim3(256), 0, st, Linv, NP, z, alpha);
+    TB_LAUNCH(logdet_from_diag_kernel, dim3(1), dim3(256), 0, st, Ldiag, n, logdet);
+    TB_LAUNCH(lml_kernel, dim3(1), dim3(256), 0, st, ypad, 0L, alpha, NP, n, logdet, info0, lml);
+    return 0;
 }
 
 int tb200_dgemm(int ta, int tb, int M, int N, int K, double alpha, const double* A, int lda, const double* B, int ldb,

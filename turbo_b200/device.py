@@ -102,6 +102,42 @@ class Factor:
                                             _lib.ptr(self.linvS), _lib.ptr(self.rowscale), _lib.stream_ptr()))
         return self
 
+    def append(self, X_new, yn_dev, n_total, jitter):
+        """incremental refit at fixed theta (tb200_factor_append): append the rows of X_new (k,d) one by
+        one, then recompute alpha and the LML for the n_total (re-normalised) targets in yn_dev.  Returns False --
+        with the factor unchanged in every way that matters -- if the padding is exhausted or a pivot fails."""
+        lib = _lib.load()
+        X_new = np.ascontiguousarray(np.atleast_2d(X_new), dtype=np.float64)
+        k = X_new.shape[0]
+        if self.n + k != n_total or n_total > self.NP or self.info != 0:
+            return False
+        dev = device()
+        xd = torch.from_numpy(X_new).to(dev)
+        info = torch.zeros(1, dtype=torch.int32, device=dev)
+        nbytes = lib.tb200_append_workspace_bytes(n_total)
+        work = _workspace(nbytes)
+        cs = self.spec.to_c()
+        n0 = self.n
+        for i in range(k):
+            _lib.check(lib.tb200_factor_append(_lib.ptr(xd[i:]), _lib.ptr(self.XsT), _lib.ptr(self.Linv),
+                                               _lib.ptr(self.Ldiag), n0 + i, C.byref(cs), _lib.ptr(self.theta),
+                                               float(jitter), _lib.ptr(info), _lib.ptr(work), nbytes, _lib.stream_ptr()))
+            if int(info.item()) != 0:
+                # rows n0..n0+i-1 were appended: put the identity padding back so the factor is the old one again
+                for r in range(n0, n0 + i):
+                    self.Linv[r].zero_()
+                    self.Linv[r, r] = 1.0
+                    self.XsT[:, r] = 0.0
+                return False
+        self.n = n_total
+        lml = torch.empty(1, dtype=torch.float64, device=dev)
+        _lib.check(lib.tb200_alpha_lml(_lib.ptr(yn_dev), n_total, _lib.ptr(self.Linv), _lib.ptr(self.Ldiag),
+                                       _lib.ptr(self.alpha), _lib.ptr(lml), _lib.ptr(work), nbytes, _lib.stream_ptr()))
+        self.lml = float(lml.item())
+        self.linvS = self.rowscale = None  # the byte-slice planes are rebuilt on the next acquisition (~0.1 ms)
+        del work
+        return True
+
     def nbytes(self):
         ts = [self.XsT, self.Linv, self.alpha, self.Ldiag] + ([self.linvS, self.rowscale] if self.linvS is not None else [])
         return sum(t.numel() * t.element_size() for t in ts)

@@ -25,6 +25,18 @@ class KernelSpec:
     def to_c(self):
         return _lib.KernelSpecC(self.kind, self.d, int(self.ard), int(self.has_const), int(self.has_white))
 
+    def _key(self):
+        return (self.kind, self.d, self.ard, self.has_const, self.has_white)
+
+    def __eq__(self, other):
+        return isinstance(other, KernelSpec) and self._key() == other._key()
+
+    def __ne__(self, other):
+        return not self.__eq__(other)
+
+    def __hash__(self):
+        return hash(self._key())
+
     def names(self):
         """same strings as SciKitGPSurrogate.ModelInstance.get_hyper_param_names
         (surrogates.py:350-362) gives for the equivalent scikit-learn kernel."""

@@ -55,7 +55,7 @@ class GpuGPSurrogate(Surrogate):
     default_model_params = {'kernel': 'default', 'normalize_y': True}
 
     def __init__(self, model_params=None, training_iterations=None, param_continuity=True, max_iter=200,
-                 seed=None, group=None, variance_engine=None):
+                 seed=None, group=None, variance_engine=None, incremental=True):
         """model_params: as for SciKitGPSurrogate -- ``kernel`` (a scikit-learn kernel of the supported
         family, a KernelSpec, or (KernelSpec, theta0[, bounds])), ``normalize_y``, ``alpha`` (jitter),
         ``n_restarts_optimizer``, ``random_state``.  The default kernel is the reference's
@@ -73,6 +73,9 @@ class GpuGPSurrogate(Surrogate):
         self.group = group
         # predictive-variance engine: 'auto' (default) | 'dmma' | 'i8' | 'i8x' (device.resolve_engine)
         self.variance_engine = variance_engine
+        # trials that only append rows at unchanged hyper-parameters extend the previous factor in O(n^2) (8f-2)
+        self.incremental = bool(incremental)
+        self._live = None
         rs = self.model_params.get('random_state', seed)
         self._rng = rs if isinstance(rs, np.random.RandomState) else np.random.RandomState(rs)
         self._last_model_params = None
@@ -120,13 +123,40 @@ class GpuGPSurrogate(Surrogate):
                 theta, fit_stats = self._optimise(X_dev, yn_dev, n, spec, theta0, bounds, iterations, jitter,
                                                   start_thetas)
                 fitting_info.update(fit_stats)
+            factor = None
+            if 'fixed' in fitting_info and self.incremental:
+                factor = self._try_incremental(spec, theta, X, yn_dev, jitter)
+                if factor is not None:
+                    theta = self._live[2].copy()  # the factor's own theta (equal up to an exp/log round trip)
+                    fitting_info['incremental'] = True
             model = GpuGPSurrogate.ModelInstance(spec, theta, X, y_n, y_mean, y_std, jitter,
-                                                 device_inputs=(X_dev, yn_dev), variance_engine=self.variance_engine)
+                                                 device_inputs=(X_dev, yn_dev), variance_engine=self.variance_engine,
+                                                 factor=factor)
+            self._live = (model, spec, theta.copy(), float(jitter))
         if len(ws) > 0:
             fitting_info['warnings'] = [w.message for w in ws]
         if iterations > 0:
             self._last_model_params = np.exp(theta.copy())
         return model, fitting_info
+
+    def _try_incremental(self, spec, theta, X, yn_dev, jitter):
+        """when a trial only ADDS rows to the previous trial's X and theta, kernel and jitter are unchanged
+        (the reference's `training_iterations` callable returning 0, surrogates.py:250-269), the previous factor is
+        extended in O(n^2) per new point instead of refactorised.  The factor object moves to the new model; the old
+        model rebuilds its own lazily if plotting asks for it.  Returns None when the conditions do not hold."""
+        live = getattr(self, '_live', None)
+        if live is None:
+            return None
+        old, ospec, otheta, ojit = live
+        f = old._factor
+        n_old = old.X.shape[0]
+        if (f is None or ospec != spec or ojit != float(jitter) or not np.allclose(otheta, theta, rtol=0.0, atol=1e-13)
+                or X.shape[0] <= n_old or X.shape[1] != old.X.shape[1] or not np.array_equal(X[:n_old], old.X)):
+            return None
+        if not f.append(X[n_old:], yn_dev, X.shape[0], jitter):
+            return None
+        old._factor = None
+        return f
 
     def _optimise(self, X_dev, yn_dev, n, spec, theta0, bounds, iterations, jitter, start_thetas):
         if start_thetas is not None:
@@ -170,7 +200,8 @@ class GpuGPSurrogate(Surrogate):
     class ModelInstance(SciKitModelInstance):
         """surrogates.py:328-365 contract; holds only NumPy state + lazily built device buffers."""
 
-        def __init__(self, spec, theta, X, y_n, y_mean, y_std, jitter, device_inputs=None, variance_engine=None):
+        def __init__(self, spec, theta, X, y_n, y_mean, y_std, jitter, device_inputs=None, variance_engine=None,
+                     factor=None):
             self.variance_engine = variance_engine
             self.spec, self.theta = spec, np.asarray(theta, dtype=np.float64).copy()
             self.X, self.y_n = X, y_n
@@ -178,7 +209,10 @@ class GpuGPSurrogate(Surrogate):
             self.model = self  # the reference exposes the sklearn estimator here; plotting only calls predict
             self._factor = None
             self._log_likelihood = None
-            self._build(device_inputs)
+            if factor is not None:  # an incrementally updated factor handed over by the surrogate
+                self._factor, self._log_likelihood = factor, factor.lml
+            else:
+                self._build(device_inputs)
 
         # --- device state -------------------------------------------------------------------
         def _build(self, device_inputs=None):
