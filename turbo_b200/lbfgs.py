@@ -1,115 +1,108 @@
-"""Lock-step batched L-BFGS-B (projected L-BFGS with box bounds) over R restarts.
+"""Lock-step batched L-BFGS-B over R restarts.
 
 scikit-learn runs SciPy's L-BFGS-B once per restart, sequentially
-(sklearn:_gpr.py:312-333, :658-674 behind turbo/modules/surrogates.py:313-318).  Here all R
-restarts advance together so that every objective evaluation is ONE batched device call
-(tb200_lml_batched over the still-active members).  The iterates are not SciPy's iterates --
-parity with the reference is defined at fixed theta (BASELINE.json) -- but the stopping rules are
-SciPy's defaults: projected-gradient tolerance 1e-5 and relative decrease factr*eps = 2.2e-9.
+(sklearn:_gpr.py:312-333, :658-674 behind turbo/modules/surrogates.py:313-318), and the reference's
+auxiliary optimiser does the same per starting point (turbo/modules/auxiliary_optimisers.py:84-93).
+Here every restart IS a SciPy L-BFGS-B instance (same algorithm, line search and stopping rules as
+the reference: projected-gradient tolerance 1e-5, relative decrease factr*eps = 2.2e-9), but the R
+instances advance together: each runs in its own thread and blocks inside its objective call until
+the coordinator has collected the requests of all live instances and answered them with ONE batched
+device call (tb200_lml_batched / tb200_acquire_grad over the members that asked).  The number of
+device calls is therefore max_r(nfev_r), not sum_r(nfev_r), and the iterates of every restart are
+exactly SciPy's.
 
-Pure host logic on (R, p) NumPy arrays: p <= 66 numbers per restart, no device math here.
+Pure host logic on (R, p) NumPy arrays: p <= 66 numbers per restart, no device math here.  The
+device is only ever touched from the calling thread.
 """
+import threading
+
 import numpy as np
-
-
-def _two_loop(g, S, Y):
-    """H*g by the L-BFGS two-loop recursion for one member (lists of s, y pairs, newest last)."""
-    q = g.copy()
-    al = []
-    for s, y in zip(reversed(S), reversed(Y)):
-        a = (s @ q) / (y @ s)
-        al.append(a)
-        q -= a * y
-    if S:
-        q *= (S[-1] @ Y[-1]) / (Y[-1] @ Y[-1])
-    for (s, y), a in zip(zip(S, Y), reversed(al)):
-        b = (y @ q) / (y @ s)
-        q += (a - b) * s
-    return q
+import scipy.optimize
 
 
 def minimize_batched(fun, x0, bounds, max_iter=200, history=10, pgtol=1e-5, ftol=2.220446049250313e-09,
-                     max_ls=20, c1=1e-4):
+                     max_ls=20):
     """minimise R independent functions f_r(x_r) under the same box.
 
     fun(X (k,p), members (k,) int) -> (f (k,), g (k,p)) evaluates the listed members only;
-    non-finite f means "infeasible here" (the line search backs off).
-    Returns (x (R,p), f (R,), n_iter (R,), n_eval).
+    non-finite f means "infeasible here" (a failed Cholesky).  SciPy's line search does not survive a
+    +inf trial value (it returns the start and reports convergence, which is what happens to a
+    scikit-learn restart that steps into a non-PD region); such trials are answered with a large
+    finite penalty and a zero gradient instead, so the line search backs off and the restart goes on.
+    Returns (x (R,p), f (R,), n_iter (R,), n_eval) where n_eval is the
+    number of batched calls of ``fun``.
     """
-    x = np.clip(np.array(x0, dtype=np.float64), bounds[:, 0], bounds[:, 1])
-    R, p = x.shape
+    bounds = np.asarray(bounds, dtype=np.float64)
     lo, hi = bounds[:, 0], bounds[:, 1]
-    f, g = fun(x, np.arange(R))
-    f, g = np.array(f, dtype=np.float64), np.array(g, dtype=np.float64)
+    x0 = np.clip(np.array(x0, dtype=np.float64, ndmin=2), lo, hi)
+    R, p = x0.shape
+    f0, g0 = fun(x0, np.arange(R))
+    f0, g0 = np.array(f0, dtype=np.float64), np.array(g0, dtype=np.float64)
     n_eval = 1
-    S = [[] for _ in range(R)]
-    Y = [[] for _ in range(R)]
-    active = np.isfinite(f)
-    n_iter = np.zeros(R, dtype=int)
+    x_out, f_out, n_iter = x0.copy(), f0.copy(), np.zeros(R, dtype=int)
+    live = [r for r in range(R) if np.isfinite(f0[r]) and np.all(np.isfinite(g0[r]))]
+    if not live:
+        return x_out, f_out, n_iter, n_eval  # every start infeasible: reported, not crashed
 
-    def proj_grad(xr, gr):
-        return xr - np.clip(xr - gr, lo, hi)
+    cond = threading.Condition()
+    requests, answers, finished = {}, {}, set()
+    errors = []
 
-    for _ in range(max_iter):
-        for r in np.flatnonzero(active):
-            if np.max(np.abs(proj_grad(x[r], g[r]))) <= pgtol:
-                active[r] = False
-        idx = np.flatnonzero(active)
-        if idx.size == 0:
-            break
-        # search directions
-        D = np.zeros((R, p))
-        for r in idx:
-            at_bound = ((x[r] <= lo) & (g[r] > 0)) | ((x[r] >= hi) & (g[r] < 0))
-            gf = np.where(at_bound, 0.0, g[r])
-            d = -_two_loop(gf, S[r], Y[r])
-            d[at_bound] = 0.0
-            if not np.all(np.isfinite(d)) or d @ g[r] >= 0:
-                S[r], Y[r] = [], []
-                d = -gf
-            if not S[r]:
-                nrm = np.linalg.norm(d)
-                if nrm > 1.0:
-                    d = d / nrm  # first step (or after a reset): at most unit length, as L-BFGS-B does
-            D[r] = d
-        # projected backtracking line search, all members in lock step
-        t = np.ones(R)
-        pending = idx.copy()
-        x_new, f_new, g_new = x.copy(), f.copy(), g.copy()
-        accepted = np.zeros(R, dtype=bool)
-        for _ls in range(max_ls):
-            if pending.size == 0:
+    def worker(r):
+        first = [True]
+
+        def objective(x):
+            if first[0]:  # SciPy starts by evaluating x0, which the first batched call already did
+                first[0] = False
+                if np.array_equal(x, x0[r]):
+                    return f0[r], g0[r].copy()
+            with cond:
+                requests[r] = np.array(x, dtype=np.float64)
+                cond.notify_all()
+                while r not in answers:
+                    cond.wait()
+                f, g = answers.pop(r)
+            return f, g
+
+        try:
+            res = scipy.optimize.minimize(objective, x0[r], jac=True, method="L-BFGS-B",
+                                          bounds=list(zip(lo, hi)),
+                                          options=dict(maxiter=int(max_iter), maxcor=int(history), ftol=ftol,
+                                                       gtol=pgtol, maxls=int(max_ls)))
+            if np.isfinite(res.fun) and res.fun <= f0[r]:
+                x_out[r], f_out[r] = np.clip(res.x, lo, hi), float(res.fun)
+            n_iter[r] = int(res.nit)
+        except Exception as e:  # never leave the coordinator waiting
+            errors.append(e)
+        finally:
+            with cond:
+                finished.add(r)
+                cond.notify_all()
+
+    threads = [threading.Thread(target=worker, args=(r,), daemon=True) for r in live]
+    for t in threads:
+        t.start()
+    while True:
+        with cond:
+            while len(requests) + len(finished) < len(live):
+                cond.wait()
+            if not requests:
                 break
-            trial = np.clip(x[pending] + t[pending, None] * D[pending], lo, hi)
-            ft, gt = fun(trial, pending)
-            n_eval += 1
-            still = []
-            for k, r in enumerate(pending):
-                decrease = g[r] @ (trial[k] - x[r])
-                if np.isfinite(ft[k]) and np.all(np.isfinite(gt[k])) and ft[k] <= f[r] + c1 * decrease:
-                    x_new[r], f_new[r], g_new[r] = trial[k], ft[k], gt[k]
-                    accepted[r] = True
+            members = np.array(sorted(requests), dtype=int)
+            X = np.stack([requests[r] for r in members])
+            requests.clear()
+        f, g = fun(X, members)  # the one device call of this round, from the calling thread
+        n_eval += 1
+        f, g = np.asarray(f, dtype=np.float64), np.asarray(g, dtype=np.float64)
+        with cond:
+            for k, r in enumerate(members):
+                if np.isfinite(f[k]) and np.all(np.isfinite(g[k])):
+                    answers[int(r)] = (float(f[k]), g[k].copy())
                 else:
-                    t[r] *= 0.5 if np.isfinite(ft[k]) else 0.1
-                    still.append(r)
-            pending = np.array(still, dtype=int)
-        for r in idx:
-            n_iter[r] += 1
-            if not accepted[r]:
-                if S[r]:  # retry once from steepest descent before giving up
-                    S[r], Y[r] = [], []
-                else:
-                    active[r] = False
-                continue
-            s, y = x_new[r] - x[r], g_new[r] - g[r]
-            if s @ y > 1e-10 * (y @ y):
-                S[r].append(s)
-                Y[r].append(y)
-                if len(S[r]) > history:
-                    S[r].pop(0)
-                    Y[r].pop(0)
-            rel = (f[r] - f_new[r]) / max(abs(f[r]), abs(f_new[r]), 1.0)
-            x[r], f[r], g[r] = x_new[r], f_new[r], g_new[r]
-            if rel <= ftol:
-                active[r] = False
-    return x, f, n_iter, n_eval
+                    answers[int(r)] = (1e8 * max(1.0, abs(f0[r])), np.zeros(p))
+            cond.notify_all()
+    for t in threads:
+        t.join()
+    if errors:
+        raise errors[0]
+    return x_out, f_out, n_iter, n_eval
