@@ -29,10 +29,18 @@ import time
 
 import numpy as np
 
-# rank 0 prints ONE JSON line on stdout: NCCL's "NCCL version ..." banner (printed at VERSION and at WARN level) goes
-# to a file unless the caller asked for INFO/TRACE output explicitly
-if os.environ.get("NCCL_DEBUG", "VERSION").upper() in ("VERSION", "WARN"):
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/null")
+# rank 0 prints ONE JSON line on stdout.  Libraries write there too (NCCL prints "NCCL version ..." at its default
+# debug level, from C, whatever NCCL_DEBUG_FILE says), so file descriptor 1 is pointed at stderr for the whole run and
+# the JSON line goes to the saved descriptor of the real stdout.
+sys.stdout.flush()
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
@@ -153,7 +161,7 @@ def run_reference(args):
                                        "(NumPy/SciPy; same LAPACK/BLAS calls as the reference's sklearn path)" % sample},
             "e2e": {"value": value, "unit": "candidates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
 
 
 def run_ours(args):
@@ -376,7 +384,7 @@ def run_ours(args):
                         "d2h_bytes_per_step": 16 * world, "ms_per_step": ms_e2e / args.steps},
                 "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "fit": fit,
                 "argmax": {"value": res[0], "index": res[1]}, "factor_ms_cold": factor_ms_cold}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         td.destroy_process_group()
 
