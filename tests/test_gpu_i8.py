@@ -95,3 +95,55 @@ def test_i8_rejects_large_n():
     with pytest.raises(ValueError):
         device.resolve_engine("i8", 65536)
     assert device.resolve_engine("auto", 65536) == "dmma" and device.resolve_engine("auto", 16384) == "i8"
+
+
+def test_max_dimension_and_slot_reuse_over_many_small_batches():
+    """d = TB200_MAX_D (64) and a candidate set that is 11 ragged batches of 256 (every buffer slot is reused several
+    times, the last batch is partial): mean/variance match the oracle, the fused argmax equals evaluate-then-argmax,
+    for both engines; generated (uniform, LHS) sets give the same winner on both engines"""
+    import turbo_b200 as tb
+    from turbo_b200 import device
+    rng = np.random.default_rng(64)
+    n, d, m = 200, 64, 2700
+    X = rng.random((n, d))
+    y = np.sin(X[:, :5]).sum(axis=1) + 0.01 * rng.standard_normal(n)
+    theta = np.log(np.r_[1.0, np.full(d, 3.0), 1e-3])
+    Xc = rng.random((m, d))
+    og = O.FittedGP(O.KernelSpec(3, d, True), theta, X, y)
+    mu_o, sd_o = og.predict(Xc)
+    ei_o = O.acquisition(O.ACQ_EI, mu_o, sd_o, -1.0, float(y.min()), 0.01)
+    winners = {}
+    for engine in ("dmma", "i8"):
+        sur = tb.GpuGPSurrogate(model_params=dict(kernel=(tb.KernelSpec(3, d, True), theta), normalize_y=True),
+                                training_iterations=0, variance_engine=engine)
+        model = sur.construct_model(0, X, y)[0]
+        mu, sd = model.predict(Xc, return_std_dev=True)
+        np.testing.assert_allclose(mu, mu_o, rtol=1e-8, atol=1e-8 * np.abs(mu_o).max())
+        np.testing.assert_allclose(sd ** 2, sd_o ** 2, rtol=1e-8, atol=256 * EPS * n * model.y_std ** 2)
+        acq = tb.GpuEI(0.01).construct_function(0, model, 'min', float(y.min()))[0]
+        val, idx, x = acq.argmax_over(candidates=Xc, batch=256)
+        assert idx == O.argmax_first(ei_o) and np.array_equal(x[0], Xc[idx])
+        assert val == pytest.approx(ei_o[idx], rel=1e-8)
+        for gen in ("uniform", "lhs"):
+            v, i, xg = acq.argmax_over(generator=gen, m=3001, lo=[0.0] * d, hi=[1.0] * d, seed=11, batch=256)
+            winners.setdefault(gen, []).append((i, xg.tobytes()))
+            assert acq(xg)[0] == pytest.approx(v, rel=1e-8)
+    assert winners["uniform"][0] == winners["uniform"][1] and winners["lhs"][0] == winners["lhs"][1]
+
+
+def test_max_dimension_lml_and_gradient():
+    """the fit kernels at d = 64 (64-70 KB of dynamic shared memory): LML and gradient against the oracle"""
+    from turbo_b200 import device
+    import turbo_b200 as tb
+    rng = np.random.default_rng(65)
+    n, d = 150, 64
+    X = rng.random((n, d))
+    y = np.sin(X[:, :5]).sum(axis=1) + 0.01 * rng.standard_normal(n)
+    y = (y - y.mean()) / y.std()
+    T = np.log(np.r_[1.0, np.full(d, 3.0), 1e-3]) + rng.normal(0, 0.2, (3, d + 2))
+    lml, grad, info = device.lml_batched(device.to_device(X), device.to_device(y), n, tb.KernelSpec(3, d, True), T, 1e-10)
+    assert not info.any()
+    for r in range(3):
+        ol, og = O.log_marginal_likelihood(O.KernelSpec(3, d, True), T[r], X, y, 1e-10, True)
+        assert lml[r] == pytest.approx(ol, rel=1e-6)
+        np.testing.assert_allclose(grad[r], og, rtol=1e-6, atol=1e-6 * np.abs(og).max())

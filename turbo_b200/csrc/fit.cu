@@ -988,6 +988,19 @@ static int fit_pipeline(const double* X, const double* y_n, int n, const tb200_k
     TB_LAUNCH(pad_vector_kernel, dim3((NP + 255) / 256), dim3(256), 0, st, y_n, n, NP, fb.ypad);
     TB_LAUNCH(scale_points_kernel, dim3((NP + 255) / 256, R), dim3(256), 0, st, X, n, NP, spec, theta, p, XsT);
     const size_t gsm = sizeof(double) * 2 * d * GT;
+    {
+        // d up to TB200_MAX_D = 64 needs 64 KB (gram) / 70 KB (gradient) of dynamic shared memory: opt in once
+        static bool configured = false;
+        if (!configured) {
+            const int mx = (int)(sizeof(double) * (2 * TB200_MAX_D * GT + 8 * (TB200_MAX_D + 2)));
+            TB_CUDA(cudaFuncSetAttribute(gram_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+            TB_CUDA(cudaFuncSetAttribute(lml_grad_kernel<TB200_RBF>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+            TB_CUDA(cudaFuncSetAttribute(lml_grad_kernel<TB200_MATERN12>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+            TB_CUDA(cudaFuncSetAttribute(lml_grad_kernel<TB200_MATERN32>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+            TB_CUDA(cudaFuncSetAttribute(lml_grad_kernel<TB200_MATERN52>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+            configured = true;
+        }
+    }
     TB_LAUNCH(gram_train_kernel, dim3(nt64, R), dim3(256), gsm, st, XsT, n, NP, spec, theta, p, jitter, fb.K);
     if (potrf_batched(fb, NP, R, info, st)) return -1;
     TB_LAUNCH(logdet_kernel, dim3(R), dim3(256), 0, st, fb.K, NP, Ldiag, fb.logdet);
