@@ -39,12 +39,22 @@ def padded_n(n):
 
 
 def lml_batched(X_dev, yn_dev, n, spec, thetas, jitter, with_grad=True):
-    """log-marginal likelihood (+ gradient) of R theta rows in one device call.
+    """log-marginal likelihood (+ gradient) of R theta rows in one device call (several when the R working sets --
+    about 23 n^2 bytes each -- do not fit in the free device memory: 64 restarts at n = 16384 would need 390 GB).
     -> (lml (R,), grad (R,p) or None, info (R,)) as NumPy."""
     lib = _lib.load()
     thetas = np.ascontiguousarray(np.atleast_2d(thetas), dtype=np.float64)
     R, p = thetas.shape
     assert p == spec.p
+    free_bytes = torch.cuda.mem_get_info()[0] + torch.cuda.memory_reserved() - torch.cuda.memory_allocated()
+    chunk = R
+    while chunk > 1 and lib.tb200_fit_workspace_bytes(n, spec.d, chunk, int(with_grad)) > 0.8 * free_bytes:
+        chunk = (chunk + 1) // 2
+    if chunk < R:
+        parts = [lml_batched(X_dev, yn_dev, n, spec, thetas[o:o + chunk], jitter, with_grad) for o in range(0, R, chunk)]
+        return (np.concatenate([q[0] for q in parts]),
+                np.concatenate([q[1] for q in parts]) if with_grad else None,
+                np.concatenate([q[2] for q in parts]))
     dev = device()
     th = torch.from_numpy(thetas).to(dev)
     lml = torch.empty(R, dtype=torch.float64, device=dev)
