@@ -677,7 +677,7 @@ static bool use_left_looking(int NB, int R) {
         const char* e = getenv("TB200_FIT_LEFT_MIN");  // R * (n/128) at which the batched schedule takes over
         thr = e ? atol(e) : 128;  // measured at n = 4096: the batched INT8 schedule wins from R = 4 (profiles/r1_fit_schedule_threshold.md)
     }
-    return (long)R * NB >= thr;
+    return R >= 4 && (long)R * NB >= thr;  // one to three matrices: the right-looking schedule has more tiles per step
 }
 
 // The batched (left-looking) schedule runs its long-K products on the INT8 tensor cores when one INT32 pass covers
@@ -733,7 +733,7 @@ size_t fit_workspace_layout(int n, int d, int R, int p, bool own_linv, bool own_
 }
 
 // Two schedules of the same blocked algorithms, chosen by how many independent matrices there are:
-//  * several matrices (batched restarts, R * n/128 >= 128): LEFT-looking.  Every tile accumulates its whole update in
+//  * several matrices (batched restarts, R >= 4 and R * n/128 >= 128): LEFT-looking.  Every tile accumulates its whole update in
 //    registers over a long K range and is written once, so the GEMMs run at long-K efficiency and
 //    each tile of C is read/written O(1) times instead of once per 128-wide step;
 //  * few matrices (the final factor, n large): RIGHT-looking, which exposes (NB-k)^2/2 tiles per
