@@ -59,6 +59,17 @@ typedef struct {
     double hi[TB200_MAX_D];
 } tb200_cand_spec;
 
+/* points no selected candidate may come too close to: the reference discards a Bayesian trial whose
+ * point x has np.sum((X - x)**2, axis=1) <= tol for some row of X (turbo/utils.py:111-130 via
+ * turbo/modules/fallback.py:49-54, turbo/optimiser.py:349-352) and draws a random one instead; with an exclusion set
+ * the argmax skips such candidates in the same pass.  tol < 0 or n == 0 disables it (fallback.py:51-52). */
+typedef struct {
+    const double* X;  /* device, (n, d) row-major, UNSCALED coordinates (the space the candidates live in) */
+    int n;
+    double tol;       /* close_tolerance: largest SQUARED Euclidean distance considered too close */
+    double* min_out;  /* optional device (m,) : every candidate's smallest squared distance; NULL = scratch */
+} tb200_exclusion;
+
 int tb200_version(void);
 const char* tb200_last_error(void);
 int tb200_padded_n(int n);
@@ -98,6 +109,18 @@ int tb200_acquire(const double* Xc, int64_t m, int64_t index_base, const tb200_c
                   double* best_val, int64_t* best_idx, int64_t batch, void* work, size_t work_bytes,
                   void* stream);
 int tb200_best_reset(double* best_val, int64_t* best_idx, void* stream);
+/* tb200_acquire with an exclusion set (NULL excl = tb200_acquire).  acq_out still holds the value of an excluded
+ * candidate; only the argmax skips it. */
+int tb200_acquire_excl(const tb200_exclusion* excl_host, const double* Xc, int64_t m, int64_t index_base,
+                       const tb200_cand_spec* cand_host, const double* XsT, const double* Linv, const double* alpha,
+                       int n, const tb200_kernel_spec* spec_host, const double* theta, const tb200_acq_spec* acq_host,
+                       double* mu_out, double* sigma_out, double* acq_out, double* best_val, int64_t* best_idx,
+                       int64_t batch, void* work, size_t work_bytes, void* stream);
+/* smallest squared Euclidean distance (and its row, optional) from each of m query rows to the n rows of X: the
+ * batched form of turbo/utils.py:111-130 `close_to_any` (x close <=> min_out <= tol), summed in NumPy's order so the
+ * comparison agrees bit for bit.  n == 0: +inf / -1 (close_to_any of an empty set is False). */
+int tb200_min_sqdist(const double* Xq, int64_t m, const double* X, int n, int d, double* min_out, int64_t* arg_out,
+                     void* stream);
 
 /* INT8-tensor-core engine for the predictive variance (tcgen05.mma kind::i8 + TMEM, csrc/ozaki_i8.cuh).
  * Same contract and results as tb200_acquire (same sklearn lines); the O(n^2)-per-candidate contraction
@@ -119,6 +142,12 @@ int tb200_acquire_i8(const double* Xc, int64_t m, int64_t index_base, const tb20
                      const tb200_acq_spec* acq_host, double* mu_out, double* sigma_out, double* acq_out,
                      double* best_val, int64_t* best_idx, int64_t batch, void* work, size_t work_bytes,
                      void* stream);
+int tb200_acquire_i8_excl(const tb200_exclusion* excl_host, const double* Xc, int64_t m, int64_t index_base,
+                          const tb200_cand_spec* cand_host, const double* XsT, const uint8_t* linvS,
+                          const double* rowscale, int gmax, const double* alpha, int n,
+                          const tb200_kernel_spec* spec_host, const double* theta, const tb200_acq_spec* acq_host,
+                          double* mu_out, double* sigma_out, double* acq_out, double* best_val, int64_t* best_idx,
+                          int64_t batch, void* work, size_t work_bytes, void* stream);
 
 /* write candidates [index_base, index_base+m) of a generated set into out (m x d) */
 int tb200_generate_candidates(const tb200_cand_spec* cand_host, int d, int64_t index_base, int64_t m,

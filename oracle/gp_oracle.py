@@ -225,6 +225,29 @@ def argmax_first(values):
     return int(np.argmax(v))
 
 
+def min_sqdist(Xq, X):
+    """smallest squared Euclidean distance from each row of Xq to the rows of X, the quantity
+    turbo/utils.py:130 compares with the tolerance: ``np.sum((xs - x)**2, axis=1)`` (same expression, row by row,
+    so NumPy's own summation order is the reference).  Empty X: +inf (turbo/utils.py:119-121: not close)."""
+    Xq, X = np.atleast_2d(Xq), np.atleast_2d(X)
+    out = np.full(Xq.shape[0], np.inf)
+    arg = np.full(Xq.shape[0], -1, dtype=np.int64)
+    if X.shape[0] == 0:
+        return out, arg
+    for i in range(Xq.shape[0]):
+        s = np.sum((X - Xq[i:i + 1]) ** 2, axis=1)
+        if not np.all(np.isnan(s)):
+            arg[i] = int(np.nanargmin(s))
+            out[i] = s[arg[i]]
+    return out, arg
+
+
+def close_to_any(x, xs, tol=1e-5):
+    """turbo/utils.py:111-130"""
+    assert x.shape[1] == xs.shape[1] and x.shape[0] == 1
+    return bool(np.any(np.sum((xs - x) ** 2, axis=1) <= tol))
+
+
 def uniform_candidates(rng, m, lo, hi):
     """naive_selectors.py:41-46: one uniform column per bound."""
     lo, hi = np.asarray(lo, float), np.asarray(hi, float)

@@ -314,3 +314,91 @@ def test_incremental_refit_equals_full_refactorisation():
     np.testing.assert_allclose(mu, mu_o, rtol=1e-8, atol=1e-8 * np.abs(mu_o).max())
     np.testing.assert_allclose(sd ** 2, sd_o ** 2, rtol=1e-8, atol=256 * np.finfo(float).eps * (n0 + 5) * model.y_std ** 2)
     assert model.get_log_likelihood() == pytest.approx(og.lml(), rel=1e-8)
+
+
+# ---------------------------------------------------------------------------------------------
+# the fallback's "too close to an existing sample" test over the whole candidate set
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("d", [1, 2, 5, 7, 8, 9, 10, 16, 17, 20, 33, 64])
+def test_min_sqdist_is_bit_exact_with_numpy(d):
+    from turbo_b200 import device
+    rng = np.random.default_rng(d)
+    for n, m in ((1, 1), (63, 127), (64, 128), (65, 129), (300, 1000)):
+        X = rng.random((n, d)) * rng.choice([1e-3, 1.0, 1e3], size=(1, d))
+        Xq = rng.random((m, d)) * rng.choice([1e-3, 1.0, 1e3], size=(1, d))
+        Xq[::7] = X[rng.integers(0, n, size=len(Xq[::7]))]          # exact duplicates: distance 0
+        Xq[1::7] = X[rng.integers(0, n, size=len(Xq[1::7]))] + 1e-6  # near duplicates around the tolerance
+        got, arg = device.min_sqdist(Xq, X, want_arg=True)
+        want, warg = O.min_sqdist(Xq, X)
+        np.testing.assert_array_equal(got, want)   # bit for bit: the comparison with tol must agree
+        np.testing.assert_array_equal(arg, warg)   # first of the nearest rows
+        np.testing.assert_array_equal(device.min_sqdist(Xq, X), want)  # the split-over-points schedule (no arg)
+        for tol in (0.0, 1e-10, 1e-12 * d, 1e-5):
+            close = np.array([O.close_to_any(Xq[i:i + 1], X, tol) for i in range(m)])
+            np.testing.assert_array_equal(got <= tol, close)
+
+
+def test_min_sqdist_empty_sets_and_nan():
+    from turbo_b200 import device
+    Xq = np.random.default_rng(0).random((5, 3))
+    got, arg = device.min_sqdist(Xq, np.zeros((0, 3)), want_arg=True)
+    assert np.all(np.isinf(got)) and np.all(arg == -1)  # turbo/utils.py:119-121: nothing to be close to
+    assert device.min_sqdist(np.zeros((0, 3)), Xq).shape == (0,)
+    X = np.random.default_rng(1).random((4, 3))
+    X[2, 1] = np.nan
+    got, arg = device.min_sqdist(Xq, X, want_arg=True)
+    want, warg = O.min_sqdist(Xq, X)
+    np.testing.assert_array_equal(got, want)  # a NaN row is never the nearest (NaN <= tol is False)
+    np.testing.assert_array_equal(arg, warg)
+
+
+@pytest.mark.parametrize("engine", ["dmma", "i8"])
+def test_argmax_skips_candidates_too_close_to_a_sample(engine):
+    import turbo_b200 as tb
+    rng = np.random.default_rng(11)
+    n, d = 150, 3
+    X = rng.random((n, d))
+    y = np.sin(3 * X.sum(1))
+    spec = tb.KernelSpec(3, d, True)
+    theta = np.log([1.0, 0.5, 0.5, 0.5, 1e-6])
+    model = _fixed_model(spec, theta, X, y)
+    # optimism with beta = 0 on 'max': the acquisition is the posterior mean, whose best candidates are the samples
+    acq = tb.GpuUCB(0.0).construct_function(0, model, "max")[0]
+    cand = np.vstack([rng.random((3000, d)), X, X + 3e-6, rng.random((777, d))])
+    values = acq(cand)
+    v0, i0, x0 = acq.argmax_over(candidates=cand, engine=engine)
+    assert i0 == O.argmax_first(values)
+    for tol in (1e-10, 1e-9, 0.01):
+        mind, _ = O.min_sqdist(cand, X)
+        masked = np.where(mind <= tol, -np.inf, values)
+        v, i, x = acq.argmax_over(candidates=cand, engine=engine, exclude=(X, tol), batch=512)
+        assert i == O.argmax_first(masked)
+        assert not O.close_to_any(x, X, tol)
+        np.testing.assert_array_equal(x[0], cand[i])
+    # disabled (fallback.py:51-52) and empty sets change nothing
+    assert acq.argmax_over(candidates=cand, engine=engine, exclude=(X, -1.0))[1] == i0
+    assert acq.argmax_over(candidates=cand, engine=engine, exclude=(np.zeros((0, d)), 1e-3))[1] == i0
+    # everything excluded: nothing selectable (auxiliary_optimisers.py:117-118)
+    v, i, x = acq.argmax_over(candidates=X, engine=engine, exclude=(X, 1e-10))
+    assert i == -1 and x is None and v == -np.inf
+
+
+def test_aux_optimiser_close_tolerance_never_returns_a_known_point():
+    import turbo_b200 as tb
+    from types import SimpleNamespace
+    rng = np.random.default_rng(3)
+    n, d = 60, 2
+    X = rng.random((n, d))
+    y = np.cos(4 * X[:, 0]) + X[:, 1]
+    model = _fixed_model(tb.KernelSpec(3, d, True), np.log([1.0, 0.4, 0.4, 1e-6]), X, y)
+    acq = tb.GpuUCB(0.0).construct_function(0, model, "max")[0]
+    bounds = SimpleNamespace(ordered=[("a", 0.0, 1.0), ("b", 0.0, 1.0)])
+    pool = np.vstack([X, rng.random((500, d))])
+    plain = tb.GpuCandidateArgmax(num_random=len(pool), candidates=lambda m, lb: pool, release_model=False)
+    x_plain, _ = plain(bounds, acq)
+    guarded = tb.GpuCandidateArgmax(num_random=len(pool), candidates=lambda m, lb: pool, release_model=False,
+                                    close_tolerance=1e-10)
+    x_g, info = guarded(bounds, acq)
+    assert O.close_to_any(x_plain, X, 1e-10)      # the reference would now discard the trial (optimiser.py:349-352)
+    assert not O.close_to_any(x_g, X, 1e-10)
+    assert info["argmax_index"] >= n

@@ -33,6 +33,10 @@ class CandSpecC(C.Structure):
                 ("lo", C.c_double * MAX_D), ("hi", C.c_double * MAX_D)]
 
 
+class ExclusionC(C.Structure):
+    _fields_ = [("X", C.c_void_p), ("n", C.c_int), ("tol", C.c_double), ("min_out", C.c_void_p)]
+
+
 _P = C.c_void_p
 _SIGNATURES = {
     # name: (restype, argtypes)  -- one entry per declaration in include/turbo_b200.h
@@ -56,6 +60,13 @@ _SIGNATURES = {
     "tb200_acquire_i8": (C.c_int, [_P, C.c_int64, C.c_int64, C.POINTER(CandSpecC), _P, _P, _P, C.c_int, _P, C.c_int,
                                    C.POINTER(KernelSpecC), _P, C.POINTER(AcqSpecC), _P, _P, _P, _P, _P, C.c_int64,
                                    _P, C.c_size_t, _P]),
+    "tb200_acquire_excl": (C.c_int, [C.POINTER(ExclusionC), _P, C.c_int64, C.c_int64, C.POINTER(CandSpecC), _P, _P, _P,
+                                     C.c_int, C.POINTER(KernelSpecC), _P, C.POINTER(AcqSpecC), _P, _P, _P, _P, _P,
+                                     C.c_int64, _P, C.c_size_t, _P]),
+    "tb200_acquire_i8_excl": (C.c_int, [C.POINTER(ExclusionC), _P, C.c_int64, C.c_int64, C.POINTER(CandSpecC), _P, _P,
+                                        _P, C.c_int, _P, C.c_int, C.POINTER(KernelSpecC), _P, C.POINTER(AcqSpecC), _P,
+                                        _P, _P, _P, _P, C.c_int64, _P, C.c_size_t, _P]),
+    "tb200_min_sqdist": (C.c_int, [_P, C.c_int64, _P, C.c_int, C.c_int, _P, _P, _P]),
     "tb200_generate_candidates": (C.c_int, [C.POINTER(CandSpecC), C.c_int, C.c_int64, C.c_int64, _P, _P]),
     "tb200_fp64_peak": (C.c_int, [C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "tb200_append_workspace_bytes": (C.c_size_t, [C.c_int]),

@@ -45,7 +45,7 @@ class _DeviceFunction:
         return device.acquisition_value_and_grad(self.model.factor, self._spec_c(), X)
 
     def argmax_over(self, candidates=None, generator=None, m=None, lo=None, hi=None, seed=0, group=None,
-                    chunk=1 << 18, batch=0, engine=None, keep_top=0):
+                    chunk=1 << 18, batch=0, engine=None, keep_top=0, exclude=None):
         """argmax of the acquisition function over a candidate set.
 
         candidates: (m,d) host array (every rank passes the same full set when ``group`` is given), or
@@ -53,14 +53,21 @@ class _DeviceFunction:
                     from the global index, so the result does not depend on how ranks split the range.
         Returns (value, global index, x (1,d)); (-inf, -1, None) if no candidate is selectable.
         Ties keep the lowest index; NaN never wins (auxiliary_optimisers.py:63-66 picks argsort's first).
+        exclude = (X (k,d), tol): candidates whose squared Euclidean distance to a row of X is <= tol are never selected
+        (turbo/utils.py:111-130 `close_to_any`, applied to every candidate on the device in the same pass instead of
+        to the winner afterwards, turbo/optimiser.py:349-352); tol < 0 disables it (fallback.py:51-52).
         keep_top > 0: additionally returns (values, indices, X) of up to keep_top distinct good candidates, best
         first (the winner, then per-CTA running bests merged over chunks and ranks) as a 4th element.
         """
         import torch
         from . import dist
         rank, world = dist.rank_world(group)
+        exclusion = None
+        if exclude is not None and exclude[1] >= 0 and len(exclude[0]):
+            exclusion = (device.to_device(np.ascontiguousarray(np.atleast_2d(exclude[0]), dtype=np.float64)),
+                         float(exclude[1]))
         a = device.Acquirer(self.model.factor, self._spec_c(), batch,
-                            engine=engine or getattr(self.model, 'variance_engine', None))
+                            engine=engine or getattr(self.model, 'variance_engine', None), exclusion=exclusion)
         d = self.model.spec.d
         if candidates is not None:
             if isinstance(candidates, torch.Tensor):  # a (pinned) host tensor is used in place

@@ -19,7 +19,7 @@ import numpy as np
 
 class GpuCandidateArgmax:
     def __init__(self, num_random=1 << 20, candidates='uniform', seed=0, group=None, release_model=True,
-                 grad_restarts=0, start_from_best=2, polish_max_iter=100):
+                 grad_restarts=0, start_from_best=2, polish_max_iter=100, close_tolerance=-1.0):
         """candidates:
              'uniform' -- generated on the device (Philox keyed by seed, trial counter and global index);
              'lhs'     -- Latin hypercube on the device (naive_selectors.py:65-83 semantics);
@@ -27,6 +27,11 @@ class GpuCandidateArgmax:
                           (naive_selectors.py:41-46: one np.random.uniform column per bound), then
                           streamed to the device: reproduces the reference's candidate sequence;
              callable  -- ``f(num_points, latent_bounds) -> (m,d)`` (any reference selector).
+        close_tolerance >= 0: candidates whose squared distance to a training point is <= close_tolerance
+        (``Fallback.close_tolerance``, turbo/modules/fallback.py:49-54 -> turbo/utils.py:111-130) are skipped by the
+        device argmax, so the optimiser's too-close test (turbo/optimiser.py:349-352) never has to throw the Bayesian
+        trial away; a polished point that ends up too close is dropped for the random-stage winner.  Default -1:
+        off, the reference's behaviour.
         release_model: free the model's O(n^2) device buffers after the argmax (the Recorder keeps
         every trial's model object alive; they are rebuilt lazily if plotting calls predict later)."""
         self.num_random = int(num_random)
@@ -37,6 +42,7 @@ class GpuCandidateArgmax:
         self.grad_restarts = int(grad_restarts)
         self.start_from_best = min(int(start_from_best), self.grad_restarts)
         self.polish_max_iter = int(polish_max_iter)
+        self.close_tolerance = float(close_tolerance)
         assert self.start_from_best <= self.num_random
         self._calls = 0
 
@@ -50,16 +56,17 @@ class GpuCandidateArgmax:
         keep = self.start_from_best if self.grad_restarts > 0 else 0
         top = None
         seed = (self.seed * 1000003 + self._calls) & (2 ** 63 - 1)  # a fresh set every trial
+        exclude = (acq.model.X, self.close_tolerance) if self.close_tolerance >= 0 else None
         if self.candidates in ('uniform', 'lhs'):
             res = acq.argmax_over(generator=self.candidates, m=self.num_random, lo=lo, hi=hi, seed=seed,
-                                  group=self.group, keep_top=keep)
+                                  group=self.group, keep_top=keep, exclude=exclude)
         else:
             if self.candidates == 'numpy':
                 cols = [np.random.uniform(pmin, pmax, size=(self.num_random, 1)) for pmin, pmax in zip(lo, hi)]
                 X = np.hstack(cols)
             else:
                 X = np.asarray(self.candidates(self.num_random, latent_bounds), dtype=np.float64)
-            res = acq.argmax_over(candidates=X, group=self.group, keep_top=keep)
+            res = acq.argmax_over(candidates=X, group=self.group, keep_top=keep, exclude=exclude)
         val, idx, x = res[:3]
         if keep:
             top = res[3]
@@ -98,5 +105,10 @@ class GpuCandidateArgmax:
         j = int(np.argmin(fs))
         info.update({'polish_starts': len(x0), 'polish_evaluations': int(n_eval), 'random_stage_max_acq': float(val)})
         if -fs[j] > val:  # :108-110 keep the better of the two stages
+            if self.close_tolerance >= 0:
+                # same test, same arithmetic as turbo/utils.py:130 on the one polished point
+                if np.any(np.sum((acq.model.X - xs[j:j + 1]) ** 2, axis=1) <= self.close_tolerance):
+                    info['polish_rejected'] = 'too_close'
+                    return val, x
             return float(-fs[j]), xs[j:j + 1].copy()
         return val, x

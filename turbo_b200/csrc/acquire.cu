@@ -354,6 +354,125 @@ __global__ void __launch_bounds__(256) linv_slice_kernel(const double* __restric
 }
 
 // ---------------------------------------------------------------------------------------------
+// "too close to an existing sample" over a whole candidate batch.  The reference tests ONE selected point
+// against the trial set after the argmax, turbo/utils.py:111-130 `close_to_any`:
+//     np.any(np.sum((xs - x)**2, axis=1) <= tol)
+// and throws the Bayesian trial away when it is too close (turbo/optimiser.py:349-352, turbo/modules/fallback.py:49-54).
+// Here every candidate gets its smallest squared distance to the n points so the argmax can skip such candidates in
+// the same pass.  The sum over the d attributes follows NumPy's contiguous reduction bit for bit: fewer than 8 terms
+// are added left to right; otherwise 8 running sums over strides of 8, combined pairwise, then the tail left to right
+// (no FMA contraction: NumPy squares, then adds).  One thread per candidate; the points are staged through shared
+// memory in chunks and read as broadcasts.  FP64-pipe bound: 3 n d operations per candidate.
+// ---------------------------------------------------------------------------------------------
+constexpr int MSD_THREADS = 128, MSD_CHUNK = 64;
+static int g_sm_count = 148;  // refreshed by configure_carveout()
+
+__global__ void __launch_bounds__(MSD_THREADS) min_sqdist_kernel(const double* __restrict__ Xc, int64_t m,
+                                                                 const double* __restrict__ X, int n, int d,
+                                                                 double* __restrict__ min_out,
+                                                                 int64_t* __restrict__ arg_out, int jchunk) {
+    extern __shared__ double msd_sh[];
+    double* xs = msd_sh;                     // [d][MSD_THREADS]: column t belongs to thread t
+    double* xt = msd_sh + (size_t)d * MSD_THREADS;  // [MSD_CHUNK][d]
+    const int64_t c0 = (int64_t)blockIdx.x * MSD_THREADS;
+    const int64_t rows = (m - c0 < MSD_THREADS) ? (m - c0) : MSD_THREADS;
+    for (int64_t e = threadIdx.x; e < (int64_t)MSD_THREADS * d; e += MSD_THREADS) {
+        const int64_t r = e / d;
+        const int k = (int)(e - r * d);
+        xs[(size_t)k * MSD_THREADS + r] = (r < rows) ? Xc[c0 * d + e] : 0.0;
+    }
+    double best = INFINITY;
+    int64_t arg = -1;
+    const double* mine = xs + threadIdx.x;
+    const int d8 = d - (d & 7);
+    // blockIdx.y owns the points [jlo, jhi): with more than one such range the results meet in an atomic min on the
+    // bit pattern (non-negative doubles order like unsigned integers; min_out starts at +inf, arg_out is not kept)
+    const int jlo = (int)blockIdx.y * jchunk;
+    const int jhi = (jlo + jchunk < n) ? (jlo + jchunk) : n;
+    for (int j0 = jlo; j0 < jhi; j0 += MSD_CHUNK) {
+        const int cnt = (jhi - j0 < MSD_CHUNK) ? (jhi - j0) : MSD_CHUNK;
+        __syncthreads();
+        for (int e = threadIdx.x; e < cnt * d; e += MSD_THREADS) xt[e] = X[(size_t)j0 * d + e];
+        __syncthreads();
+        for (int j = 0; j < cnt; ++j) {
+            const double* t = xt + (size_t)j * d;
+            double sum;
+            if (d < 8) {
+                sum = 0.0;
+                for (int k = 0; k < d; ++k) {
+                    const double df = __dsub_rn(t[k], mine[(size_t)k * MSD_THREADS]);
+                    sum = __dadd_rn(sum, __dmul_rn(df, df));
+                }
+            } else {
+                double r[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const double df = __dsub_rn(t[u], mine[(size_t)u * MSD_THREADS]);
+                    r[u] = __dmul_rn(df, df);
+                }
+                for (int k = 8; k < d8; k += 8) {
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        const double df = __dsub_rn(t[k + u], mine[(size_t)(k + u) * MSD_THREADS]);
+                        r[u] = __dadd_rn(r[u], __dmul_rn(df, df));
+                    }
+                }
+                sum = __dadd_rn(__dadd_rn(__dadd_rn(r[0], r[1]), __dadd_rn(r[2], r[3])),
+                                __dadd_rn(__dadd_rn(r[4], r[5]), __dadd_rn(r[6], r[7])));
+                for (int k = d8; k < d; ++k) {
+                    const double df = __dsub_rn(t[k], mine[(size_t)k * MSD_THREADS]);
+                    sum = __dadd_rn(sum, __dmul_rn(df, df));
+                }
+            }
+            if (sum < best) { best = sum; arg = j0 + j; }  // NaN never wins; ties keep the first point
+        }
+    }
+    if (threadIdx.x < rows) {
+        if (gridDim.y > 1) {
+            if (best < INFINITY)
+                atomicMin(reinterpret_cast<unsigned long long*>(min_out + c0 + threadIdx.x),
+                          (unsigned long long)__double_as_longlong(best));
+        } else {
+            min_out[c0 + threadIdx.x] = best;
+            if (arg_out) arg_out[c0 + threadIdx.x] = arg;
+        }
+    }
+}
+
+__global__ void fill_inf_kernel(double* __restrict__ out, int64_t count) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) out[i] = INFINITY;
+}
+
+static size_t msd_smem(int d) { return sizeof(double) * (size_t)d * (MSD_THREADS + MSD_CHUNK); }
+
+static int launch_min_sqdist(const double* Xc, int64_t m, const double* X, int n, int d, double* min_out,
+                             int64_t* arg_out, cudaStream_t st) {
+    static bool configured = false;
+    if (!configured) {
+        TB_CUDA(cudaFuncSetAttribute(min_sqdist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)msd_smem(TB200_MAX_D)));
+        configured = true;
+    }
+    if (m <= 0) return 0;
+    // few candidates (one pipeline batch): split the points over blockIdx.y so the launch fills the machine
+    const int64_t ctas = (m + MSD_THREADS - 1) / MSD_THREADS;
+    int split = 1;
+    if (!arg_out && n > MSD_CHUNK && ctas < 8 * g_sm_count) {
+        const int64_t want = (8 * (int64_t)g_sm_count + ctas - 1) / ctas;
+        const int chunks = (n + MSD_CHUNK - 1) / MSD_CHUNK;
+        split = (int)(want < chunks ? want : chunks);
+    }
+    int jchunk = n > 0 ? ((n + split - 1) / split + MSD_CHUNK - 1) / MSD_CHUNK * MSD_CHUNK : MSD_CHUNK;
+    split = n > 0 ? (n + jchunk - 1) / jchunk : 1;
+    if (split > 1)
+        TB_LAUNCH(fill_inf_kernel, dim3((unsigned)((m + 255) / 256)), dim3(256), 0, st, min_out, m);
+    TB_LAUNCH(min_sqdist_kernel, dim3((unsigned)ctas, (unsigned)split), dim3(MSD_THREADS), msd_smem(d), st, Xc, m, X, n,
+              d, min_out, arg_out, jchunk);
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
 // variance, acquisition value and running argmax for one batch (single CTA)
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ double norm_cdf(double z) { return 0.5 * erfc(-z * 0.7071067811865476); }
@@ -377,7 +496,8 @@ __global__ void __launch_bounds__(EPI_THREADS) acquire_epilogue_kernel(
     int64_t m_valid, int64_t local_base, int64_t index_base, tb200_kernel_spec spec,
     const double* __restrict__ theta, tb200_acq_spec acq,
     double* __restrict__ mu_out, double* __restrict__ sigma_out, double* __restrict__ acq_out,
-    double* __restrict__ best_val, int64_t* __restrict__ best_idx) {
+    double* __restrict__ best_val, int64_t* __restrict__ best_idx, const double* __restrict__ min_sqdist,
+    double close_tol) {
     __shared__ double sv[EPI_THREADS / 32];
     __shared__ int64_t si[EPI_THREADS / 32];
     double bv = -INFINITY;
@@ -424,7 +544,9 @@ __global__ void __launch_bounds__(EPI_THREADS) acquire_epilogue_kernel(
         if (sigma_out) sigma_out[lc] = sigma;
         if (acq_out) acq_out[lc] = a;
         const int64_t gi = index_base + lc;
-        if (better(a, gi, bv, bi)) { bv = a; bi = gi; }
+        // a candidate within close_tol of an existing sample keeps its value in acq_out but cannot be selected
+        const bool too_close = min_sqdist != nullptr && min_sqdist[c] <= close_tol;
+        if (!too_close && better(a, gi, bv, bi)) { bv = a; bi = gi; }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -625,6 +747,7 @@ struct AcqBuffers {
     double* partial;  // [NB][batch]
     double* best_val; // [1] running best of this slot
     int64_t* best_idx;
+    double* mind;     // [batch]      smallest squared distance to an excluded point (tb200_exclusion)
 };
 
 static size_t a256(size_t b) { return (b + 255) / 256 * 256; }
@@ -654,7 +777,8 @@ static size_t acquire_layout(int n, int d, int64_t batch, AcqBuffers* ab, char* 
         double* Ks = take(use_i8 ? (size_t)i8::S * batch * NP : sizeof(double) * batch * NP);
         double* mean = take(sizeof(double) * KSPLIT_MAX * batch);
         double* partial = take(sizeof(double) * (use_i8 ? NP / i8::TN : NB) * batch);
-        if (ab) { ab[s].cand = cand; ab[s].Ks = Ks; ab[s].mean = mean; ab[s].partial = partial; }
+        double* mind = take(sizeof(double) * batch);
+        if (ab) { ab[s].cand = cand; ab[s].Ks = Ks; ab[s].mean = mean; ab[s].partial = partial; ab[s].mind = mind; }
     }
     // running best per epilogue CTA, all slots contiguous (one reset, one merge)
     const size_t nb = (size_t)(batch / EPI_THREADS);
@@ -726,7 +850,6 @@ static int acq_streams_for_device(AcqStreams** out) {
 // whose resident CTAs were launched with a small carve-out cannot take a 174 KB variance CTA until it has drained and
 // been reconfigured, which serialised the "concurrent" K* and variance kernels (tools/trace_acquire.py).
 static bool g_carveout_set[64] = {};
-static int g_sm_count = 148;
 static int configure_carveout() {
     int dev = 0;
     TB_CUDA(cudaGetDevice(&dev));
@@ -801,8 +924,10 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
                         const double* Linv, const I8Factor& f8, const double* alpha, int n,
                         const tb200_kernel_spec* spec, const double* theta, const tb200_acq_spec* acq, double* mu_out,
                         double* sigma_out, double* acq_out, double* best_val, int64_t* best_idx, int64_t batch,
-                        void* work, size_t work_bytes, void* stream) {
+                        void* work, size_t work_bytes, void* stream, const tb200_exclusion* excl = nullptr) {
     const bool use_i8 = f8.linvS != nullptr;
+    if (excl && (excl->n <= 0 || excl->tol < 0.0)) excl = nullptr;  // nothing to exclude / disabled (fallback.py:51-52)
+    TB_CHECK(!excl || excl->X, "exclusion: X is NULL");
     TB_CHECK(spec && acq && XsT && alpha && theta && best_val && best_idx && work, "NULL pointer argument");
     TB_CHECK(use_i8 ? f8.rowscale != nullptr : Linv != nullptr, "NULL factor pointer");
     TB_CHECK(spec->kind >= TB200_RBF && spec->kind <= TB200_MATERN52, "unknown kernel kind");
@@ -875,6 +1000,10 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
                       index_base + q.off, q.mb, w.cand);
             xc = w.cand;
         }
+        if (excl) {
+            double* mo = excl->min_out ? excl->min_out + q.off : w.mind;
+            if (launch_min_sqdist(xc, q.mb, excl->X, excl->n, d, mo, nullptr, s_small)) return -1;
+        }
         trace_mark(q.sl * 16 + 0, s_small);
         if (use_i8) {
             const size_t ksm8 = sizeof(double) * (CPB * d + (KS_THREADS / 32) * CPB);
@@ -934,7 +1063,8 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
         const AcqBuffers& w = ab[q.sl];
         TB_LAUNCH(acquire_epilogue_kernel, dim3((unsigned)(q.mbp / EPI_THREADS)), dim3(EPI_THREADS), 0, s_small, w.mean,
                   ksplit, w.partial, ntiles, (long)batch, q.mbp, q.mb, q.off, index_base, *spec, theta, *acq, mu_out,
-                  sigma_out, acq_out, w.best_val, w.best_idx);
+                  sigma_out, acq_out, w.best_val, w.best_idx,
+                  excl ? (excl->min_out ? excl->min_out + q.off : w.mind) : nullptr, excl ? excl->tol : 0.0);
         trace_mark(q.sl * 16 + 3, s_small);
         return 0;
     };
@@ -987,6 +1117,38 @@ int tb200_acquire_i8(const double* Xc, int64_t m, int64_t index_base, const tb20
     const I8Factor f8{linvS, rowscale, gmax};
     return acquire_impl(Xc, m, index_base, cand, XsT, nullptr, f8, alpha, n, spec, theta, acq, mu_out, sigma_out,
                         acq_out, best_val, best_idx, batch, work, work_bytes, stream);
+}
+
+// the same two calls with an exclusion set: candidates whose squared distance to any of excl->X's rows
+// is <= excl->tol (turbo/utils.py:111-130) are evaluated but never selected
+int tb200_acquire_excl(const tb200_exclusion* excl, const double* Xc, int64_t m, int64_t index_base,
+                       const tb200_cand_spec* cand, const double* XsT, const double* Linv, const double* alpha, int n,
+                       const tb200_kernel_spec* spec, const double* theta, const tb200_acq_spec* acq, double* mu_out,
+                       double* sigma_out, double* acq_out, double* best_val, int64_t* best_idx, int64_t batch,
+                       void* work, size_t work_bytes, void* stream) {
+    const I8Factor none{nullptr, nullptr, 0};
+    return acquire_impl(Xc, m, index_base, cand, XsT, Linv, none, alpha, n, spec, theta, acq, mu_out, sigma_out, acq_out,
+                        best_val, best_idx, batch, work, work_bytes, stream, excl);
+}
+
+int tb200_acquire_i8_excl(const tb200_exclusion* excl, const double* Xc, int64_t m, int64_t index_base,
+                          const tb200_cand_spec* cand, const double* XsT, const uint8_t* linvS, const double* rowscale,
+                          int gmax, const double* alpha, int n, const tb200_kernel_spec* spec, const double* theta,
+                          const tb200_acq_spec* acq, double* mu_out, double* sigma_out, double* acq_out,
+                          double* best_val, int64_t* best_idx, int64_t batch, void* work, size_t work_bytes,
+                          void* stream) {
+    TB_CHECK(linvS && rowscale, "NULL pointer argument");
+    const I8Factor f8{linvS, rowscale, gmax};
+    return acquire_impl(Xc, m, index_base, cand, XsT, nullptr, f8, alpha, n, spec, theta, acq, mu_out, sigma_out,
+                        acq_out, best_val, best_idx, batch, work, work_bytes, stream, excl);
+}
+
+int tb200_min_sqdist(const double* Xq, int64_t m, const double* X, int n, int d, double* min_out, int64_t* arg_out,
+                     void* stream) {
+    TB_CHECK((m <= 0 || (Xq && min_out)) && (n <= 0 || X), "NULL pointer argument");
+    TB_CHECK(d >= 1 && d <= TB200_MAX_D, "d out of range (1..64)");
+    TB_CHECK(n >= 0, "n negative");
+    return launch_min_sqdist(Xq, m, X, n, d, min_out, arg_out, (cudaStream_t)stream);
 }
 
 size_t tb200_acquire_i8_workspace_bytes(int n, int d, int64_t batch) {

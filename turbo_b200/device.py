@@ -172,9 +172,16 @@ class Acquirer:
     best on device.  engine: 'dmma' (FP64 tensor-core GEMM), 'i8' (INT8 tensor cores, 28 slice products),
     'i8x' (34 slice products), 'auto' (i8 when n <= I8_MAX_N = 32768)."""
 
-    def __init__(self, factor, acq_c, batch=0, engine=None):
+    def __init__(self, factor, acq_c, batch=0, engine=None, exclusion=None):
+        """exclusion: None or (X_dev (n,d) device tensor of UNSCALED points, tol): candidates whose squared distance to
+        a row of X is <= tol are never selected (tb200_exclusion; turbo/utils.py:111-130)"""
         lib = _lib.load()
         self.lib, self.f, self.acq_c = lib, factor, acq_c
+        self.excl_c, self._excl_X = None, None
+        if exclusion is not None and exclusion[1] >= 0 and exclusion[0].shape[0] > 0:
+            self._excl_X = exclusion[0].contiguous()
+            assert self._excl_X.shape[1] == factor.spec.d, 'different number of attributes'
+            self.excl_c = _lib.ExclusionC(_lib.ptr(self._excl_X), int(self._excl_X.shape[0]), float(exclusion[1]), None)
         self.engine = resolve_engine(engine, factor.NP)
         self.batch = int(batch) if batch else int(lib.tb200_default_batch(factor.n))
         if self.engine == "dmma":
@@ -195,16 +202,17 @@ class Acquirer:
     def run(self, Xc_dev, m, index_base=0, cand_c=None, mu=None, sigma=None, acq=None):
         """candidates [index_base, index_base+m): Xc_dev (m,d) device tensor, or generated from cand_c"""
         f = self.f
+        ex = C.byref(self.excl_c) if self.excl_c is not None else None
         if self.engine != "dmma":
-            _lib.check(self.lib.tb200_acquire_i8(
-                _lib.ptr(Xc_dev), int(m), int(index_base), C.byref(cand_c) if cand_c is not None else None,
+            _lib.check(self.lib.tb200_acquire_i8_excl(
+                ex, _lib.ptr(Xc_dev), int(m), int(index_base), C.byref(cand_c) if cand_c is not None else None,
                 _lib.ptr(f.XsT), _lib.ptr(f.linvS), _lib.ptr(f.rowscale), 8 if self.engine == "i8" else 9,
                 _lib.ptr(f.alpha), f.n, C.byref(self.spec_c), _lib.ptr(f.theta), C.byref(self.acq_c), _lib.ptr(mu),
                 _lib.ptr(sigma), _lib.ptr(acq), _lib.ptr(self.best_val), _lib.ptr(self.best_idx), self.batch,
                 _lib.ptr(self.work), self.nbytes, _lib.stream_ptr()))
             return
-        _lib.check(self.lib.tb200_acquire(
-            _lib.ptr(Xc_dev), int(m), int(index_base), C.byref(cand_c) if cand_c is not None else None,
+        _lib.check(self.lib.tb200_acquire_excl(
+            ex, _lib.ptr(Xc_dev), int(m), int(index_base), C.byref(cand_c) if cand_c is not None else None,
             _lib.ptr(f.XsT), _lib.ptr(f.Linv), _lib.ptr(f.alpha), f.n, C.byref(self.spec_c), _lib.ptr(f.theta),
             C.byref(self.acq_c), _lib.ptr(mu), _lib.ptr(sigma), _lib.ptr(acq), _lib.ptr(self.best_val),
             _lib.ptr(self.best_idx), self.batch, _lib.ptr(self.work), self.nbytes, _lib.stream_ptr()))
@@ -228,6 +236,23 @@ class Acquirer:
         v, i = v[keep], i[keep]
         order = np.lexsort((i, -v))
         return v[order], i[order]
+
+
+def min_sqdist(Xq, X, want_arg=False):
+    """smallest squared Euclidean distance from each row of Xq (m,d) to the rows of X (n,d), on the device
+    (tb200_min_sqdist; batched turbo/utils.py:111-130).  Host or device inputs; returns host arrays."""
+    lib = _lib.load()
+    Xq_dev = Xq if torch.is_tensor(Xq) else to_device(np.ascontiguousarray(Xq, dtype=np.float64))
+    X_dev = X if torch.is_tensor(X) else to_device(np.ascontiguousarray(X, dtype=np.float64))
+    assert Xq_dev.dim() == 2 and X_dev.dim() == 2, 'must be 2D arrays'
+    assert Xq_dev.shape[1] == X_dev.shape[1], 'different number of attributes'
+    m, d = Xq_dev.shape
+    dev = device()
+    out = torch.empty(m, dtype=torch.float64, device=dev)
+    arg = torch.empty(m, dtype=torch.int64, device=dev) if want_arg else None
+    _lib.check(lib.tb200_min_sqdist(_lib.ptr(Xq_dev), m, _lib.ptr(X_dev), int(X_dev.shape[0]), d, _lib.ptr(out),
+                                    _lib.ptr(arg), _lib.stream_ptr()))
+    return (out.cpu().numpy(), arg.cpu().numpy()) if want_arg else out.cpu().numpy()
 
 
 def acquisition_value_and_grad(factor, acq_c, X):
