@@ -402,3 +402,66 @@ def test_aux_optimiser_close_tolerance_never_returns_a_known_point():
     assert O.close_to_any(x_plain, X, 1e-10)      # the reference would now discard the trial (optimiser.py:349-352)
     assert not O.close_to_any(x_g, X, 1e-10)
     assert info["argmax_index"] >= n
+
+
+# ---------------------------------------------------------------------------------------------
+# the GPy-parametrised surrogate (turbo/modules/surrogates.py:84-222).  GPy is absent, so the checker is the
+# oracle's restatement of the same model (variance inside the kernel + Gaussian noise, no jitter, Standardize).
+# ---------------------------------------------------------------------------------------------
+def _gpy_problem(n=120, d=3, seed=2):
+    rng = np.random.default_rng(seed)
+    X = rng.random((n, d))
+    y = 3.0 + 2.0 * np.sin(3 * X.sum(1)) + 0.05 * rng.normal(size=n)
+    return rng, X, y
+
+
+def test_gpy_surrogate_fixed_parameters_match_the_restated_model():
+    import turbo_b200 as tb
+    rng, X, y = _gpy_problem()
+    params = np.array([1.3, 0.4, 0.5, 0.6, 1e-3])
+    k = tb.gpy_kernel('Matern52', ARD=True, variance=1.3, lengthscale=[0.4, 0.5, 0.6])
+    sur = tb.GpuGPySurrogate(model_params=dict(kernel=k, normalizer=True, noise_var=1e-3), training_iterations=0)
+    model, info = sur.construct_model(7, X, y)
+    assert info["iterations"] == 0
+    np.testing.assert_allclose(info["fixed"], params, rtol=1e-15)  # surrogates.py:176-177
+    assert model.get_hyper_param_names() == ["Mat52.variance", "Mat52.lengthscale[0]", "Mat52.lengthscale[1]",
+                                             "Mat52.lengthscale[2]", "Gaussian_noise.variance"]
+    np.testing.assert_allclose(model.get_hyper_params(), params, rtol=1e-14)
+    gp = O.FittedGP(O.KernelSpec(O.KIND_MATERN52, 3, True), np.log(params), X, y, normalize_y=True, alpha_jitter=0.0)
+    Xc = rng.random((1000, 3))
+    mu, sd = model.predict(Xc, return_std_dev=True)
+    omu, osd = gp.predict(Xc)
+    np.testing.assert_allclose(mu, omu, rtol=1e-8, atol=1e-8 * np.abs(omu).max())
+    np.testing.assert_allclose(sd, osd, rtol=1e-8, atol=1e-8 * osd.max())
+    assert sd.min() >= np.sqrt(1e-3) * gp.y_std * (1 - 1e-9)  # the noise term is part of the predictive variance
+    assert abs(model.get_log_likelihood() - gp.lml()) <= 1e-6 * abs(gp.lml())
+    assert model.predict(Xc).shape == (1000,)
+    # the default model: isotropic RBF, unit parameters, GPy's names
+    m2, _ = tb.GpuGPySurrogate(training_iterations=0).construct_model(0, X, y)
+    assert m2.get_hyper_param_names() == ["rbf.variance", "rbf.lengthscale", "Gaussian_noise.variance"]
+    np.testing.assert_allclose(m2.get_hyper_params(), [1.0, 1.0, 1.0], rtol=1e-15)
+    import pickle
+    m3 = pickle.loads(pickle.dumps(model))  # recorder.py:141-146 keeps every model
+    np.testing.assert_allclose(m3.predict(Xc[:10]), mu[:10], rtol=1e-12)
+    with pytest.raises(NotImplementedError):
+        tb.GpuGPySurrogate(sparse=True, model_params=dict(kernel=k))
+
+
+def test_gpy_surrogate_restarts_and_parameter_continuity():
+    import turbo_b200 as tb
+    rng, X, y = _gpy_problem(n=80)
+    sur = tb.GpuGPySurrogate(training_iterations=lambda t: 4 if t == 0 else 1, seed=3)
+    m0, info0 = sur.construct_model(0, X[:70], y[:70])
+    assert info0["iterations"] == 4 and info0["restarts"] == 4  # restarts == iterations (surrogates.py:185-186)
+    start = tb.GpuGPySurrogate(training_iterations=0).construct_model(0, X[:70], y[:70])[0]
+    assert m0.get_log_likelihood() > start.get_log_likelihood()  # better than GPy's unit starting parameters
+    # the optimum is a stationary point of the restated objective
+    gp = O.FittedGP(O.KernelSpec(O.KIND_RBF, 3, False), np.log(m0.get_hyper_params()), X[:70], y[:70], True, 0.0)
+    lml, grad = gp.lml(eval_gradient=True)
+    assert abs(lml - m0.get_log_likelihood()) <= 1e-6 * abs(lml)
+    assert np.abs(grad).max() < 1e-2
+    # next trial: one restart, started from the stored parameter array (surrogates.py:171-173)
+    m1, info1 = sur.construct_model(1, X, y)
+    assert info1["restarts"] == 1
+    np.testing.assert_allclose(sur._last_model_params, m1.get_hyper_params(), rtol=1e-14)
+    assert np.all(np.abs(np.log(m1.get_hyper_params() / m0.get_hyper_params())) < 1.0)

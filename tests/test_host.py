@@ -227,6 +227,10 @@ def test_plugins_subclass_the_reference_classes_when_turbo_is_importable():
     assert issubclass(tb.GpuEI, api.EI) and issubclass(tb.GpuPI, api.PI) and issubclass(tb.GpuUCB, api.UCB)
     assert issubclass(tb.GpuGPSurrogate, api.Surrogate)
     assert issubclass(tb.GpuGPSurrogate.ModelInstance, api.SciKitModelInstance)
+    # the GPy flavour answers plotting's GPySurrogate.ModelInstance check (plotting/surrogates.py:71), never the sklearn one
+    assert issubclass(tb.GpuGPySurrogate, api.Surrogate)
+    assert issubclass(tb.GpuGPySurrogate.ModelInstance, api.GPyModelInstance)
+    assert tb.GpuGPySurrogate.ModelInstance.__mro__[1] is tb.GpuGPSurrogate.ModelInstance.__mro__[1]  # one device model
     assert tb.GpuEI(0.01).get_type() == "improvement" and tb.GpuUCB(2.0).get_type() == "optimism"
     assert tb.GpuEI(lambda t: 0.1 * t).xi(3) == pytest.approx(0.3)
     if os.path.isdir("/root/reference"):  # build container only: the real classes
@@ -236,3 +240,36 @@ def test_plugins_subclass_the_reference_classes_when_turbo_is_importable():
         import turbo.modules as tm
         importlib.reload(api)
         assert api.HAVE_TURBO and api.EI is tm.EI and api.SciKitModelInstance is tm.SciKitGPSurrogate.ModelInstance
+        assert api.GPyModelInstance is tm.GPySurrogate.ModelInstance
+        assert not issubclass(api.GPyModelInstance, api.SciKitModelInstance)
+
+
+def test_gpy_surrogate_arguments_follow_the_reference():
+    """turbo/modules/surrogates.py:101-158: same constructor arguments, same assertions, no device needed"""
+    import turbo_b200 as tb
+    from turbo_b200 import gpy_surrogate as G
+    s = tb.GpuGPySurrogate()
+    assert s.model_params == {'normalizer': True} and s.training_iterations == 10 and s.param_continuity
+    assert s._get_training_iterations(3) == 10
+    assert tb.GpuGPySurrogate(training_iterations=lambda t: [10, 5, 2][t % 3])._get_training_iterations(4) == 5
+    assert tb.GpuGPySurrogate(training_iterations=None,
+                              optimise_params={'num_restarts': 7})._get_training_iterations(0) == 7
+    with pytest.raises(AssertionError):  # :138-139
+        tb.GpuGPySurrogate(training_iterations=3, optimise_params={'num_restarts': 7})
+    with pytest.raises(AssertionError):  # :156
+        tb.GpuGPySurrogate(training_iterations=None)._get_training_iterations(0)
+    with pytest.raises(NotImplementedError):
+        tb.GpuGPySurrogate(sparse=True)
+    with pytest.raises(ValueError):
+        tb.GpuGPySurrogate(model_params={'inference_method': None})
+    spec, prefix, params = G._describe_kernel(None, 4)  # GPRegression's default kernel: isotropic RBF, unit parameters
+    assert (spec.kind, spec.ard, spec.has_const, spec.has_white, prefix) == (0, False, True, True, 'rbf')
+    np.testing.assert_array_equal(params, [1.0, 1.0])
+    spec, prefix, params = G._describe_kernel(tb.gpy_kernel('Mat32', ARD=True, variance=2.0, lengthscale=0.3), 3)
+    assert (spec.kind, spec.ard, prefix) == (2, True, 'Mat32')
+    np.testing.assert_array_equal(params, [2.0, 0.3, 0.3, 0.3])
+
+    class Exponential:  # duck-typed GPy kernel object
+        ARD, variance, lengthscale = False, np.array([0.5]), np.array([2.0])
+    spec, prefix, params = G._describe_kernel(Exponential(), 2)
+    assert (spec.kind, prefix) == (1, 'Exponential') and list(params) == [0.5, 2.0]

@@ -12,6 +12,7 @@ try:  # pragma: no cover - depends on the environment
     HAVE_TURBO = True
     Surrogate = _tm.Surrogate
     SciKitModelInstance = _tm.SciKitGPSurrogate.ModelInstance
+    GPyModelInstance = _tm.GPySurrogate.ModelInstance  # defined even when GPy itself is missing
     EI, PI, UCB = _tm.EI, _tm.PI, _tm.UCB
 except Exception:  # turbo (or one of its imports) is not available
     HAVE_TURBO = False
@@ -36,6 +37,9 @@ except Exception:  # turbo (or one of its imports) is not available
                 raise NotImplementedError()
 
     SciKitModelInstance = Surrogate.ModelInstance
+
+    class GPyModelInstance(Surrogate.ModelInstance):
+        """turbo/modules/surrogates.py:199-220"""
 
     class _AcquisitionFunction:
         """turbo/modules/acquisition_functions.py:12-77"""

@@ -51,6 +51,95 @@ def _resolve_kernel(kernel, d):
     return kernels.from_sklearn(kernel, d)
 
 
+class _DeviceModelInstance:
+    """surrogates.py:328-365 contract; holds only NumPy state + lazily built device buffers.  The reference base
+    class (scikit-learn or GPy flavour) is mixed in by the surrogate that builds it."""
+
+    def __init__(self, spec, theta, X, y_n, y_mean, y_std, jitter, device_inputs=None, variance_engine=None,
+                 factor=None):
+        self.variance_engine = variance_engine
+        self.spec, self.theta = spec, np.asarray(theta, dtype=np.float64).copy()
+        self.X, self.y_n = X, y_n
+        self.y_mean, self.y_std, self.jitter = float(y_mean), float(y_std), float(jitter)
+        self.model = self  # the reference exposes the sklearn estimator here; plotting only calls predict
+        self._factor = None
+        self._log_likelihood = None
+        if factor is not None:  # an incrementally updated factor handed over by the surrogate
+            self._factor, self._log_likelihood = factor, factor.lml
+        else:
+            self._build(device_inputs)
+
+    # --- device state -------------------------------------------------------------------
+    def _build(self, device_inputs=None):
+        X_dev, yn_dev = device_inputs or (device.to_device(self.X), device.to_device(self.y_n))
+        f = device.Factor(X_dev, yn_dev, self.X.shape[0], self.spec, self.theta, self.jitter)
+        if f.info != 0:
+            # sklearn raises from the final factorisation (sklearn:_gpr.py:351-362)
+            raise np.linalg.LinAlgError(
+                "The kernel, %r, is not returning a positive definite matrix (pivot %d). Try gradually "
+                "increasing the 'alpha' parameter." % (self.spec, f.info))
+        self._factor, self._log_likelihood = f, f.lml
+        return f
+
+    @property
+    def factor(self):
+        return self._factor if self._factor is not None else self._build()
+
+    def release(self):
+        """free the O(n^2) device buffers (rebuilt on demand); the Recorder keeps every trial's
+        model alive (optimiser.py:343), so the aux-optimiser calls this after choosing a point"""
+        self._factor = None
+
+    def __getstate__(self):
+        s = dict(self.__dict__)
+        s['_factor'] = None
+        s['model'] = None
+        return s
+
+    def __setstate__(self, s):
+        self.__dict__.update(s)
+        self.model = self
+
+    # --- reference contract ---------------------------------------------------------------
+    def predict(self, X, return_std_dev=False, return_std=None):
+        """mus (m,) [, sigmas (m,)] as NumPy (surrogates.py:332-338)"""
+        if return_std is not None:  # sklearn spelling, for callers that hold `.model`
+            return_std_dev = return_std
+        import torch
+        X = np.ascontiguousarray(np.atleast_2d(X), dtype=np.float64)
+        m = X.shape[0]
+        assert X.shape[1] == self.spec.d, 'X has the wrong number of columns'
+        dev = device.device()
+        mu = torch.empty(m, dtype=torch.float64, device=dev)
+        sigma = torch.empty(m, dtype=torch.float64, device=dev)
+        acq_c = device.acq_spec(_lib.ACQ_UCB, 1.0, 0.0, 0.0, self.y_mean, self.y_std)
+        a = device.Acquirer(self.factor, acq_c, engine=getattr(self, 'variance_engine', None))
+        a.run(device.to_device(X), m, 0, None, mu=mu, sigma=sigma)
+        if return_std_dev:
+            return mu.cpu().numpy(), sigma.cpu().numpy()
+        return mu.cpu().numpy()
+
+    def get_hyper_params(self):
+        return np.exp(self.theta)
+
+    def get_hyper_param_names(self):
+        return self.spec.names()
+
+    def get_log_likelihood(self):
+        if self._log_likelihood is None:
+            self._build()
+        return self._log_likelihood
+
+    def log_marginal_likelihood(self, theta=None, eval_gradient=False):
+        """GaussianProcessRegressor.log_marginal_likelihood (sklearn:_gpr.py:541-656) on the device"""
+        if theta is None and not eval_gradient:
+            return self.get_log_likelihood()
+        th = self.theta if theta is None else np.asarray(theta, dtype=np.float64)
+        lml, grad, info = device.lml_batched(device.to_device(self.X), device.to_device(self.y_n),
+                                             self.X.shape[0], self.spec, th[None, :], self.jitter, eval_gradient)
+        return (float(lml[0]), grad[0]) if eval_gradient else float(lml[0])
+
+
 class GpuGPSurrogate(Surrogate):
     default_model_params = {'kernel': 'default', 'normalize_y': True}
 
@@ -197,89 +286,5 @@ class GpuGPSurrogate(Surrogate):
         return theta, {'restarts': R, 'lml_evaluations': int(n_eval), 'optimiser_iterations': iters.tolist(),
                        'best_neg_lml': best_f}
 
-    class ModelInstance(SciKitModelInstance):
-        """surrogates.py:328-365 contract; holds only NumPy state + lazily built device buffers."""
-
-        def __init__(self, spec, theta, X, y_n, y_mean, y_std, jitter, device_inputs=None, variance_engine=None,
-                     factor=None):
-            self.variance_engine = variance_engine
-            self.spec, self.theta = spec, np.asarray(theta, dtype=np.float64).copy()
-            self.X, self.y_n = X, y_n
-            self.y_mean, self.y_std, self.jitter = float(y_mean), float(y_std), float(jitter)
-            self.model = self  # the reference exposes the sklearn estimator here; plotting only calls predict
-            self._factor = None
-            self._log_likelihood = None
-            if factor is not None:  # an incrementally updated factor handed over by the surrogate
-                self._factor, self._log_likelihood = factor, factor.lml
-            else:
-                self._build(device_inputs)
-
-        # --- device state -------------------------------------------------------------------
-        def _build(self, device_inputs=None):
-            X_dev, yn_dev = device_inputs or (device.to_device(self.X), device.to_device(self.y_n))
-            f = device.Factor(X_dev, yn_dev, self.X.shape[0], self.spec, self.theta, self.jitter)
-            if f.info != 0:
-                # sklearn raises from the final factorisation (sklearn:_gpr.py:351-362)
-                raise np.linalg.LinAlgError(
-                    "The kernel, %r, is not returning a positive definite matrix (pivot %d). Try gradually "
-                    "increasing the 'alpha' parameter." % (self.spec, f.info))
-            self._factor, self._log_likelihood = f, f.lml
-            return f
-
-        @property
-        def factor(self):
-            return self._factor if self._factor is not None else self._build()
-
-        def release(self):
-            """free the O(n^2) device buffers (rebuilt on demand); the Recorder keeps every trial's
-            model alive (optimiser.py:343), so the aux-optimiser calls this after choosing a point"""
-            self._factor = None
-
-        def __getstate__(self):
-            s = dict(self.__dict__)
-            s['_factor'] = None
-            s['model'] = None
-            return s
-
-        def __setstate__(self, s):
-            self.__dict__.update(s)
-            self.model = self
-
-        # --- reference contract ---------------------------------------------------------------
-        def predict(self, X, return_std_dev=False, return_std=None):
-            """mus (m,) [, sigmas (m,)] as NumPy (surrogates.py:332-338)"""
-            if return_std is not None:  # sklearn spelling, for callers that hold `.model`
-                return_std_dev = return_std
-            import torch
-            X = np.ascontiguousarray(np.atleast_2d(X), dtype=np.float64)
-            m = X.shape[0]
-            assert X.shape[1] == self.spec.d, 'X has the wrong number of columns'
-            dev = device.device()
-            mu = torch.empty(m, dtype=torch.float64, device=dev)
-            sigma = torch.empty(m, dtype=torch.float64, device=dev)
-            acq_c = device.acq_spec(_lib.ACQ_UCB, 1.0, 0.0, 0.0, self.y_mean, self.y_std)
-            a = device.Acquirer(self.factor, acq_c, engine=getattr(self, 'variance_engine', None))
-            a.run(device.to_device(X), m, 0, None, mu=mu, sigma=sigma)
-            if return_std_dev:
-                return mu.cpu().numpy(), sigma.cpu().numpy()
-            return mu.cpu().numpy()
-
-        def get_hyper_params(self):
-            return np.exp(self.theta)
-
-        def get_hyper_param_names(self):
-            return self.spec.names()
-
-        def get_log_likelihood(self):
-            if self._log_likelihood is None:
-                self._build()
-            return self._log_likelihood
-
-        def log_marginal_likelihood(self, theta=None, eval_gradient=False):
-            """GaussianProcessRegressor.log_marginal_likelihood (sklearn:_gpr.py:541-656) on the device"""
-            if theta is None and not eval_gradient:
-                return self.get_log_likelihood()
-            th = self.theta if theta is None else np.asarray(theta, dtype=np.float64)
-            lml, grad, info = device.lml_batched(device.to_device(self.X), device.to_device(self.y_n),
-                                                 self.X.shape[0], self.spec, th[None, :], self.jitter, eval_gradient)
-            return (float(lml[0]), grad[0]) if eval_gradient else float(lml[0])
+    class ModelInstance(_DeviceModelInstance, SciKitModelInstance):
+        """isinstance(model, turbo.modules.SciKitGPSurrogate.ModelInstance) holds (plotting/surrogates.py:67-75)"""
