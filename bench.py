@@ -337,7 +337,7 @@ def run_ours(args):
     e1.record()
     torch.cuda.synchronize()
     fit = {"lml_grad_batched_ms": min(fit_ms[1:]), "restarts": R, "restarts_per_gpu": Rl,
-           "engine": "i8 (potrf column updates, trtri, K^-1 on tcgen05 kind::i8, 34 slice products) when the batch is "
+           "engine": "i8 (potrf column updates, trtri, K^-1 on tcgen05 kind::i8, 28/28/21 slice products) when the batch is "
                      "large enough for the left-looking schedule, else FP64 DMMA; TB200_FIT_ENGINE=dmma forces DMMA",
            "flop_per_evaluation": float(n) ** 3 + float(n) ** 2 * (3 * d + 42),
            "tflops": Rl * (float(n) ** 3 + float(n) ** 2 * (3 * d + 42)) / (min(fit_ms[1:]) * 1e-3) / 1e12,

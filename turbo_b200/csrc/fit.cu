@@ -655,18 +655,35 @@ struct FitBuffers {
     uint8_t* bpanel; // [R][7][2][NP/64][4096] byte slices of one weighted L panel (B operand of the trtri step)
 };
 
-// slice products kept by the fit GEMMs: 9 (34 products, as accurate as the FP64 GEMM it replaces; default) or
-// 8 (28 products, TB200_FIT_GMAX=8)
-static int fit_gmax() {
-    static int g = 0;
-    if (!g) {
-        const char* e = getenv("TB200_FIT_GMAX");
-        g = (e && atoi(e) == 8) ? 8 : 9;
+// slice products kept by the fit GEMMs, per stage: 9 (34 products, truncation 2^-64: below FP64 rounding), 8 (28
+// products, 2^-56: the size of FP64 rounding itself) or 7 (21 products, 2^-48).  Defaults: Cholesky column update 8 (its
+// error is amplified by the rest of the factorisation: 7 costs three digits of the LML on ill-conditioned members),
+// inverse factor 8, K^-1 = Linv^T Linv 7 (feeds only the gradient: 1.7e-10 of max|grad|).  Measured against the FP64
+// DMMA path in profiles/r1_fit_precision.md.  TB200_FIT_GMAX sets all three stages, TB200_FIT_GMAX_TRTRI /
+// TB200_FIT_GMAX_KINV one stage.
+enum FitStage { FIT_POTRF = 0, FIT_TRTRI = 1, FIT_KINV = 2 };
+static int fit_gmax(int stage) {
+    static int g[3] = {0, 0, 0};
+    if (!g[0]) {
+        const int dflt[3] = {8, 8, 7};
+        const char* names[3] = {nullptr, "TB200_FIT_GMAX_TRTRI", "TB200_FIT_GMAX_KINV"};
+        const char* all = getenv("TB200_FIT_GMAX");
+        for (int s = 2; s >= 0; --s) {
+            int v = dflt[s];
+            if (all && atoi(all) >= 7 && atoi(all) <= 9) v = atoi(all);
+            const char* e = names[s] ? getenv(names[s]) : nullptr;
+            if (e && atoi(e) >= 7 && atoi(e) <= 9) v = atoi(e);
+            g[s] = v;
+        }
     }
-    return g;
+    return g[stage];
 }
-static int launch_fit_gemm_i8(const i8::GemmI8Params& g, int ntiles, int R, cudaStream_t st) {
-    return fit_gmax() == 8 ? i8::launch_gemm_i8<8>(g, ntiles, R, st) : i8::launch_gemm_i8<9>(g, ntiles, R, st);
+static int launch_fit_gemm_i8(const i8::GemmI8Params& g, int ntiles, int R, cudaStream_t st, int stage) {
+    switch (fit_gmax(stage)) {
+        case 7: return i8::launch_gemm_i8<7>(g, ntiles, R, st);
+        case 8: return i8::launch_gemm_i8<8>(g, ntiles, R, st);
+        default: return i8::launch_gemm_i8<9>(g, ntiles, R, st);
+    }
 }
 
 static size_t align256(size_t b) { return (b + 255) / 256 * 256; }
@@ -811,15 +828,15 @@ static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStr
             if (NB - k > 1 && !fit_streams_for_device(&fs)) {
                 TB_CUDA(cudaEventRecord(fs->fork, st));
                 TB_CUDA(cudaStreamWaitEvent(fs->side, fs->fork, 0));
-                if (launch_fit_gemm_i8(g, 2, R, fs->side)) return -1;           // diagonal tile (it = k)
+                if (launch_fit_gemm_i8(g, 2, R, fs->side, FIT_POTRF)) return -1;           // diagonal tile (it = k)
                 if (launch_diag(fb, NP, R, k, info, fs->side)) return -1;
                 TB_CUDA(cudaEventRecord(fs->join, fs->side));
                 g.rowTile0 = k + 1;
-                if (launch_fit_gemm_i8(g, (NB - k - 1) * 2, R, st)) return -1;  // rows below
+                if (launch_fit_gemm_i8(g, (NB - k - 1) * 2, R, st, FIT_POTRF)) return -1;  // rows below
                 TB_CUDA(cudaStreamWaitEvent(st, fs->join, 0));
                 diag_done = true;
             } else {
-                if (launch_fit_gemm_i8(g, (NB - k) * 2, R, st)) return -1;
+                if (launch_fit_gemm_i8(g, (NB - k) * 2, R, st, FIT_POTRF)) return -1;
             }
         } else if (left && k > 0) {
             // block column k: A[i,k] -= L[i,0:k] L[k,0:k]^T  (i >= k), K = k*128 accumulated in registers
@@ -915,7 +932,7 @@ static int trtri_batched_i8(const FitBuffers& fb, double* Linv, int NP, int R, c
             g.kblks = kblks; g.tri = 0;
             g.rowTile0 = c1; g.colTile0 = 2 * c; g.nColTiles = 2; g.kbLo = 2 * c1; g.kbHi = kblks; g.kbHiByRow = 1;
             g.alpha = -1.0; g.beta = 0.0;
-            if (launch_fit_gemm_i8(g, rem * 2, R, st)) return -1;
+            if (launch_fit_gemm_i8(g, rem * 2, R, st, FIT_TRTRI)) return -1;
         }
         // X[i, c-block] = T[i, c-block] * Dinv_c  (in place, 128-deep DMMA GEMM)
         {
@@ -1025,7 +1042,7 @@ static int fit_pipeline(const double* X, const double* y_n, int n, const tb200_k
             g.C = fb.K; g.ldc = NP; g.cStride = sK;
             g.kblks = NP / i8::KB; g.tri = 1;
             g.alpha = 1.0; g.beta = 0.0;
-            if (launch_fit_gemm_i8(g, NB * (NB + 1), R, st)) return -1;
+            if (launch_fit_gemm_i8(g, NB * (NB + 1), R, st, FIT_KINV)) return -1;
         } else {
             GemmParams q = gemm_params(Linv, NP, Linv, NP, fb.K, NP, NP / TILE, NP / TILE, NP, 1.0, 0.0);
             q.order = ORDER_LOWER;
