@@ -266,8 +266,10 @@ __global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_kernel(
 #pragma unroll
             for (int q = 0; q < KS_JG; q += 2) {
                 const double2 a = __ldg(al + (q >> 1));
-                const double g0 = (j0 + q < n) ? shape_fn(KIND, r2[q]) : 0.0;
-                const double g1 = (j0 + q + 1 < n) ? shape_fn(KIND, r2[q + 1]) : 0.0;
+                // evaluated for the padding rows too and masked afterwards: straight-line code over the 16 pairs
+                const double s0 = shape_fn(KIND, r2[q]), s1 = shape_fn(KIND, r2[q + 1]);
+                const double g0 = (j0 + q < n) ? s0 : 0.0;
+                const double g1 = (j0 + q + 1 < n) ? s1 : 0.0;
                 msum = fma(sf2 * g0, a.x, msum);
                 msum = fma(sf2 * g1, a.y, msum);
                 // 56-bit fixed point of g in [0,1] (see slice_unsigned): its bytes are the 7 digits

@@ -69,31 +69,79 @@ __device__ inline double length_scale(const tb200_kernel_spec& s, const double* 
     return exp(theta[(s.has_const ? 1 : 0) + (s.ard ? k : 0)]);
 }
 
+// Branch-free sqrt and exp(-t) for the pair loops.  The library versions carry slow-path branches and calls (denormals,
+// overflow) that end a basic block per evaluation, so the 16 independent evaluations of an unrolled pair loop ran one
+// after the other on their dependent chains; these two are straight-line code the compiler interleaves.
+// sqrt_pos: a >= 0.  Single-precision reciprocal square root, two coupled Newton steps (2^-22 -> 2^-44 -> 2^-88) and a
+// residual correction: <= 1 ulp.  a < 1e-30 returns a*1e15 (a value below 1e-15, where every caller's result is 1 to
+// working precision); a > 1e36 returns 1e18 (every caller's result is 0 there); NaN propagates.
+__device__ __forceinline__ double sqrt_pos(double a) {
+    const float af = fminf(fmaxf((float)a, 1e-30f), 1e37f);
+    const double y = (double)rsqrtf(af);
+    double g = a * y, h = 0.5 * y;
+    double r = fma(-g, h, 0.5);
+    g = fma(g, r, g);
+    h = fma(h, r, h);
+    r = fma(-g, h, 0.5);
+    g = fma(g, r, g);
+    h = fma(h, r, h);
+    g = fma(fma(-g, g, a), h, g);
+    return a > 1e36 ? 1e18 : g;
+}
+// exp_neg(t) = exp(-t), t >= 0: k = round(-t / ln 2) by the 1.5 * 2^52 shift, two-term Cody-Waite reduction, degree-13
+// Taylor polynomial on |r| <= ln(2)/2 (remainder 4e-18), scaling through the exponent field.  Results below 2^-1021
+// are flushed to 0 (absolute error 5e-308).  About 1 ulp; NaN propagates.
+__device__ __forceinline__ double exp_neg(double t) {
+    const double x = -(t > 750.0 ? 750.0 : t);
+    const double kd = fma(x, 1.4426950408889634, 6755399441055744.0);
+    const int k = __double2loint(kd);
+    const double kf = kd - 6755399441055744.0;
+    double r = fma(kf, -6.93147180369123816490e-01, x);
+    r = fma(kf, -1.90821492927058770002e-10, r);
+    double p = 1.6059043836821613e-10;              // 1/13!
+    p = fma(p, r, 2.08767569878681e-09);            // 1/12!
+    p = fma(p, r, 2.505210838544172e-08);           // 1/11!
+    p = fma(p, r, 2.755731922398589e-07);           // 1/10!
+    p = fma(p, r, 2.7557319223985893e-06);          // 1/9!
+    p = fma(p, r, 2.48015873015873e-05);            // 1/8!
+    p = fma(p, r, 1.984126984126984e-04);           // 1/7!
+    p = fma(p, r, 1.388888888888889e-03);           // 1/6!
+    p = fma(p, r, 8.333333333333333e-03);           // 1/5!
+    p = fma(p, r, 4.1666666666666664e-02);          // 1/4!
+    p = fma(p, r, 1.6666666666666666e-01);          // 1/3!
+    p = fma(p, r, 0.5);
+    p = fma(p, r, 1.0);
+    p = fma(p, r, 1.0);
+    const double scaled = __hiloint2double(__double2hiint(p) + (k << 20), __double2loint(p));
+    const double v = k < -1020 ? 0.0 : scaled;
+    return t != t ? t : v;
+}
+
 // stationary shape g as a function of the squared scaled distance r2 (sklearn:kernels.py:1561-1570,
 // :1722-1729).  Matern families take sqrt first, exactly as cdist/pdist 'euclidean' does.
 __device__ __forceinline__ double shape_fn(int kind, double r2) {
-    if (kind == TB200_RBF) return exp(-0.5 * r2);
-    const double r = sqrt(r2);
-    if (kind == TB200_MATERN12) return exp(-r);
+    if (kind == TB200_RBF) return exp_neg(0.5 * r2);
+    const double r = sqrt_pos(r2);
+    if (kind == TB200_MATERN12) return exp_neg(r);
     if (kind == TB200_MATERN32) {
         const double t = r * 1.7320508075688772;  // math.sqrt(3)
-        return (1.0 + t) * exp(-t);
+        return (1.0 + t) * exp_neg(t);
     }
     const double t = r * 2.23606797749979;  // math.sqrt(5)
-    return (1.0 + t + t * t * (1.0 / 3.0)) * exp(-t);  // sklearn divides by 3.0: <= 1 ulp apart
+    return (1.0 + t + t * t * (1.0 / 3.0)) * exp_neg(t);  // sklearn divides by 3.0: <= 1 ulp apart
 }
 
 // h(r2) with dK/dlog(l_k) = sf2 * h * D_k, D_k = ((x_k - x'_k)/l_k)^2 (sklearn:kernels.py:1581-1584,
 // :1757-1771)
 __device__ __forceinline__ double shape_grad_fn(int kind, double r2) {
-    if (kind == TB200_RBF) return exp(-0.5 * r2);
+    if (kind == TB200_RBF) return exp_neg(0.5 * r2);
     if (kind == TB200_MATERN12) {
-        const double r = sqrt(r2);
-        return r != 0.0 ? exp(-r) / r : 0.0;
+        const double r = sqrt_pos(r2);
+        return r2 != 0.0 ? exp_neg(r) / r : 0.0;
     }
-    if (kind == TB200_MATERN32) return 3.0 * exp(-sqrt(3.0 * r2));
-    const double t = sqrt(5.0 * r2);
-    return 5.0 / 3.0 * (t + 1.0) * exp(-t);
+    if (kind == TB200_MATERN32) return 3.0 * exp_neg(sqrt_pos(3.0 * r2));
+    const double t = sqrt_pos(5.0 * r2);
+    return 5.0 / 3.0 * (t + 1.0) * exp_neg(t);
 }
 
 __device__ __forceinline__ double warp_sum(double v) {

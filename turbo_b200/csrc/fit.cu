@@ -272,19 +272,19 @@ __global__ void lml_kernel(const double* __restrict__ y, long strideY, const dou
 template <int KIND>
 __device__ __forceinline__ void shape_pair(double r2, double& g, double& h) {
     if (KIND == TB200_RBF) {
-        g = h = exp(-0.5 * r2);
+        g = h = exp_neg(0.5 * r2);
     } else if (KIND == TB200_MATERN12) {
-        const double r = sqrt(r2);
-        g = exp(-r);
-        h = r != 0.0 ? g / r : 0.0;
+        const double r = sqrt_pos(r2);
+        g = exp_neg(r);
+        h = r2 != 0.0 ? g / r : 0.0;
     } else if (KIND == TB200_MATERN32) {
-        const double t = sqrt(3.0 * r2);  // shape_grad_fn's form; shape_fn's r*sqrt(3) differs by <= 1 ulp
-        const double e = exp(-t);
+        const double t = sqrt_pos(3.0 * r2);  // shape_grad_fn's form; shape_fn's r*sqrt(3) differs by <= 1 ulp
+        const double e = exp_neg(t);
         g = (1.0 + t) * e;
         h = 3.0 * e;
     } else {
-        const double t = sqrt(5.0 * r2);
-        const double e = exp(-t);
+        const double t = sqrt_pos(5.0 * r2);
+        const double e = exp_neg(t);
         g = (1.0 + t + t * t * (1.0 / 3.0)) * e;
         h = 5.0 / 3.0 * (t + 1.0) * e;
     }
