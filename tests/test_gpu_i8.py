@@ -1,6 +1,8 @@
 """INT8 tensor-core variance engine (csrc/ozaki_i8.cuh) against the DMMA engine, the oracle and the golden
 vectors: same tolerances as the FP64 path (mean/variance/acquisition 1e-8 relative with the documented
 absolute variance floor; argmax exact)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -147,3 +149,74 @@ def test_max_dimension_lml_and_gradient():
         ol, og = O.log_marginal_likelihood(O.KernelSpec(3, d, True), T[r], X, y, 1e-10, True)
         assert lml[r] == pytest.approx(ol, rel=1e-6)
         np.testing.assert_allclose(grad[r], og, rtol=1e-6, atol=1e-6 * np.abs(og).max())
+
+
+_FIT_CHILD = r"""
+import json, sys
+import os
+
+import numpy as np
+sys.path.insert(0, %(root)r)
+import turbo_b200 as tb
+from turbo_b200 import device
+rng = np.random.default_rng(%(seed)d)
+n, d, R = %(n)d, %(d)d, %(R)d
+X = rng.random((n, d))
+y = np.sin(3 * X.sum(1)) + 0.01 * rng.standard_normal(n)
+y = (y - y.mean()) / y.std()
+spec = tb.KernelSpec(3, d, True)
+T = np.log(np.r_[1.0, np.full(d, 0.3), 1e-3]) + rng.normal(0, 0.2, (R, d + 2))
+X_dev, y_dev = device.to_device(X), device.to_device(y)
+out = {}
+if R > 1:
+    lml, grad, info = device.lml_batched(X_dev, y_dev, n, spec, T, 1e-10)
+    out.update(lml=lml.tolist(), grad=grad.tolist(), info=info.tolist())
+else:
+    f = device.Factor(X_dev, y_dev, n, spec, T[0], 1e-10)
+    acq_c = device.acq_spec(2, 1.0, 0.0, 0.0, 0.0, 1.0)
+    import torch
+    Xc = device.to_device(rng.random((256, d)))
+    mu = torch.empty(256, dtype=torch.float64, device=Xc.device)
+    sg = torch.empty(256, dtype=torch.float64, device=Xc.device)
+    device.Acquirer(f, acq_c, engine="dmma").run(Xc, 256, 0, None, mu=mu, sigma=sg)
+    out.update(lml=float(f.lml), info=int(f.info), mu=mu.cpu().tolist(), sigma=sg.cpu().tolist())
+print("RESULT" + json.dumps(out))
+"""
+
+
+def _fit_in_child(engine, **kw):
+    import json
+    import subprocess
+    import sys
+    env = dict(os.environ)
+    env.pop("TB200_FIT_ENGINE", None)
+    if engine == "dmma":
+        env["TB200_FIT_ENGINE"] = "dmma"
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    res = subprocess.run([sys.executable, "-c", _FIT_CHILD % dict(root=root, **kw)], env=env, capture_output=True,
+                         text=True, timeout=600)
+    assert res.returncode == 0, res.stderr[-2000:]
+    line = [ln for ln in res.stdout.splitlines() if ln.startswith("RESULT")][-1]
+    return json.loads(line[len("RESULT"):])
+
+
+def test_batched_fit_beyond_one_int32_window_matches_dmma():
+    """n > 8192: the fit GEMMs cut their k-ranges into exact INT32 windows of 8192 terms (ozaki_gemm.cuh); the whole
+    batched LML + gradient must agree with the FP64 DMMA engine (each engine in its own process: the switch is read
+    once)"""
+    kw = dict(n=8300, d=4, R=4, seed=7)
+    a, b = _fit_in_child("i8", **kw), _fit_in_child("dmma", **kw)
+    assert a["info"] == b["info"] == [0, 0, 0, 0]
+    np.testing.assert_allclose(a["lml"], b["lml"], rtol=1e-9)
+    ga, gb = np.array(a["grad"]), np.array(b["grad"])
+    assert np.abs(ga - gb).max() <= 1e-7 * np.abs(gb).max()
+
+
+def test_single_large_factor_on_the_int8_schedule_matches_dmma():
+    """one matrix with n >= 12288 takes the batched INT8 schedule too (a block column alone fills the machine)"""
+    kw = dict(n=12400, d=3, R=1, seed=9)
+    a, b = _fit_in_child("i8", **kw), _fit_in_child("dmma", **kw)
+    assert a["info"] == b["info"] == 0
+    assert a["lml"] == pytest.approx(b["lml"], rel=1e-9)
+    np.testing.assert_allclose(a["mu"], b["mu"], rtol=1e-7, atol=1e-9)
+    np.testing.assert_allclose(a["sigma"], b["sigma"], rtol=1e-7, atol=1e-9)

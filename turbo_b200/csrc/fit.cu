@@ -119,13 +119,24 @@ __global__ void __launch_bounds__(256) gram_train_kernel(const double* __restric
 //   completed with pivot 1 so the rest of the batch keeps running.
 // ---------------------------------------------------------------------------------------------
 constexpr int DB = 128, DLD = 129;
-constexpr size_t DIAG_SMEM = (size_t)(DB * DLD + DB) * sizeof(double);
+// S[128][129] (factor, row stride 129: a thread walking its own row and the broadcast of the pivot row are both
+// conflict-free) + X packed lower triangle [k(k+1)/2 + c] (inverse) + one pivot slot
+constexpr size_t DIAG_SMEM = (size_t)(DB * DLD + DB * (DB + 1) / 2 + 2) * sizeof(double);
 
+// One CTA per 128x128 diagonal block, everything in shared memory, at most two barriers per column:
+//   factor : Cholesky-Crout by rows.  Two threads own row t (even / odd pairs of k); at column j they form
+//            A[t,j] - sum_k L[t,k] L[j,k] against the broadcast pivot row, thread pair j takes the square root and
+//            publishes the reciprocal, every row below scales with it (LAPACK dpotf2 scales by the reciprocal too).
+//   inverse: thread c owns column c of X = L^-1 and runs the forward substitution x_i = (delta_ic - sum_k L[i,k] x_k)
+//            / L[i,i] down the rows with four running sums, no barriers.
+// Latency-bound (8 warps, 0.75 IPC, 218 us per launch: ncu, round 1); it runs on the look-ahead stream beside the
+// block column's row update, which hides it for all but the first and last few block columns of a batched fit.
 __global__ void __launch_bounds__(256, 1) diag_potrf_inv_kernel(double* __restrict__ Abase, long ld, long strideA,
                                                                  int kb, double* __restrict__ Dinv, long strideD,
                                                                  int* __restrict__ info) {
-    extern __shared__ double S[];  // [128][129] + tmp[128]
-    double* tmp = S + DB * DLD;
+    extern __shared__ double S[];
+    double* Xp = S + DB * DLD;
+    double* piv = Xp + DB * (DB + 1) / 2;
     const int tid = threadIdx.x;
     const int r = blockIdx.x;
     double* A = Abase + (long)r * strideA + (long)kb * DB * ld + (long)kb * DB;
@@ -134,49 +145,69 @@ __global__ void __launch_bounds__(256, 1) diag_potrf_inv_kernel(double* __restri
         S[i * DLD + j] = (j <= i) ? A[(long)i * ld + j] : 0.0;
     }
     __syncthreads();
-    const int ty = tid >> 4, tx = tid & 15;
+    const int t = tid >> 1, half = tid & 1;
+    const double* mine = S + t * DLD;
     for (int j = 0; j < DB; ++j) {
-        __syncthreads();  // trailing update of step j-1 complete
-        double dj = S[j * DLD + j];
-        if (!(dj > 0.0)) {  // also catches NaN, as LAPACK dpotrf does
-            if (tid == 0) atomicCAS(&info[r], 0, kb * DB + j + 1);
-            dj = 1.0;
+        double v = 0.0;
+        if (t >= j) {
+            const double* pr = S + j * DLD;
+            double a0 = 0.0, a1 = 0.0;
+            int k = 2 * half;
+            for (; k + 1 < j; k += 4) {
+                a0 = fma(mine[k], pr[k], a0);
+                a1 = fma(mine[k + 1], pr[k + 1], a1);
+            }
+            if (k < j) a0 = fma(mine[k], pr[k], a0);
+            v = a0 + a1;
         }
-        const double rd = sqrt(dj);
-        for (int i = j + 1 + tid; i < DB; i += 256) S[i * DLD + j] = S[i * DLD + j] / rd;
-        __syncthreads();  // pivot read by everyone, column j scaled
-        if (tid == 0) S[j * DLD + j] = rd;
-        for (int i = j + 1 + ty; i < DB; i += 16) {
-            const double lij = S[i * DLD + j];
-            for (int k = j + 1 + tx; k <= i; k += 16) S[i * DLD + k] -= lij * S[k * DLD + j];
+        v += __shfl_xor_sync(0xffffffffu, v, 1);
+        v = mine[j] - v;
+        if (t == j && half == 0) {
+            if (!(v > 0.0)) {  // also catches NaN, as LAPACK dpotrf does
+                atomicCAS(&info[r], 0, kb * DB + j + 1);
+                v = 1.0;
+            }
+            const double rd = sqrt(v);
+            S[j * DLD + j] = rd;
+            piv[0] = 1.0 / rd;
         }
+        __syncthreads();  // reciprocal pivot published; every dot product of this column has read row j
+        if (t > j && half == 0) S[t * DLD + j] = v * piv[0];
+        __syncthreads();  // column j final: row j+1 is complete through column j
     }
-    __syncthreads();
     for (int e = tid; e < DB * DB; e += 256) {
         const int i = e >> 7, j = e & 127;
         A[(long)i * ld + j] = S[i * DLD + j];  // upper part already 0
     }
-    __syncthreads();
-    // in-place inverse, columns right to left (LAPACK dtrti2, lower): two threads per row
-    const int row = tid >> 1, half = tid & 1;
-    for (int j = DB - 1; j >= 0; --j) {
-        const double ljj = S[j * DLD + j];
-        if (tid > j && tid < DB) tmp[tid] = S[tid * DLD + j];
-        __syncthreads();
-        const double inv = 1.0 / ljj;
-        double s = 0.0;
-        if (row > j) {
-            for (int k = j + 1 + half; k <= row; k += 2) s += S[row * DLD + k] * tmp[k];
+    if (tid < DB) {
+        // the lanes of a warp walk the same (i, k): L[i,k] is one broadcast and X[k, c] one conflict-free row segment;
+        // a lane whose column starts below row k (c > k) adds nothing
+        const int c = tid, c0 = tid & ~31;
+        for (int i = c0; i < DB; ++i) {
+            const double* li = S + i * DLD;
+            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+            int k = c0;
+            for (; k + 3 < i; k += 4) {
+                const double x0 = (k >= c) ? Xp[k * (k + 1) / 2 + c] : 0.0;
+                const double x1 = (k + 1 >= c) ? Xp[(k + 1) * (k + 2) / 2 + c] : 0.0;
+                const double x2 = (k + 2 >= c) ? Xp[(k + 2) * (k + 3) / 2 + c] : 0.0;
+                const double x3 = (k + 3 >= c) ? Xp[(k + 3) * (k + 4) / 2 + c] : 0.0;
+                a0 = fma(li[k], x0, a0);
+                a1 = fma(li[k + 1], x1, a1);
+                a2 = fma(li[k + 2], x2, a2);
+                a3 = fma(li[k + 3], x3, a3);
+            }
+            for (; k < i; ++k) a0 = fma(li[k], (k >= c) ? Xp[k * (k + 1) / 2 + c] : 0.0, a0);
+            const double sum = (a0 + a1) + (a2 + a3);
+            if (i >= c) Xp[i * (i + 1) / 2 + c] = ((i == c ? 1.0 : 0.0) - sum) / li[i];
+            __syncwarp();
         }
-        s += __shfl_xor_sync(0xffffffffu, s, 1);
-        if (row > j && half == 0) S[row * DLD + j] = -inv * s;
-        if (tid == 0) S[j * DLD + j] = inv;
-        __syncthreads();
     }
+    __syncthreads();
     double* D = Dinv + (long)r * strideD + (long)kb * DB * DB;
     for (int e = tid; e < DB * DB; e += 256) {
         const int i = e >> 7, j = e & 127;
-        D[e] = S[i * DLD + j];
+        D[e] = (j <= i) ? Xp[i * (i + 1) / 2 + j] : 0.0;
     }
 }
 
@@ -688,24 +719,32 @@ static int launch_fit_gemm_i8(const i8::GemmI8Params& g, int ntiles, int R, cuda
 
 static size_t align256(size_t b) { return (b + 255) / 256 * 256; }
 
-static bool use_left_looking(int NB, int R) {
-    static long thr = -1;
-    if (thr < 0) {
-        const char* e = getenv("TB200_FIT_LEFT_MIN");  // R * (n/128) at which the batched schedule takes over
-        thr = e ? atol(e) : 128;  // measured at n = 4096: the batched INT8 schedule wins from R = 4 (profiles/r1_fit_schedule_threshold.md)
-    }
-    return R >= 4 && (long)R * NB >= thr;  // one to three matrices: the right-looking schedule has more tiles per step
-}
-
-// The batched (left-looking) schedule runs its long-K products on the INT8 tensor cores when one INT32 pass covers
-// the k-range (NP <= 8192).  TB200_FIT_ENGINE=dmma keeps everything on the FP64 DMMA GEMM.
-static bool fit_uses_i8(int NP, int R) {
+static bool fit_dmma_forced() {
     static int forced = -1;
     if (forced < 0) {
         const char* e = getenv("TB200_FIT_ENGINE");
         forced = (e && e[0] == 'd') ? 1 : 0;
     }
-    return !forced && NP <= 8192 && use_left_looking(NP / TILE, R);
+    return forced != 0;
+}
+
+static bool use_left_looking(int NB, int R) {
+    static long thr = -1, thr_few = -1;
+    if (thr < 0) {
+        const char* e = getenv("TB200_FIT_LEFT_MIN");  // R * (n/128) at which the batched schedule takes over
+        thr = e ? atol(e) : 128;  // measured at n = 4096: the batched INT8 schedule wins from R = 4 (profiles/r1_fit_schedule_threshold.md)
+        const char* f = getenv("TB200_FIT_LEFT_MIN_FEW");  // the same for one to three matrices (INT8 engine only)
+        thr_few = f ? atol(f) : 96;
+    }
+    // one to three matrices: a block column must offer about one CTA per SM by itself (n >= 12288 for a single
+    // matrix) and the products must be on the INT8 engine; otherwise the right-looking schedule has more tiles per step
+    return R >= 4 ? (long)R * NB >= thr : (!fit_dmma_forced() && (long)R * NB >= thr_few);
+}
+
+// The batched (left-looking) schedule runs its long-K products on the INT8 tensor cores (k-ranges above 8192 in
+// several exact INT32 windows, ozaki_gemm.cuh).  TB200_FIT_ENGINE=dmma keeps everything on the FP64 DMMA GEMM.
+static bool fit_uses_i8(int NP, int R) {
+    return !fit_dmma_forced() && NP <= TB200_I8_MAX_N && use_left_looking(NP / TILE, R);
 }
 
 size_t fit_workspace_layout(int n, int d, int R, int p, bool own_linv, bool own_xst, bool own_alpha, FitBuffers* fb,

@@ -30,6 +30,11 @@ struct GemmI8Params {
     int kbLo, kbHi;
     int kbHiByRow;         // rectangle mode: k-blocks [kbLo, 2*(it+1)) (A is lower triangular: X[i,k] = 0 for k > i)
     double alpha, beta;
+    // One launch accumulates at most PASS_KB k-blocks (8192 terms) exactly in INT32.  Longer k-ranges are cut into
+    // windows [kbWinLo, kbWinHi) launched in increasing order: a CTA whose range misses the window does nothing, and
+    // a window that does not contain the start of the CTA's range accumulates onto C (beta = 1) instead of applying
+    // the caller's beta.  kbWinHi = 0: no window.
+    int kbWinLo, kbWinHi;
 };
 
 template <int GMAX>
@@ -57,7 +62,13 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_i8_kernel(const GemmI8Params 
         kb_lo = p.kbLo;
         kb_hi = p.kbHiByRow ? 2 * (it + 1) : p.kbHi;
     }
+    double beta = p.beta;
+    if (p.kbWinHi > 0) {
+        if (kb_lo < p.kbWinLo) { kb_lo = p.kbWinLo; beta = 1.0; }
+        if (kb_hi > p.kbWinHi) kb_hi = p.kbWinHi;
+    }
     const int nkb = kb_hi - kb_lo;
+    if (nkb <= 0) return;  // uniform over the CTA, before any barrier or TMEM allocation
     const int rs = (int)blockIdx.y;  // restart
 
     if (threadIdx.x == 0) {
@@ -153,12 +164,12 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_i8_kernel(const GemmI8Params 
                 out[c] = v * (srow * __ldg(scol + cc * 8 + c));
             }
             double2* dst = reinterpret_cast<double2*>(crow + cc * 8);
-            if (p.beta != 0.0) {
+            if (beta != 0.0) {
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
                     const double2 old = dst[c];
-                    out[2 * c] = fma(p.beta, old.x, out[2 * c]);
-                    out[2 * c + 1] = fma(p.beta, old.y, out[2 * c + 1]);
+                    out[2 * c] = fma(beta, old.x, out[2 * c]);
+                    out[2 * c + 1] = fma(beta, old.y, out[2 * c + 1]);
                 }
             }
 #pragma unroll
@@ -180,7 +191,19 @@ inline int launch_gemm_i8(const GemmI8Params& p, int ntiles, int R, cudaStream_t
         configured = true;
     }
     if (ntiles <= 0 || R <= 0) return 0;
-    TB_LAUNCH((gemm_i8_kernel<GMAX>), dim3((unsigned)ntiles, (unsigned)R), dim3(THREADS), SMEM_BYTES, stream, p);
+    // the longest k-range any CTA of this launch can have
+    const int span = p.tri ? p.kblks : (p.kbHiByRow ? p.kblks : p.kbHi) - p.kbLo;
+    if (span <= PASS_KB) {
+        TB_LAUNCH((gemm_i8_kernel<GMAX>), dim3((unsigned)ntiles, (unsigned)R), dim3(THREADS), SMEM_BYTES, stream, p);
+        return 0;
+    }
+    const int lo0 = p.tri ? 0 : p.kbLo, hi0 = p.tri ? p.kblks : (p.kbHiByRow ? p.kblks : p.kbHi);
+    for (int w = lo0; w < hi0; w += PASS_KB) {
+        GemmI8Params q = p;
+        q.kbWinLo = w;
+        q.kbWinHi = (w + PASS_KB < hi0) ? w + PASS_KB : hi0;
+        TB_LAUNCH((gemm_i8_kernel<GMAX>), dim3((unsigned)ntiles, (unsigned)R), dim3(THREADS), SMEM_BYTES, stream, q);
+    }
     return 0;
 }
 
