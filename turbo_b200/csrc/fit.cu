@@ -464,20 +464,15 @@ __global__ void pad_vector_kernel(const double* __restrict__ y, int n, int NP, d
 // ---------------------------------------------------------------------------------------------
 // INT8 engine of the batched fit (ozaki_gemm.cuh): scales and byte slicing of L and L^-1
 // ---------------------------------------------------------------------------------------------
-// balanced s8 digits of a, |a| <= 0.98 (same construction as slice_signed in acquire.cu)
-__device__ __forceinline__ void fit_slice_signed(double a, uint8_t (&u)[i8::S]) {
-    double t = a * 128.0;
-#pragma unroll
-    for (int s = 0; s < i8::S; ++s) {
-        if (s > 0) t *= 256.0;
-        int q = __double2int_rn(t);
-        q = max(q, -128);
-        q = min(q, 127);
-        double rem = t - (double)q;
-        if (s < i8::S - 1 && rem > 127.0 / 255.0 && q < 127) { q += 1; rem -= 1.0; }
-        u[s] = (uint8_t)(int8_t)q;
-        t = rem;
-    }
+// balanced s8 digits of a, |a| <= 0.98:  a ~= sum_{s=0..6} b_s 2^(-7-8s), b_s in [-128, 127].
+// X = rn(a 2^55) is a 56-bit signed integer.  Its balanced base-256 digits obey digit = (int8)(low byte),
+// X <- (X + 128) >> 8; adding 128 at every byte position at once propagates exactly those carries, so byte j of
+// (X + 0x80..80) ^ 0x80..80 is the two's-complement digit of weight 2^(8j): digit s of the GEMM is byte 6 - s.
+// One multiply and one conversion on the FP64 pipe per element; the per-digit FP64 round / subtract chain this
+// replaces made the slicing kernels FP64-pipe bound (7 x 5 FP64-class operations per element).
+__device__ __forceinline__ unsigned long long fit_slice_signed(double a) {
+    const long long x = __double2ll_rn(a * 36028797018963968.0);  // 2^55: exact scaling, one rounding
+    return ((unsigned long long)x + 0x0080808080808080ull) ^ 0x0080808080808080ull;
 }
 
 __device__ __forceinline__ double pow2_cover(double mx) {
@@ -523,10 +518,24 @@ __global__ void __launch_bounds__(128) colmax_bits_kernel(const double* __restri
     const int r_lo = row0 + blockIdx.x * 128, r_hi = min(NP, r_lo + 128);
     const double* x = M + (size_t)rs * mStride + c;
     double m = 0.0;
-    for (int r = r_lo; r < r_hi; ++r) {
+    const double* ks = kscale ? kscale + (size_t)rs * NP : nullptr;
+    int r = r_lo;
+    for (; r + 8 <= r_hi; r += 8) {  // 8 independent loads in flight per thread
+        double v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = fabs(x[(size_t)(r + u) * NP]);
+        if (ks) {
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v[u] *= ks[r + u];
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+            if (v[u] > m) m = v[u];  // NaN never enters
+    }
+    for (; r < r_hi; ++r) {
         double v = fabs(x[(size_t)r * NP]);
-        if (kscale) v *= kscale[(size_t)rs * NP + r];
-        if (v > m) m = v;  // NaN never enters
+        if (ks) v *= ks[r];
+        if (v > m) m = v;
     }
     if (m > 0.0) atomicMax(out + (size_t)rs * NP + c, (unsigned long long)__double_as_longlong(m));
 }
@@ -577,21 +586,31 @@ __global__ void __launch_bounds__(256) slice_operand_kernel(const double* __rest
             for (int q = 0; q < 16; ++q) kw[q] = 1.0 / kw[q];  // exact
         }
     }
-    __align__(16) uint8_t bytes[i8::S][16];
+    uint32_t lo[16], hi[16];
 #pragma unroll
     for (int q = 0; q < 16; ++q) {
         double v = TRANSPOSED ? src[(size_t)(k0 + q) * NP + orow] : src[(size_t)orow * NP + k0 + q];
         if (kmode) v *= kw[q];
-        uint8_t u[i8::S];
-        fit_slice_signed(v * inv, u);
-#pragma unroll
-        for (int s = 0; s < i8::S; ++s) bytes[s][q] = u[s];
+        const unsigned long long y = fit_slice_signed(v * inv);
+        lo[q] = (uint32_t)y;
+        hi[q] = (uint32_t)(y >> 32);
     }
     const size_t off = (size_t)rs * restartStride + ((size_t)((orow - tileRow0) / 64) * kblks + kb) * i8::B_TILE +
                        (size_t)((orow % 64) >> 3) * i8::SBO + (lane >> 3) * i8::LBO + (lane & 7) * 16;
 #pragma unroll
-    for (int s = 0; s < i8::S; ++s)
-        *reinterpret_cast<uint4*>(out + (size_t)s * sliceStride + off) = *reinterpret_cast<const uint4*>(bytes[s]);
+    for (int sl = 0; sl < i8::S; ++sl) {
+        // digit sl = byte (6 - sl) of the value: bytes 2,1,0 of hi, then 3,2,1,0 of lo
+        const int byte = (sl < 3) ? 2 - sl : 6 - sl;
+        uint32_t w[4];
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+            const uint32_t* srcw = (sl < 3) ? hi : lo;
+            const uint32_t p01 = __byte_perm(srcw[4 * v], srcw[4 * v + 1], byte | ((4 + byte) << 4));
+            const uint32_t p23 = __byte_perm(srcw[4 * v + 2], srcw[4 * v + 3], byte | ((4 + byte) << 4));
+            w[v] = __byte_perm(p01, p23, 0x5410);
+        }
+        *reinterpret_cast<uint4*>(out + (size_t)sl * sliceStride + off) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
