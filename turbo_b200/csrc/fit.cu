@@ -123,46 +123,58 @@ constexpr int DB = 128, DLD = 129;
 // conflict-free) + X packed lower triangle [k(k+1)/2 + c] (inverse) + one pivot slot
 constexpr size_t DIAG_SMEM = (size_t)(DB * DLD + DB * (DB + 1) / 2 + 2) * sizeof(double);
 
-// One CTA per 128x128 diagonal block, everything in shared memory, at most two barriers per column:
-//   factor : Cholesky-Crout by rows.  Two threads own row t (even / odd pairs of k); at column j they form
-//            A[t,j] - sum_k L[t,k] L[j,k] against the broadcast pivot row, thread pair j takes the square root and
+// One CTA of 1024 threads per 128x128 diagonal block, everything in shared memory, at most two barriers per column.
+// The block is a chain of 128 dependent columns, so the kernel is latency-bound: the work of every column is spread
+// over as many warps as the SM holds (8 threads per row / per column of the inverse) to shorten each link.
+//   factor : Cholesky-Crout by rows.  Eight threads own row t (pairs of k, stride 16); at column j they form
+//            A[t,j] - sum_k L[t,k] L[j,k] against the broadcast pivot row, the owner of row j takes the square root and
 //            publishes the reciprocal, every row below scales with it (LAPACK dpotf2 scales by the reciprocal too).
-//   inverse: thread c owns column c of X = L^-1 and runs the forward substitution x_i = (delta_ic - sum_k L[i,k] x_k)
-//            / L[i,i] down the rows with four running sums, no barriers.
-// Latency-bound (8 warps, 0.75 IPC, 218 us per launch: ncu, round 1); it runs on the look-ahead stream beside the
-// block column's row update, which hides it for all but the first and last few block columns of a batched fit.
-__global__ void __launch_bounds__(256, 1) diag_potrf_inv_kernel(double* __restrict__ Abase, long ld, long strideA,
-                                                                 int kb, double* __restrict__ Dinv, long strideD,
-                                                                 int* __restrict__ info) {
+//   inverse: eight threads own column c of X = L^-1 and run the forward substitution
+//            x_i = (delta_ic - sum_k L[i,k] x_k) / L[i,i] down the rows; a warp (4 columns) needs no barrier.
+// Measured (ncu, round 1): 199 us per launch, 648 K warp instructions per CTA at 1.7 IPC -- the fixed cost of a column
+// step (reduce, two barriers, predicates) times 32 warps is what remains; 256 threads gave 218 us at 0.75 IPC.  A
+// panel-blocked variant (several columns per barrier pair) is the next step if this kernel matters more.
+// It runs on the look-ahead stream beside the block column's row update, which hides it for all but the first and
+// last few block columns of a batched fit; for one large matrix (n = 16384: 128 launches) it is on the critical path.
+constexpr int DT = 8;  // threads per row (factor) / per column (inverse)
+constexpr int DIAG_THREADS = DB * DT;
+
+__device__ __forceinline__ double diag_group_sum(double v) {
+#pragma unroll
+    for (int o = DT / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__global__ void __launch_bounds__(DIAG_THREADS, 1) diag_potrf_inv_kernel(double* __restrict__ Abase, long ld,
+                                                                          long strideA, int kb,
+                                                                          double* __restrict__ Dinv, long strideD,
+                                                                          int* __restrict__ info) {
     extern __shared__ double S[];
     double* Xp = S + DB * DLD;
     double* piv = Xp + DB * (DB + 1) / 2;
     const int tid = threadIdx.x;
     const int r = blockIdx.x;
     double* A = Abase + (long)r * strideA + (long)kb * DB * ld + (long)kb * DB;
-    for (int e = tid; e < DB * DB; e += 256) {
+    for (int e = tid; e < DB * DB; e += DIAG_THREADS) {
         const int i = e >> 7, j = e & 127;
         S[i * DLD + j] = (j <= i) ? A[(long)i * ld + j] : 0.0;
     }
     __syncthreads();
-    const int t = tid >> 1, half = tid & 1;
+    const int t = tid / DT, h = tid % DT;
     const double* mine = S + t * DLD;
     for (int j = 0; j < DB; ++j) {
-        double v = 0.0;
+        double a0 = 0.0, a1 = 0.0;
         if (t >= j) {
             const double* pr = S + j * DLD;
-            double a0 = 0.0, a1 = 0.0;
-            int k = 2 * half;
-            for (; k + 1 < j; k += 4) {
+            int k = 2 * h;
+            for (; k + 1 < j; k += 2 * DT) {
                 a0 = fma(mine[k], pr[k], a0);
                 a1 = fma(mine[k + 1], pr[k + 1], a1);
             }
             if (k < j) a0 = fma(mine[k], pr[k], a0);
-            v = a0 + a1;
         }
-        v += __shfl_xor_sync(0xffffffffu, v, 1);
-        v = mine[j] - v;
-        if (t == j && half == 0) {
+        double v = mine[j] - diag_group_sum(a0 + a1);
+        if (t == j && h == 0) {
             if (!(v > 0.0)) {  // also catches NaN, as LAPACK dpotrf does
                 atomicCAS(&info[r], 0, kb * DB + j + 1);
                 v = 1.0;
@@ -172,40 +184,36 @@ __global__ void __launch_bounds__(256, 1) diag_potrf_inv_kernel(double* __restri
             piv[0] = 1.0 / rd;
         }
         __syncthreads();  // reciprocal pivot published; every dot product of this column has read row j
-        if (t > j && half == 0) S[t * DLD + j] = v * piv[0];
+        if (t > j && h == 0) S[t * DLD + j] = v * piv[0];
         __syncthreads();  // column j final: row j+1 is complete through column j
     }
-    for (int e = tid; e < DB * DB; e += 256) {
+    for (int e = tid; e < DB * DB; e += DIAG_THREADS) {
         const int i = e >> 7, j = e & 127;
         A[(long)i * ld + j] = S[i * DLD + j];  // upper part already 0
     }
-    if (tid < DB) {
-        // the lanes of a warp walk the same (i, k): L[i,k] is one broadcast and X[k, c] one conflict-free row segment;
-        // a lane whose column starts below row k (c > k) adds nothing
-        const int c = tid, c0 = tid & ~31;
+    {
+        // the lanes of a warp walk the same row i; lane (c, h) takes k = c0 + h, c0 + h + 8, ... of the warp's common
+        // range [c0, i) and adds nothing where its column starts below row k (c > k)
+        const int c = t, c0 = (tid & ~31) / DT;
         for (int i = c0; i < DB; ++i) {
             const double* li = S + i * DLD;
-            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-            int k = c0;
-            for (; k + 3 < i; k += 4) {
+            double b0 = 0.0, b1 = 0.0;
+            int k = c0 + h;
+            for (; k + DT < i; k += 2 * DT) {
                 const double x0 = (k >= c) ? Xp[k * (k + 1) / 2 + c] : 0.0;
-                const double x1 = (k + 1 >= c) ? Xp[(k + 1) * (k + 2) / 2 + c] : 0.0;
-                const double x2 = (k + 2 >= c) ? Xp[(k + 2) * (k + 3) / 2 + c] : 0.0;
-                const double x3 = (k + 3 >= c) ? Xp[(k + 3) * (k + 4) / 2 + c] : 0.0;
-                a0 = fma(li[k], x0, a0);
-                a1 = fma(li[k + 1], x1, a1);
-                a2 = fma(li[k + 2], x2, a2);
-                a3 = fma(li[k + 3], x3, a3);
+                const double x1 = (k + DT >= c) ? Xp[(k + DT) * (k + DT + 1) / 2 + c] : 0.0;
+                b0 = fma(li[k], x0, b0);
+                b1 = fma(li[k + DT], x1, b1);
             }
-            for (; k < i; ++k) a0 = fma(li[k], (k >= c) ? Xp[k * (k + 1) / 2 + c] : 0.0, a0);
-            const double sum = (a0 + a1) + (a2 + a3);
-            if (i >= c) Xp[i * (i + 1) / 2 + c] = ((i == c ? 1.0 : 0.0) - sum) / li[i];
+            if (k < i) b0 = fma(li[k], (k >= c) ? Xp[k * (k + 1) / 2 + c] : 0.0, b0);
+            const double sum = diag_group_sum(b0 + b1);
+            if (i >= c && h == 0) Xp[i * (i + 1) / 2 + c] = ((i == c ? 1.0 : 0.0) - sum) / li[i];
             __syncwarp();
         }
     }
     __syncthreads();
     double* D = Dinv + (long)r * strideD + (long)kb * DB * DB;
-    for (int e = tid; e < DB * DB; e += 256) {
+    for (int e = tid; e < DB * DB; e += DIAG_THREADS) {
         const int i = e >> 7, j = e & 127;
         D[e] = (j <= i) ? Xp[i * (i + 1) / 2 + j] : 0.0;
     }
@@ -823,7 +831,7 @@ static int launch_diag(const FitBuffers& fb, int NP, int R, int k, int* info, cu
                                      (int)DIAG_SMEM));
         configured = true;
     }
-    TB_LAUNCH(diag_potrf_inv_kernel, dim3(R), dim3(256), DIAG_SMEM, st, fb.K, (long)NP, sK, k, fb.Dinv, sD, info);
+    TB_LAUNCH(diag_potrf_inv_kernel, dim3(R), dim3(DIAG_THREADS), DIAG_SMEM, st, fb.K, (long)NP, sK, k, fb.Dinv, sD, info);
     return 0;
 }
 
