@@ -119,26 +119,27 @@ __global__ void __launch_bounds__(256) gram_train_kernel(const double* __restric
 //   completed with pivot 1 so the rest of the batch keeps running.
 // ---------------------------------------------------------------------------------------------
 constexpr int DB = 128, DLD = 129;
-// S[128][129] (factor, row stride 129: a thread walking its own row and the broadcast of the pivot row are both
-// conflict-free) + X packed lower triangle [k(k+1)/2 + c] (inverse) + one pivot slot
-constexpr size_t DIAG_SMEM = (size_t)(DB * DLD + DB * (DB + 1) / 2 + 2) * sizeof(double);
-
-// One CTA of 1024 threads per 128x128 diagonal block, everything in shared memory, at most two barriers per column.
-// The block is a chain of 128 dependent columns, so the kernel is latency-bound: the work of every column is spread
-// over as many warps as the SM holds (8 threads per row / per column of the inverse) to shorten each link.
-//   factor : Cholesky-Crout by rows.  Eight threads own row t (pairs of k, stride 16); at column j they form
-//            A[t,j] - sum_k L[t,k] L[j,k] against the broadcast pivot row, the owner of row j takes the square root and
-//            publishes the reciprocal, every row below scales with it (LAPACK dpotf2 scales by the reciprocal too).
-//   inverse: eight threads own column c of X = L^-1 and run the forward substitution
-//            x_i = (delta_ic - sum_k L[i,k] x_k) / L[i,i] down the rows; a warp (4 columns) needs no barrier.
-// Measured (ncu, round 1): 199 us per launch, 648 K warp instructions per CTA at 1.7 IPC -- the fixed cost of a column
-// step (reduce, two barriers, predicates) times 32 warps is what remains; 256 threads gave 218 us at 0.75 IPC.  A
-// panel-blocked variant (several columns per barrier pair) is the next step if this kernel matters more.
-// It runs on the look-ahead stream beside the block column's row update, which hides it for all but the first and
-// last few block columns of a batched fit; for one large matrix (n = 16384: 128 launches) it is on the critical path.
-constexpr int DT = 8;  // threads per row (factor) / per column (inverse)
+constexpr int DP = 8;   // columns per panel (factor) / rows per block (inverse)
+constexpr int DT = 4;   // threads per row (factor) / per column (inverse)
 constexpr int DIAG_THREADS = DB * DT;
+// S[128][129] (factor, row stride 129: a thread walking its own row and the broadcast of a pivot row are both
+// conflict-free) + X packed lower triangle [k(k+1)/2 + c] (inverse) + reciprocal diagonal + the 8x8 panel block
+constexpr size_t DIAG_SMEM = (size_t)(DB * DLD + DB * (DB + 1) / 2 + DB + DP * (DP + 1) + DP) * sizeof(double);
 
+// Cholesky factor and inverse factor of one 128x128 diagonal block per CTA, everything in shared memory.  The block is
+// a chain of dependent columns, so the kernel is latency-bound and what counts is the fixed cost per step: a first
+// version with one column per step (two barriers, a reduction and a square root each) took 199-225 us at any thread
+// count (648 K warp instructions at 1.7 IPC with 1024 threads, 313 K at 0.75 with 256: ncu, round 1).  Here a step
+// is a PANEL of 8 columns:
+//   factor : four threads own row t.  Left-looking: they form A[t, j0..j0+7] - sum_{k<j0} L[t,k] L[j0+q,k] for the 8
+//            columns of the panel at once (one load of L[t,k] feeds 8 FMAs against broadcast pivot rows), the 8 rows
+//            of the diagonal 8x8 block publish theirs, ONE thread factorises that 8x8 block in registers, and every
+//            row below solves its 8 entries against it in registers.  Three barriers per panel, 48 in all.
+//   inverse: four threads own column c of X = L^-1; forward substitution in blocks of 8 rows:
+//            y = delta - L[i0..i0+7, c0..i0) x, then the 8x8 triangular solve in registers with the reciprocal
+//            diagonal kept from the factorisation.  A warp (8 columns) needs no barrier.
+// LAPACK dpotf2 scales by the reciprocal pivot as well.  Measured: 85.7 us per launch (164 K warp instructions per CTA,
+// IPC 1.0); what is left is the serial 8x8 factorisation of each panel and the short late panels.
 __device__ __forceinline__ double diag_group_sum(double v) {
 #pragma unroll
     for (int o = DT / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -151,7 +152,9 @@ __global__ void __launch_bounds__(DIAG_THREADS, 1) diag_potrf_inv_kernel(double*
                                                                           int* __restrict__ info) {
     extern __shared__ double S[];
     double* Xp = S + DB * DLD;
-    double* piv = Xp + DB * (DB + 1) / 2;
+    double* rdiag = Xp + DB * (DB + 1) / 2;  // 1 / L[i,i]
+    double* Bd = rdiag + DB;                 // [8][9] diagonal block of the current panel
+    double* rd8 = Bd + DP * (DP + 1);        // reciprocal pivots of the current panel
     const int tid = threadIdx.x;
     const int r = blockIdx.x;
     double* A = Abase + (long)r * strideA + (long)kb * DB * ld + (long)kb * DB;
@@ -162,52 +165,114 @@ __global__ void __launch_bounds__(DIAG_THREADS, 1) diag_potrf_inv_kernel(double*
     __syncthreads();
     const int t = tid / DT, h = tid % DT;
     const double* mine = S + t * DLD;
-    for (int j = 0; j < DB; ++j) {
-        double a0 = 0.0, a1 = 0.0;
-        if (t >= j) {
-            const double* pr = S + j * DLD;
-            int k = 2 * h;
-            for (; k + 1 < j; k += 2 * DT) {
-                a0 = fma(mine[k], pr[k], a0);
-                a1 = fma(mine[k + 1], pr[k + 1], a1);
+    for (int j0 = 0; j0 < DB; j0 += DP) {
+        double v[DP];
+#pragma unroll
+        for (int q = 0; q < DP; ++q) v[q] = 0.0;
+        if (t >= j0) {
+            const double* pr = S + j0 * DLD;
+            for (int k = h; k < j0; k += DT) {
+                const double m = mine[k];
+#pragma unroll
+                for (int q = 0; q < DP; ++q) v[q] = fma(m, pr[q * DLD + k], v[q]);
             }
-            if (k < j) a0 = fma(mine[k], pr[k], a0);
         }
-        double v = mine[j] - diag_group_sum(a0 + a1);
-        if (t == j && h == 0) {
-            if (!(v > 0.0)) {  // also catches NaN, as LAPACK dpotrf does
-                atomicCAS(&info[r], 0, kb * DB + j + 1);
-                v = 1.0;
+#pragma unroll
+        for (int q = 0; q < DP; ++q) v[q] = mine[j0 + q] - diag_group_sum(v[q]);
+        if (t >= j0 && t < j0 + DP && h == 0) {
+#pragma unroll
+            for (int q = 0; q < DP; ++q) Bd[(t - j0) * (DP + 1) + q] = v[q];
+        }
+        __syncthreads();
+        if (tid == 0) {
+            double b[DP][DP];
+#pragma unroll
+            for (int i = 0; i < DP; ++i)
+#pragma unroll
+                for (int q = 0; q <= i; ++q) b[i][q] = Bd[i * (DP + 1) + q];
+#pragma unroll
+            for (int q = 0; q < DP; ++q) {
+                double d = b[q][q];
+#pragma unroll
+                for (int pp = 0; pp < q; ++pp) d = fma(-b[q][pp], b[q][pp], d);
+                if (!(d > 0.0)) {  // also catches NaN, as LAPACK dpotrf does
+                    atomicCAS(&info[r], 0, kb * DB + j0 + q + 1);
+                    d = 1.0;
+                }
+                // reciprocal square root + one Newton correction each (the IEEE sqrt and division sequences are ~250
+                // dependent cycles apiece, and this thread is the critical path of the panel): <= 1 ulp
+                double ri = rsqrt(d);
+                double rd = d * ri;
+                rd = fma(fma(-rd, rd, d), 0.5 * ri, rd);
+                ri = fma(fma(-rd, ri, 1.0), ri, ri);
+                b[q][q] = rd;
+                rd8[q] = ri;
+                rdiag[j0 + q] = ri;
+#pragma unroll
+                for (int i = q + 1; i < DP; ++i) {
+                    double sacc = b[i][q];
+#pragma unroll
+                    for (int pp = 0; pp < q; ++pp) sacc = fma(-b[i][pp], b[q][pp], sacc);
+                    b[i][q] = sacc * ri;
+                }
             }
-            const double rd = sqrt(v);
-            S[j * DLD + j] = rd;
-            piv[0] = 1.0 / rd;
+#pragma unroll
+            for (int i = 0; i < DP; ++i)
+#pragma unroll
+                for (int q = 0; q <= i; ++q) Bd[i * (DP + 1) + q] = b[i][q];
         }
-        __syncthreads();  // reciprocal pivot published; every dot product of this column has read row j
-        if (t > j && h == 0) S[t * DLD + j] = v * piv[0];
-        __syncthreads();  // column j final: row j+1 is complete through column j
+        __syncthreads();
+        if (t >= j0 && h == 0) {
+            double* dst = S + t * DLD + j0;
+            if (t < j0 + DP) {  // a row of the diagonal block: the factor of the 8x8 block itself
+                for (int q = 0; q <= t - j0; ++q) dst[q] = Bd[(t - j0) * (DP + 1) + q];
+            } else {
+                double x[DP];
+#pragma unroll
+                for (int q = 0; q < DP; ++q) {
+                    double sacc = v[q];
+#pragma unroll
+                    for (int pp = 0; pp < q; ++pp) sacc = fma(-x[pp], Bd[q * (DP + 1) + pp], sacc);
+                    x[q] = sacc * rd8[q];
+                }
+#pragma unroll
+                for (int q = 0; q < DP; ++q) dst[q] = x[q];
+            }
+        }
+        __syncthreads();  // panel final: the rows below are complete through column j0 + 7
     }
     for (int e = tid; e < DB * DB; e += DIAG_THREADS) {
         const int i = e >> 7, j = e & 127;
         A[(long)i * ld + j] = S[i * DLD + j];  // upper part already 0
     }
     {
-        // the lanes of a warp walk the same row i; lane (c, h) takes k = c0 + h, c0 + h + 8, ... of the warp's common
-        // range [c0, i) and adds nothing where its column starts below row k (c > k)
+        // the lanes of a warp (8 columns c0..c0+7) walk the same rows; lane (c, h) takes k = c0 + h, c0 + h + 4, ...
+        // of the warp's common range [c0, i0) and adds nothing where its column starts below row k (c > k)
         const int c = t, c0 = (tid & ~31) / DT;
-        for (int i = c0; i < DB; ++i) {
-            const double* li = S + i * DLD;
-            double b0 = 0.0, b1 = 0.0;
-            int k = c0 + h;
-            for (; k + DT < i; k += 2 * DT) {
-                const double x0 = (k >= c) ? Xp[k * (k + 1) / 2 + c] : 0.0;
-                const double x1 = (k + DT >= c) ? Xp[(k + DT) * (k + DT + 1) / 2 + c] : 0.0;
-                b0 = fma(li[k], x0, b0);
-                b1 = fma(li[k + DT], x1, b1);
+        for (int i0 = c0; i0 < DB; i0 += DP) {
+            double y[DP];
+#pragma unroll
+            for (int q = 0; q < DP; ++q) y[q] = 0.0;
+            const double* lb = S + i0 * DLD;
+            for (int k = c0 + h; k < i0; k += DT) {
+                const double x = (k >= c) ? Xp[k * (k + 1) / 2 + c] : 0.0;
+#pragma unroll
+                for (int q = 0; q < DP; ++q) y[q] = fma(lb[q * DLD + k], x, y[q]);
             }
-            if (k < i) b0 = fma(li[k], (k >= c) ? Xp[k * (k + 1) / 2 + c] : 0.0, b0);
-            const double sum = diag_group_sum(b0 + b1);
-            if (i >= c && h == 0) Xp[i * (i + 1) / 2 + c] = ((i == c ? 1.0 : 0.0) - sum) / li[i];
+            double xs[DP];
+#pragma unroll
+            for (int q = 0; q < DP; ++q) {
+                const int i = i0 + q;
+                double sacc = ((i == c) ? 1.0 : 0.0) - diag_group_sum(y[q]);
+#pragma unroll
+                for (int pp = 0; pp < q; ++pp) sacc = fma(-lb[q * DLD + i0 + pp], xs[pp], sacc);
+                xs[q] = (i >= c) ? sacc * rdiag[i] : 0.0;
+            }
+            if (h == 0) {
+#pragma unroll
+                for (int q = 0; q < DP; ++q)
+                    if (i0 + q >= c) Xp[(i0 + q) * (i0 + q + 1) / 2 + c] = xs[q];
+            }
             __syncwarp();
         }
     }
