@@ -1073,6 +1073,10 @@ static int trtri_batched_i8(const FitBuffers& fb, double* Linv, int NP, int R, c
             if (launch_gemm<false, false>(p, R, 1, st)) return -1;
         }
     }
+    // the recurrence never needed the scales of block column 0; with them fb.scale holds the power-of-two cover of
+    // every column maximum of X, which is exactly the operand scaling of the K^-1 = X^T X step that follows
+    TB_LAUNCH(colmax_bits_kernel, dim3(NB, R), dim3(128), 0, st, Linv, NP, sK, 0, 0, none, fb.tmax);
+    TB_LAUNCH(cover_kernel, dim3(R), dim3(128), 0, st, fb.tmax, NP, 0, tsc);
     return 0;
 }
 
@@ -1162,7 +1166,9 @@ static int fit_pipeline(const double* X, const double* y_n, int n, const tb200_k
             // INT8 tensor cores: operand rows = columns of Linv (K index = row), per-column power-of-two scales
             const long sK = (long)NP * NP;
             const int NB = NP / TILE;
-            TB_LAUNCH(colscale_kernel, dim3((NP + 127) / 128, R), dim3(128), 0, st, Linv, NP, fb.scale);
+            // column scales of Linv: left in fb.scale by the INT8 trtri recurrence; measured here otherwise
+            if (getenv("TB200_TRTRI_DMMA"))
+                TB_LAUNCH(colscale_kernel, dim3((NP + 127) / 128, R), dim3(128), 0, st, Linv, NP, fb.scale);
             const long pieces = (long)(NP / 8) * (NP / i8::KB);
             TB_LAUNCH(slice_operand_kernel<true>, dim3((unsigned)((pieces + 7) / 8), R), dim3(256), 0, st, Linv, NP, sK,
                       fb.scale, (const double*)nullptr, 0, 0, NP / 8, 0, NP / i8::KB, 1, 0, fb.sliced, sK,
