@@ -212,7 +212,8 @@ __device__ __forceinline__ void slice_signed(double a, uint8_t (&u)[i8::S]) {
 // 16-way unrolled body carries one kernel family.
 constexpr int KS_THREADS = 128;  // 16 point groups x 8 candidates; small CTAs share an SM with a variance CTA
 constexpr int KS_JG = 16;        // training points per thread and pass
-constexpr int KS_CTAS_PER_SM = 3;  // persistent grid: 3 x 128 threads x 88 registers fit beside one variance CTA
+constexpr int KS_CTAS_PER_SM = 4;  // persistent grid: 3 x 128 threads x 80 registers fit beside one variance CTA, a 4th
+                                   // where none is resident (measured: n=1024 +10 %, n=4096 unchanged; TB200_KS_CTAS)
 
 template <int KIND>
 __global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_kernel(
@@ -250,7 +251,8 @@ __global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_kernel(
             double r2[KS_JG];
 #pragma unroll
             for (int q = 0; q < KS_JG; ++q) r2[q] = 0.0;
-            for (int k = 0; k < d; ++k) {
+#pragma unroll 2
+            for (int k = 0; k < d; ++k) {  // two dimensions in flight: the next 8 loads issue under this one's FMAs
                 const double xk = xc[k * CPB + c];
                 const double2* xt = reinterpret_cast<const double2*>(XsT + (long)k * NP + j0);
 #pragma unroll
@@ -273,8 +275,8 @@ __global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_kernel(
                 msum = fma(sf2 * g0, a.x, msum);
                 msum = fma(sf2 * g1, a.y, msum);
                 // 56-bit fixed point of g in [0,1] (see slice_unsigned): its bytes are the 7 digits
-                unsigned long long x0 = __double2ull_rn(g0 * 72057594037927936.0);
-                unsigned long long x1 = __double2ull_rn(g1 * 72057594037927936.0);
+                unsigned long long x0 = (unsigned long long)fixed_point_64<24>(g0);
+                unsigned long long x1 = (unsigned long long)fixed_point_64<24>(g1);
                 x0 = min(x0, 72057594037927935ull);
                 x1 = min(x1, 72057594037927935ull);
                 lo[q] = (uint32_t)x0; hi[q] = (uint32_t)(x0 >> 32);
@@ -978,7 +980,9 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
     const size_t ksm = sizeof(double) * (CPB * d + 8 * CPB);
     // split the training points so one K* launch is ~2k CTAs (3 resident per SM): NB/ksplit tiles each
     int ksplit = NB < KSPLIT_MAX ? NB : KSPLIT_MAX;
-    const int jchunk = (NB + ksplit - 1) / ksplit * TILE;
+    int jchunk = (NB + ksplit - 1) / ksplit * TILE;
+    // the INT8 K* kernel covers 256 points per pass of its 128 threads: a shorter chunk would idle half of them
+    if (use_i8 && jchunk < 2 * TILE) jchunk = 2 * TILE;
     ksplit = (NP + jchunk - 1) / jchunk;
 
     struct Batch { int sl; int64_t off, mb, mbp; };
@@ -1010,7 +1014,12 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
         if (use_i8) {
             const size_t ksm8 = sizeof(double) * (CPB * d + (KS_THREADS / 32) * CPB);
             const int ngroups = (int)(q.mbp / CPB);
-            const int kctas = g_sm_count * KS_CTAS_PER_SM;
+            static int ks_per_sm = 0;
+            if (!ks_per_sm) {
+                const char* e = getenv("TB200_KS_CTAS");  // diagnostics: persistent K* CTAs per SM
+                ks_per_sm = (e && atoi(e) > 0) ? atoi(e) : KS_CTAS_PER_SM;
+            }
+            const int kctas = g_sm_count * ks_per_sm;
             const dim3 kgrid((unsigned)(ngroups * ksplit < kctas ? ngroups * ksplit : kctas));
 #define TB_KSTAR_I8(KIND)                                                                                             \
     TB_LAUNCH(kstar_mean_i8_kernel<KIND>, kgrid, dim3(KS_THREADS), ksm8, s_small, xc, q.mb, XsT, n, NP, *spec, theta, \

@@ -72,12 +72,15 @@ __device__ inline double length_scale(const tb200_kernel_spec& s, const double* 
 // Branch-free sqrt and exp(-t) for the pair loops.  The library versions carry slow-path branches and calls (denormals,
 // overflow) that end a basic block per evaluation, so the 16 independent evaluations of an unrolled pair loop ran one
 // after the other on their dependent chains; these two are straight-line code the compiler interleaves.
-// sqrt_pos: a >= 0.  Single-precision reciprocal square root, two coupled Newton steps (2^-22 -> 2^-44 -> 2^-88) and a
-// residual correction: <= 1 ulp.  a < 1e-30 returns a*1e15 (a value below 1e-15, where every caller's result is 1 to
-// working precision); a > 1e36 returns 1e18 (every caller's result is 0 there); NaN propagates.
+// They also stay off the XU pipe (conversions, MUFU; 16 lanes/clk/SM): ncu showed the K* kernel at 92 % XU busy with
+// four XU operations per pair (double->float, MUFU.RSQ, float->double, double->u64), 36 % FP64.  sqrt_pos uses ONE
+// (MUFU.RSQ64H through rsqrt.approx.ftz.f64) and the fixed-point conversions below use none.
+// sqrt_pos: a >= 0.  Reciprocal square root to ~2^-22 from the high word, two coupled Newton steps (-> 2^-44 -> 2^-88)
+// and a residual correction: <= 1 ulp.  a < 1e-290 (incl. 0 and subnormals, which the approximation flushes) returns 0;
+// a > 1e300 returns 1e150 (every caller's result is 0 there); NaN propagates.
 __device__ __forceinline__ double sqrt_pos(double a) {
-    const float af = fminf(fmaxf((float)a, 1e-30f), 1e37f);
-    const double y = (double)rsqrtf(af);
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
     double g = a * y, h = 0.5 * y;
     double r = fma(-g, h, 0.5);
     g = fma(g, r, g);
@@ -86,8 +89,26 @@ __device__ __forceinline__ double sqrt_pos(double a) {
     g = fma(g, r, g);
     h = fma(h, r, h);
     g = fma(fma(-g, g, a), h, g);
-    return a > 1e36 ? 1e18 : g;
+    g = a < 1e-290 ? 0.0 : g;
+    return a > 1e300 ? 1e150 : g;
 }
+
+// rn(x * 2^(32 + S)) as a 64-bit integer for |x * 2^S| < 2^31, without a conversion instruction: the high part
+// rn(x 2^S) and the rounded remainder (x 2^S - high) 2^32 are read out of the mantissa of (value + 1.5 * 2^52).
+// The remainder is exact (one FMA), so the result is rounded once.  S = 24: unsigned digits of g in [0, 1] (2^56 g);
+// S = 23: balanced digits of |a| < 1 (2^55 a).
+template <int S>
+__device__ __forceinline__ long long fixed_point_64(double x) {
+    const double M = 6755399441055744.0;       // 1.5 * 2^52
+    const double scale = (double)(1 << S);
+    const double t = fma(x, scale, M);
+    const int hi = __double2loint(t);          // low word of the mantissa = rn(x 2^S) (two's complement)
+    const double rem = fma(x, scale, -(t - M));  // in [-0.5, 0.5], exact
+    const double u = fma(rem, 4294967296.0, M);
+    const long long lo = (__double_as_longlong(u) & 0x000FFFFFFFFFFFFFll) - (1ll << 51);  // in [-2^31, 2^31]
+    return ((long long)hi << 32) + lo;
+}
+
 // exp_neg(t) = exp(-t), t >= 0: k = round(-t / ln 2) by the 1.5 * 2^52 shift, two-term Cody-Waite reduction, degree-13
 // Taylor polynomial on |r| <= ln(2)/2 (remainder 4e-18), scaling through the exponent field.  Results below 2^-1021
 // are flushed to 0 (absolute error 5e-308).  About 1 ulp; NaN propagates.

@@ -541,10 +541,10 @@ __global__ void pad_vector_kernel(const double* __restrict__ y, int n, int NP, d
 // X = rn(a 2^55) is a 56-bit signed integer.  Its balanced base-256 digits obey digit = (int8)(low byte),
 // X <- (X + 128) >> 8; adding 128 at every byte position at once propagates exactly those carries, so byte j of
 // (X + 0x80..80) ^ 0x80..80 is the two's-complement digit of weight 2^(8j): digit s of the GEMM is byte 6 - s.
-// One multiply and one conversion on the FP64 pipe per element; the per-digit FP64 round / subtract chain this
-// replaces made the slicing kernels FP64-pipe bound (7 x 5 FP64-class operations per element).
+// Four FP64 operations per element and no conversion (common.cuh fixed_point_64); the per-digit FP64 round / subtract
+// chain this replaces made the slicing kernels FP64-pipe bound (7 x 5 FP64-class operations per element).
 __device__ __forceinline__ unsigned long long fit_slice_signed(double a) {
-    const long long x = __double2ll_rn(a * 36028797018963968.0);  // 2^55: exact scaling, one rounding
+    const long long x = fixed_point_64<23>(a);  // rn(a 2^55), rounded once, no conversion instruction
     return ((unsigned long long)x + 0x0080808080808080ull) ^ 0x0080808080808080ull;
 }
 
