@@ -311,6 +311,125 @@ __global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_kernel(
     }
 }
 
+// The same K* rows and partial means with the training points STAGED in shared memory (n <= 4096).  ncu of the kernel
+// above: 44 % of the stall samples are the loads of the scaled training points -- next to the variance kernel's 170 KB
+// of shared memory L1 is 28 KB, so every pass fetched its 16 x d values per thread from L2 and waited for them
+// (profiles/r1_kstar_ncu_full.md).  Here a CTA owns a contiguous range of items in SPLIT-MAJOR order (item = chunk of
+// 256 training points x group of 8 candidates): the chunk (d x 256 doubles + its alpha) is staged once and the CTA
+// walks candidate groups under it.  Points are stored 16 to a row of 18 doubles so that the four point groups a warp
+// reads with one 16-byte load fall into different banks.  One partial mean per chunk (NP / 256 <= KS_STAGED_SPLITS).
+constexpr int KS_CHUNK = 256;          // training points per staged chunk = one pass of the 128 threads
+constexpr int KS_ROW = KS_CHUNK / KS_JG * (KS_JG + 2);  // padded row: 288 doubles
+constexpr int KS_STAGED_SPLITS = 16;   // partial means per candidate (mean buffer rows)
+
+static size_t kstar_staged_smem(int d) { return sizeof(double) * ((size_t)d * KS_ROW + KS_ROW + CPB * d + (KS_THREADS / 32) * CPB); }
+
+template <int KIND>
+__global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_staged_kernel(
+    const double* __restrict__ Xc, int64_t m_valid, const double* __restrict__ XsT, int n, int NP,
+    tb200_kernel_spec spec, const double* __restrict__ theta, const double* __restrict__ alpha,
+    uint8_t* __restrict__ KsS, long slice_stride, double* __restrict__ mean, long mean_stride, int ngroups,
+    int nsplit) {
+    extern __shared__ double sh[];
+    const int d = spec.d;
+    double* xs = sh;                       // [d][KS_ROW] scaled training points of the current chunk
+    double* al = xs + (size_t)d * KS_ROW;  // [KS_ROW] alpha of the chunk, same padding
+    double* xc = al + KS_ROW;              // [d][CPB] scaled candidates of the current group
+    double* red = xc + CPB * d;
+    const double sf2 = unpack_hyper(spec, theta).sf2;
+    const int c = threadIdx.x & 7, jg = threadIdx.x >> 3;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int kblks = NP / i8::KB;
+    const int total = ngroups * nsplit;
+    const int per = (total + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int lo_item = (int)blockIdx.x * per, hi_item = min(total, lo_item + per);
+    int staged = -1;
+    for (int item = lo_item; item < hi_item; ++item) {
+        const int split = item / ngroups, grp = item - split * ngroups;
+        const int64_t c0 = (int64_t)grp * CPB;
+        const int jlo = split * KS_CHUNK;
+        __syncthreads();  // previous item's xs / xc / red are no longer read
+        if (split != staged) {
+            for (int e = threadIdx.x; e < (d + 1) * KS_CHUNK; e += KS_THREADS) {
+                const int k = e / KS_CHUNK, j = e - k * KS_CHUNK;
+                const int pos = j + (j / KS_JG) * 2;
+                const bool in = jlo + j < NP;
+                if (k < d) xs[(size_t)k * KS_ROW + pos] = in ? __ldg(XsT + (long)k * NP + jlo + j) : 0.0;
+                else al[pos] = in ? __ldg(alpha + jlo + j) : 0.0;
+            }
+            staged = split;
+        }
+        for (int e = threadIdx.x; e < CPB * d; e += KS_THREADS) {
+            const int k = e / CPB, cc = e - k * CPB;
+            const int64_t ci = c0 + cc;
+            xc[e] = (ci < m_valid) ? Xc[ci * d + k] / length_scale(spec, theta, k) : 0.0;
+        }
+        __syncthreads();
+        const int ct = (int)(c0 / i8::TM), rg = (int)((c0 % i8::TM) >> 3);
+        uint8_t* const tile_base = KsS + (size_t)ct * kblks * i8::A_TILE + (size_t)rg * i8::SBO + c * 16;
+        double msum = 0.0;
+        const int j0 = jlo + jg * KS_JG;
+        if (j0 < NP) {
+            const double* xrow = xs + jg * (KS_JG + 2);
+            double r2[KS_JG];
+#pragma unroll
+            for (int q = 0; q < KS_JG; ++q) r2[q] = 0.0;
+#pragma unroll 2
+            for (int k = 0; k < d; ++k) {
+                const double xk = xc[k * CPB + c];
+                const double2* xt = reinterpret_cast<const double2*>(xrow + (size_t)k * KS_ROW);
+#pragma unroll
+                for (int q = 0; q < KS_JG / 2; ++q) {
+                    const double2 v = xt[q];
+                    const double d0 = xk - v.x, d1 = xk - v.y;
+                    r2[2 * q] = fma(d0, d0, r2[2 * q]);
+                    r2[2 * q + 1] = fma(d1, d1, r2[2 * q + 1]);
+                }
+            }
+            uint32_t lo[KS_JG], hi[KS_JG];
+            const double2* ap = reinterpret_cast<const double2*>(al + jg * (KS_JG + 2));
+#pragma unroll
+            for (int q = 0; q < KS_JG; q += 2) {
+                const double2 a = ap[q >> 1];
+                const double s0 = shape_fn(KIND, r2[q]), s1 = shape_fn(KIND, r2[q + 1]);
+                const double g0 = (j0 + q < n) ? s0 : 0.0;
+                const double g1 = (j0 + q + 1 < n) ? s1 : 0.0;
+                msum = fma(sf2 * g0, a.x, msum);
+                msum = fma(sf2 * g1, a.y, msum);
+                unsigned long long x0 = (unsigned long long)fixed_point_64<24>(g0);
+                unsigned long long x1 = (unsigned long long)fixed_point_64<24>(g1);
+                x0 = min(x0, 72057594037927935ull);
+                x1 = min(x1, 72057594037927935ull);
+                lo[q] = (uint32_t)x0; hi[q] = (uint32_t)(x0 >> 32);
+                lo[q + 1] = (uint32_t)x1; hi[q + 1] = (uint32_t)(x1 >> 32);
+            }
+            uint8_t* dst = tile_base + (size_t)(j0 / i8::KB) * i8::A_TILE + ((j0 % i8::KB) >> 4) * i8::LBO;
+#pragma unroll
+            for (int sl = 0; sl < i8::S; ++sl) {
+                const int byte = (sl < 3) ? 2 - sl : 6 - sl;
+                uint32_t w[4];
+#pragma unroll
+                for (int v = 0; v < 4; ++v) {
+                    const uint32_t* src = (sl < 3) ? hi : lo;
+                    const uint32_t p01 = __byte_perm(src[4 * v], src[4 * v + 1], byte | ((4 + byte) << 4));
+                    const uint32_t p23 = __byte_perm(src[4 * v + 2], src[4 * v + 3], byte | ((4 + byte) << 4));
+                    w[v] = __byte_perm(p01, p23, 0x5410);
+                }
+                *reinterpret_cast<uint4*>(dst + (size_t)sl * slice_stride) = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+        }
+        msum += __shfl_xor_sync(0xffffffffu, msum, 8);
+        msum += __shfl_xor_sync(0xffffffffu, msum, 16);
+        if (lane < CPB) red[warp * CPB + lane] = msum;
+        __syncthreads();
+        if (threadIdx.x < CPB) {
+            double t = 0.0;
+            for (int w = 0; w < KS_THREADS / 32; ++w) t += red[w * CPB + threadIdx.x];
+            mean[split * mean_stride + c0 + threadIdx.x] = t;  // partial mean; the epilogue adds the splits in order
+        }
+    }
+}
+
 // rowscale[r] = sf2 * 2^(e_r) with 0.98 * 2^(e_r) >= max_k |Linv[r,k]|  (one warp per row)
 __global__ void __launch_bounds__(256) linv_rowscale_kernel(const double* __restrict__ Linv, int NP,
                                                             tb200_kernel_spec spec, const double* __restrict__ theta,
@@ -779,7 +898,7 @@ static size_t acquire_layout(int n, int d, int64_t batch, AcqBuffers* ab, char* 
         double* cand = take(sizeof(double) * batch * d);
         // DMMA engine: K* in FP64 (batch x NP); INT8 engine: 7 byte slices of it (tiled), partials per 64 rows
         double* Ks = take(use_i8 ? (size_t)i8::S * batch * NP : sizeof(double) * batch * NP);
-        double* mean = take(sizeof(double) * KSPLIT_MAX * batch);
+        double* mean = take(sizeof(double) * (KSPLIT_MAX > KS_STAGED_SPLITS ? KSPLIT_MAX : KS_STAGED_SPLITS) * batch);
         double* partial = take(sizeof(double) * (use_i8 ? NP / i8::TN : NB) * batch);
         double* mind = take(sizeof(double) * batch);
         if (ab) { ab[s].cand = cand; ab[s].Ks = Ks; ab[s].mean = mean; ab[s].partial = partial; ab[s].mind = mind; }
@@ -865,6 +984,15 @@ static int configure_carveout() {
     TB_CUDA(cudaFuncSetAttribute(kstar_mean_i8_kernel<TB200_MATERN12>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
     TB_CUDA(cudaFuncSetAttribute(kstar_mean_i8_kernel<TB200_MATERN32>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
     TB_CUDA(cudaFuncSetAttribute(kstar_mean_i8_kernel<TB200_MATERN52>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
+#define TB_STAGED_ATTR(KIND)                                                                                        \
+    TB_CUDA(cudaFuncSetAttribute(kstar_mean_i8_staged_kernel<KIND>, cudaFuncAttributePreferredSharedMemoryCarveout, mx)); \
+    TB_CUDA(cudaFuncSetAttribute(kstar_mean_i8_staged_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize,          \
+                                 (int)kstar_staged_smem(TB200_MAX_D)))
+    TB_STAGED_ATTR(TB200_RBF);
+    TB_STAGED_ATTR(TB200_MATERN12);
+    TB_STAGED_ATTR(TB200_MATERN32);
+    TB_STAGED_ATTR(TB200_MATERN52);
+#undef TB_STAGED_ATTR
     TB_CUDA(cudaFuncSetAttribute(kstar_mean_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
     TB_CUDA(cudaFuncSetAttribute(acquire_epilogue_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
     TB_CUDA(cudaFuncSetAttribute(generate_candidates_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
@@ -984,6 +1112,22 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
     // the INT8 K* kernel covers 256 points per pass of its 128 threads: a shorter chunk would idle half of them
     if (use_i8 && jchunk < 2 * TILE) jchunk = 2 * TILE;
     ksplit = (NP + jchunk - 1) / jchunk;
+    // staged K* kernel (training-point chunk in shared memory): 2048 <= n <= 4096 and at least two CTAs of it fit into
+    // the ~57 KB the variance kernel leaves on an SM; TB200_KS_STAGED=0 keeps the direct-load kernel.  Measured
+    // (profiles/r1_kstar_ncu_full.md): n=4096, d=10 (variance-bound step) 388.8 -> 376.2 ms per 2^21 candidates; at
+    // n=1024, d=6 the step is K*-bound and four direct-load CTAs per SM beat three staged ones (5.49e7 vs 5.00e7 /s).
+    int staged_ctas = 0;
+    const int staged_splits = (NP + KS_CHUNK - 1) / KS_CHUNK;
+    if (use_i8 && staged_splits <= KS_STAGED_SPLITS && NP >= 2048) {
+        static int allow = -1;
+        if (allow < 0) {
+            const char* e = getenv("TB200_KS_STAGED");
+            allow = (e && atoi(e) == 0) ? 0 : 1;
+        }
+        const int fit = (int)((57 * 1024) / (kstar_staged_smem(d) + 1024));
+        if (allow && fit >= 2) staged_ctas = fit < 4 ? fit : 4;
+    }
+    const int mean_splits = staged_ctas ? staged_splits : ksplit;
 
     struct Batch { int sl; int64_t off, mb, mbp; };
     auto batch_of = [&](int64_t bno) {
@@ -1019,11 +1163,20 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
                 const char* e = getenv("TB200_KS_CTAS");  // diagnostics: persistent K* CTAs per SM
                 ks_per_sm = (e && atoi(e) > 0) ? atoi(e) : KS_CTAS_PER_SM;
             }
-            const int kctas = g_sm_count * ks_per_sm;
-            const dim3 kgrid((unsigned)(ngroups * ksplit < kctas ? ngroups * ksplit : kctas));
-#define TB_KSTAR_I8(KIND)                                                                                             \
-    TB_LAUNCH(kstar_mean_i8_kernel<KIND>, kgrid, dim3(KS_THREADS), ksm8, s_small, xc, q.mb, XsT, n, NP, *spec, theta, \
-              alpha, reinterpret_cast<uint8_t*>(w.Ks), slice_stride, w.mean, jchunk, (long)batch, ngroups, ksplit)
+            const int kctas = g_sm_count * (staged_ctas ? staged_ctas : ks_per_sm);
+            const int kitems = ngroups * (staged_ctas ? staged_splits : ksplit);
+            const dim3 kgrid((unsigned)(kitems < kctas ? kitems : kctas));
+            const size_t ksm_st = kstar_staged_smem(d);
+#define TB_KSTAR_I8(KIND)                                                                                              \
+    if (staged_ctas) {                                                                                                 \
+        TB_LAUNCH(kstar_mean_i8_staged_kernel<KIND>, kgrid, dim3(KS_THREADS), ksm_st, s_small, xc, q.mb, XsT, n, NP,   \
+                  *spec, theta, alpha, reinterpret_cast<uint8_t*>(w.Ks), slice_stride, w.mean, (long)batch, ngroups,   \
+                  staged_splits);                                                                                      \
+    } else {                                                                                                           \
+        TB_LAUNCH(kstar_mean_i8_kernel<KIND>, kgrid, dim3(KS_THREADS), ksm8, s_small, xc, q.mb, XsT, n, NP, *spec,     \
+                  theta, alpha, reinterpret_cast<uint8_t*>(w.Ks), slice_stride, w.mean, jchunk, (long)batch, ngroups,  \
+                  ksplit);                                                                                             \
+    }
             switch (spec->kind) {
                 case TB200_RBF: TB_KSTAR_I8(TB200_RBF); break;
                 case TB200_MATERN12: TB_KSTAR_I8(TB200_MATERN12); break;
@@ -1073,7 +1226,7 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
         const Batch q = batch_of(bno);
         const AcqBuffers& w = ab[q.sl];
         TB_LAUNCH(acquire_epilogue_kernel, dim3((unsigned)(q.mbp / EPI_THREADS)), dim3(EPI_THREADS), 0, s_small, w.mean,
-                  ksplit, w.partial, ntiles, (long)batch, q.mbp, q.mb, q.off, index_base, *spec, theta, *acq, mu_out,
+                  mean_splits, w.partial, ntiles, (long)batch, q.mbp, q.mb, q.off, index_base, *spec, theta, *acq, mu_out,
                   sigma_out, acq_out, w.best_val, w.best_idx,
                   excl ? (excl->min_out ? excl->min_out + q.off : w.mind) : nullptr, excl ? excl->tol : 0.0);
         trace_mark(q.sl * 16 + 3, s_small);
