@@ -1119,13 +1119,15 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
     int staged_ctas = 0;
     const int staged_splits = (NP + KS_CHUNK - 1) / KS_CHUNK;
     if (use_i8 && staged_splits <= KS_STAGED_SPLITS && NP >= 2048) {
-        static int allow = -1;
+        static int allow = -1, cap = 0;
         if (allow < 0) {
             const char* e = getenv("TB200_KS_STAGED");
             allow = (e && atoi(e) == 0) ? 0 : 1;
+            const char* c = getenv("TB200_KS_STAGED_CTAS");  // diagnostics: cap on staged CTAs per SM
+            cap = (c && atoi(c) > 0) ? atoi(c) : 4;
         }
         const int fit = (int)((57 * 1024) / (kstar_staged_smem(d) + 1024));
-        if (allow && fit >= 2) staged_ctas = fit < 4 ? fit : 4;
+        if (allow && fit >= 2) staged_ctas = fit < cap ? fit : cap;
     }
     const int mean_splits = staged_ctas ? staged_splits : ksplit;
 
