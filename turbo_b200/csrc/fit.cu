@@ -907,6 +907,7 @@ static int launch_panel(const FitBuffers& fb, int NP, int R, int k, cudaStream_t
     double* panel = fb.K + (long)(k + 1) * TILE * NP + (long)k * TILE;
     GemmParams p = gemm_params(panel, NP, fb.Dinv + (long)k * TILE * TILE, TILE, panel, NP, rem, 1, TILE, 1.0, 0.0);
     p.sA1 = sK; p.sB1 = sD; p.sC1 = sK;
+    p.b_tri = 1;  // Dinv_k is lower triangular: C[i,j] = sum_{k<=j} A[i,k] Dinv[j,k]
     return launch_gemm<false, true>(p, R, 1, st);
 }
 
@@ -1070,6 +1071,7 @@ static int trtri_batched_i8(const FitBuffers& fb, double* Linv, int NP, int R, c
             double* col = Linv + (long)c1 * TILE * NP + (long)c * TILE;
             GemmParams p = gemm_params(col, NP, fb.Dinv + (long)c * TILE * TILE, TILE, col, NP, rem, 1, TILE, 1.0, 0.0);
             p.sA1 = sK; p.sB1 = sD; p.sC1 = sK;
+            p.b_tri = 2;  // X[i,j] = sum_{k>=j} T[i,k] Dinv_c[k,j]
             if (launch_gemm<false, false>(p, R, 1, st)) return -1;
         }
     }

@@ -39,6 +39,8 @@ struct GemmParams {
     double alpha, beta;
     int order, klo_mode, khi_mode, epi;
     int a_tri_diag;      // with KHI_BY_TI: A's diagonal 128-block is lower triangular -> warps skip its zero k-range
+    int b_tri;           // K == 128, one column tile: B is a lower-triangular 128-block.  1: stored [n][k] (TB), zero for
+                         // k > n -> a warp's columns need k < (wn+1)*32;  2: stored [k][n], zero for k < n -> k >= wn*32
 };
 
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
@@ -93,11 +95,9 @@ __global__ void __launch_bounds__(G_THREADS, 1) gemm_f64_kernel(const GemmParams
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     // 4 x 4 warps, warp tile 32 x 32; the four warps of one scheduler (warp % 4) cover all four wm, so the
     // triangular skip below removes the same amount of work from every scheduler
-#ifdef TB_MAP_OLD
-    const int wm = warp % G_WM, wn = warp / G_WM;
-#else
-    const int wm = warp / G_WN, wn = warp % G_WN;
-#endif
+    // (b_tri skips by wn instead, so there the four warps of a scheduler cover all four wn)
+    const bool by_wn = p.b_tri != 0;
+    const int wm = by_wn ? warp % G_WM : warp / G_WN, wn = by_wn ? warp / G_WM : warp % G_WN;
     const int g = lane >> 2, kk = lane & 3;
 
     int ti, tj;
@@ -183,6 +183,16 @@ __global__ void __launch_bounds__(G_THREADS, 1) gemm_f64_kernel(const GemmParams
     // main k-range, then (a_tri_diag) the lower-triangular diagonal block where rows wm*32..+31 are zero
     // for k >= (wm+1)*32: those warps skip the DMMAs but keep taking part in barriers and copies
     const int nk_main = p.a_tri_diag ? nk - G_TM / G_TK : nk;
+    if (p.b_tri) {
+        // warp columns wn*32..+31 of a lower-triangular B block: 2 k-tiles of 16 per 32 columns
+        const int kt_lo = p.b_tri == 2 ? wn * (G_TN / G_WN / G_TK) : 0;
+        const int kt_hi = p.b_tri == 1 ? (wn + 1) * (G_TN / G_WN / G_TK) : nk;
+        for (int kt = 0; kt < nk; ++kt) {
+            sync_and_issue(kt);
+            if (kt == kt_lo && kt > 0) load_frags(kt % G_STAGES, 0, af, bf);  // the pipeline of fragments starts here
+            if (kt >= kt_lo && kt < kt_hi) compute(kt);
+        }
+    } else
     for (int kt = 0; kt < nk_main; ++kt) {
         sync_and_issue(kt);
         compute(kt);
@@ -267,7 +277,7 @@ inline GemmParams gemm_params(const double* A, long lda, const double* B, long l
     p.lda = lda; p.ldb = ldb; p.ldc = ldc;
     p.tilesM = tilesM; p.tilesN = tilesN; p.K = K;
     p.alpha = alpha; p.beta = beta;
-    p.order = ORDER_RECT; p.klo_mode = KLO_ZERO; p.khi_mode = KHI_FULL; p.epi = EPI_STORE; p.a_tri_diag = 0;
+    p.order = ORDER_RECT; p.klo_mode = KLO_ZERO; p.khi_mode = KHI_FULL; p.epi = EPI_STORE; p.a_tri_diag = 0; p.b_tri = 0;
     return p;
 }
 
