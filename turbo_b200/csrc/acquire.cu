@@ -317,27 +317,33 @@ __global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_kernel(
 // (profiles/r1_kstar_ncu_full.md).  Here a CTA owns a contiguous range of items in SPLIT-MAJOR order (item = chunk of
 // 256 training points x group of 8 candidates): the chunk (d x 256 doubles + its alpha) is staged once and the CTA
 // walks candidate groups under it.  Points are stored 16 to a row of 18 doubles so that the four point groups a warp
-// reads with one 16-byte load fall into different banks.  One partial mean per chunk (NP / 256 <= KS_STAGED_SPLITS).
-constexpr int KS_CHUNK = 256;          // training points per staged chunk = one pass of the 128 threads
-constexpr int KS_ROW = KS_CHUNK / KS_JG * (KS_JG + 2);  // padded row: 288 doubles
-constexpr int KS_STAGED_SPLITS = 16;   // partial means per candidate (mean buffer rows)
+// reads with one 16-byte load fall into different banks.  One partial mean per chunk (at most KS_STAGED_SPLITS).
+// NC = candidates per item (8 or 16): the 128 threads are NC candidates x 128/NC point groups of 16, so a chunk is
+// 256 points (NC = 8) or 128 points (NC = 16; half the shared memory per CTA, which keeps two CTAs per SM up to
+// d = 21; at d = 10 it would allow a third CTA, which measured slower in the pipeline: 379.5 vs 375.5 ms per step).
+constexpr int KS_STAGED_SPLITS = 32;   // partial means per candidate (mean buffer rows): n <= 4096 at 128-point chunks
+__host__ __device__ constexpr int ks_chunk(int NC) { return KS_THREADS / NC * KS_JG; }
+__host__ __device__ constexpr int ks_row(int NC) { return KS_THREADS / NC * (KS_JG + 2); }  // 16 points to a padded row of 18 doubles
 
-static size_t kstar_staged_smem(int d) { return sizeof(double) * ((size_t)d * KS_ROW + KS_ROW + CPB * d + (KS_THREADS / 32) * CPB); }
+static size_t kstar_staged_smem(int d, int NC) {
+    return sizeof(double) * ((size_t)d * ks_row(NC) + ks_row(NC) + (size_t)NC * d + (KS_THREADS / 32) * NC);
+}
 
-template <int KIND>
+template <int KIND, int NC>
 __global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_staged_kernel(
     const double* __restrict__ Xc, int64_t m_valid, const double* __restrict__ XsT, int n, int NP,
     tb200_kernel_spec spec, const double* __restrict__ theta, const double* __restrict__ alpha,
     uint8_t* __restrict__ KsS, long slice_stride, double* __restrict__ mean, long mean_stride, int ngroups,
     int nsplit) {
+    constexpr int CHUNK = ks_chunk(NC), ROW = ks_row(NC);
     extern __shared__ double sh[];
     const int d = spec.d;
-    double* xs = sh;                       // [d][KS_ROW] scaled training points of the current chunk
-    double* al = xs + (size_t)d * KS_ROW;  // [KS_ROW] alpha of the chunk, same padding
-    double* xc = al + KS_ROW;              // [d][CPB] scaled candidates of the current group
-    double* red = xc + CPB * d;
+    double* xs = sh;                    // [d][ROW] scaled training points of the current chunk
+    double* al = xs + (size_t)d * ROW;  // [ROW] alpha of the chunk, same padding
+    double* xc = al + ROW;              // [d][NC] scaled candidates of the current group
+    double* red = xc + NC * d;
     const double sf2 = unpack_hyper(spec, theta).sf2;
-    const int c = threadIdx.x & 7, jg = threadIdx.x >> 3;
+    const int c = threadIdx.x % NC, jg = threadIdx.x / NC;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int kblks = NP / i8::KB;
     const int total = ngroups * nsplit;
@@ -346,27 +352,28 @@ __global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_staged_kernel(
     int staged = -1;
     for (int item = lo_item; item < hi_item; ++item) {
         const int split = item / ngroups, grp = item - split * ngroups;
-        const int64_t c0 = (int64_t)grp * CPB;
-        const int jlo = split * KS_CHUNK;
+        const int64_t c0 = (int64_t)grp * NC;
+        const int jlo = split * CHUNK;
         __syncthreads();  // previous item's xs / xc / red are no longer read
         if (split != staged) {
-            for (int e = threadIdx.x; e < (d + 1) * KS_CHUNK; e += KS_THREADS) {
-                const int k = e / KS_CHUNK, j = e - k * KS_CHUNK;
+            for (int e = threadIdx.x; e < (d + 1) * CHUNK; e += KS_THREADS) {
+                const int k = e / CHUNK, j = e - k * CHUNK;
                 const int pos = j + (j / KS_JG) * 2;
                 const bool in = jlo + j < NP;
-                if (k < d) xs[(size_t)k * KS_ROW + pos] = in ? __ldg(XsT + (long)k * NP + jlo + j) : 0.0;
+                if (k < d) xs[(size_t)k * ROW + pos] = in ? __ldg(XsT + (long)k * NP + jlo + j) : 0.0;
                 else al[pos] = in ? __ldg(alpha + jlo + j) : 0.0;
             }
             staged = split;
         }
-        for (int e = threadIdx.x; e < CPB * d; e += KS_THREADS) {
-            const int k = e / CPB, cc = e - k * CPB;
+        for (int e = threadIdx.x; e < NC * d; e += KS_THREADS) {
+            const int k = e / NC, cc = e - k * NC;
             const int64_t ci = c0 + cc;
             xc[e] = (ci < m_valid) ? Xc[ci * d + k] / length_scale(spec, theta, k) : 0.0;
         }
         __syncthreads();
-        const int ct = (int)(c0 / i8::TM), rg = (int)((c0 % i8::TM) >> 3);
-        uint8_t* const tile_base = KsS + (size_t)ct * kblks * i8::A_TILE + (size_t)rg * i8::SBO + c * 16;
+        // candidate c of the item: row group (c0 % 128) / 8 + c / 8 of candidate tile c0 / 128, row c % 8 in the group
+        const int ct = (int)(c0 / i8::TM), rg = (int)((c0 % i8::TM) >> 3) + (c >> 3);
+        uint8_t* const tile_base = KsS + (size_t)ct * kblks * i8::A_TILE + (size_t)rg * i8::SBO + (c & 7) * 16;
         double msum = 0.0;
         const int j0 = jlo + jg * KS_JG;
         if (j0 < NP) {
@@ -376,8 +383,8 @@ __global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_staged_kernel(
             for (int q = 0; q < KS_JG; ++q) r2[q] = 0.0;
 #pragma unroll 2
             for (int k = 0; k < d; ++k) {
-                const double xk = xc[k * CPB + c];
-                const double2* xt = reinterpret_cast<const double2*>(xrow + (size_t)k * KS_ROW);
+                const double xk = xc[k * NC + c];
+                const double2* xt = reinterpret_cast<const double2*>(xrow + (size_t)k * ROW);
 #pragma unroll
                 for (int q = 0; q < KS_JG / 2; ++q) {
                     const double2 v = xt[q];
@@ -418,13 +425,14 @@ __global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_staged_kernel(
                 *reinterpret_cast<uint4*>(dst + (size_t)sl * slice_stride) = make_uint4(w[0], w[1], w[2], w[3]);
             }
         }
-        msum += __shfl_xor_sync(0xffffffffu, msum, 8);
-        msum += __shfl_xor_sync(0xffffffffu, msum, 16);
-        if (lane < CPB) red[warp * CPB + lane] = msum;
+        // lanes with the same candidate (lane % NC) hold partial means: fold the point-group bits of the lane index
+#pragma unroll
+        for (int o = NC; o < 32; o <<= 1) msum += __shfl_xor_sync(0xffffffffu, msum, o);
+        if (lane < NC) red[warp * NC + lane] = msum;
         __syncthreads();
-        if (threadIdx.x < CPB) {
+        if (threadIdx.x < NC) {
             double t = 0.0;
-            for (int w = 0; w < KS_THREADS / 32; ++w) t += red[w * CPB + threadIdx.x];
+            for (int w = 0; w < KS_THREADS / 32; ++w) t += red[w * NC + threadIdx.x];
             mean[split * mean_stride + c0 + threadIdx.x] = t;  // partial mean; the epilogue adds the splits in order
         }
     }
@@ -984,10 +992,13 @@ static int configure_carveout() {
     TB_CUDA(cudaFuncSetAttribute(kstar_mean_i8_kernel<TB200_MATERN12>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
     TB_CUDA(cudaFuncSetAttribute(kstar_mean_i8_kernel<TB200_MATERN32>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
     TB_CUDA(cudaFuncSetAttribute(kstar_mean_i8_kernel<TB200_MATERN52>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
-#define TB_STAGED_ATTR(KIND)                                                                                        \
-    TB_CUDA(cudaFuncSetAttribute(kstar_mean_i8_staged_kernel<KIND>, cudaFuncAttributePreferredSharedMemoryCarveout, mx)); \
-    TB_CUDA(cudaFuncSetAttribute(kstar_mean_i8_staged_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize,          \
-                                 (int)kstar_staged_smem(TB200_MAX_D)))
+#define TB_STAGED_ATTR(KIND)                                                                                            \
+    TB_CUDA(cudaFuncSetAttribute(kstar_mean_i8_staged_kernel<KIND, 8>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));  \
+    TB_CUDA(cudaFuncSetAttribute(kstar_mean_i8_staged_kernel<KIND, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,           \
+                                 (int)kstar_staged_smem(TB200_MAX_D, 8)));                                               \
+    TB_CUDA(cudaFuncSetAttribute(kstar_mean_i8_staged_kernel<KIND, 16>, cudaFuncAttributePreferredSharedMemoryCarveout, mx)); \
+    TB_CUDA(cudaFuncSetAttribute(kstar_mean_i8_staged_kernel<KIND, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize,          \
+                                 (int)kstar_staged_smem(TB200_MAX_D, 16)))
     TB_STAGED_ATTR(TB200_RBF);
     TB_STAGED_ATTR(TB200_MATERN12);
     TB_STAGED_ATTR(TB200_MATERN32);
@@ -1116,19 +1127,30 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
     // the ~57 KB the variance kernel leaves on an SM; TB200_KS_STAGED=0 keeps the direct-load kernel.  Measured
     // (profiles/r1_kstar_ncu_full.md): n=4096, d=10 (variance-bound step) 388.8 -> 376.2 ms per 2^21 candidates; at
     // n=1024, d=6 the step is K*-bound and four direct-load CTAs per SM beat three staged ones (5.49e7 vs 5.00e7 /s).
-    int staged_ctas = 0;
-    const int staged_splits = (NP + KS_CHUNK - 1) / KS_CHUNK;
-    if (use_i8 && staged_splits <= KS_STAGED_SPLITS && NP >= 2048) {
-        static int allow = -1, cap = 0;
+    int staged_ctas = 0, staged_nc = 8;
+    if (use_i8 && NP >= 2048) {
+        static int allow = -1, cap = 0, force_nc = 0;
         if (allow < 0) {
             const char* e = getenv("TB200_KS_STAGED");
             allow = (e && atoi(e) == 0) ? 0 : 1;
             const char* c = getenv("TB200_KS_STAGED_CTAS");  // diagnostics: cap on staged CTAs per SM
-            cap = (c && atoi(c) > 0) ? atoi(c) : 4;
+            cap = (c && atoi(c) > 0) ? atoi(c) : 2;          // measured: a third staged CTA costs the variance kernel more
+                                                             // than it gains (379.5 vs 375.5 ms per step, n=4096, d=10)
+            const char* f = getenv("TB200_KS_NC");           // diagnostics: candidates per item, 8 or 16
+            force_nc = (f && (atoi(f) == 8 || atoi(f) == 16)) ? atoi(f) : 0;
         }
-        const int fit = (int)((57 * 1024) / (kstar_staged_smem(d) + 1024));
-        if (allow && fit >= 2) staged_ctas = fit < cap ? fit : cap;
+        auto fit_of = [&](int nc) {
+            if ((NP + ks_chunk(nc) - 1) / ks_chunk(nc) > KS_STAGED_SPLITS) return 0;
+            const int f = (int)((57 * 1024) / (kstar_staged_smem(d, nc) + 1024));
+            return f < cap ? f : cap;
+        };
+        const int f8 = fit_of(8), f16 = fit_of(16);
+        // the 256-point chunk unless only the 128-point chunk fits twice (d = 11..21)
+        staged_nc = force_nc ? force_nc : ((f8 < 2 && f16 >= 2) ? 16 : 8);
+        const int f = staged_nc == 16 ? f16 : f8;
+        if (allow && f >= 2) staged_ctas = f;
     }
+    const int staged_splits = (NP + ks_chunk(staged_nc) - 1) / ks_chunk(staged_nc);
     const int mean_splits = staged_ctas ? staged_splits : ksplit;
 
     struct Batch { int sl; int64_t off, mb, mbp; };
@@ -1166,14 +1188,19 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
                 ks_per_sm = (e && atoi(e) > 0) ? atoi(e) : KS_CTAS_PER_SM;
             }
             const int kctas = g_sm_count * (staged_ctas ? staged_ctas : ks_per_sm);
-            const int kitems = ngroups * (staged_ctas ? staged_splits : ksplit);
+            const int st_groups = (int)(q.mbp / staged_nc);
+            const int kitems = staged_ctas ? st_groups * staged_splits : ngroups * ksplit;
             const dim3 kgrid((unsigned)(kitems < kctas ? kitems : kctas));
-            const size_t ksm_st = kstar_staged_smem(d);
+            const size_t ksm_st = kstar_staged_smem(d, staged_nc);
+#define TB_KSTAR_ST(KIND, NC)                                                                                          \
+    TB_LAUNCH((kstar_mean_i8_staged_kernel<KIND, NC>), kgrid, dim3(KS_THREADS), ksm_st, s_small, xc, q.mb, XsT, n, NP, \
+              *spec, theta, alpha, reinterpret_cast<uint8_t*>(w.Ks), slice_stride, w.mean, (long)batch, st_groups,     \
+              staged_splits)
 #define TB_KSTAR_I8(KIND)                                                                                              \
-    if (staged_ctas) {                                                                                                 \
-        TB_LAUNCH(kstar_mean_i8_staged_kernel<KIND>, kgrid, dim3(KS_THREADS), ksm_st, s_small, xc, q.mb, XsT, n, NP,   \
-                  *spec, theta, alpha, reinterpret_cast<uint8_t*>(w.Ks), slice_stride, w.mean, (long)batch, ngroups,   \
-                  staged_splits);                                                                                      \
+    if (staged_ctas && staged_nc == 16) {                                                                              \
+        TB_KSTAR_ST(KIND, 16);                                                                                         \
+    } else if (staged_ctas) {                                                                                          \
+        TB_KSTAR_ST(KIND, 8);                                                                                          \
     } else {                                                                                                           \
         TB_LAUNCH(kstar_mean_i8_kernel<KIND>, kgrid, dim3(KS_THREADS), ksm8, s_small, xc, q.mb, XsT, n, NP, *spec,     \
                   theta, alpha, reinterpret_cast<uint8_t*>(w.Ks), slice_stride, w.mean, jchunk, (long)batch, ngroups,  \
@@ -1186,6 +1213,7 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
                 default: TB_KSTAR_I8(TB200_MATERN52); break;
             }
 #undef TB_KSTAR_I8
+#undef TB_KSTAR_ST
         } else {
             TB_LAUNCH(kstar_mean_kernel, dim3((unsigned)(q.mbp / CPB), ksplit), dim3(256), ksm, s_small, xc, q.mb, XsT, n,
                       NP, *spec, theta, alpha, w.Ks, w.mean, jchunk, (long)batch);
