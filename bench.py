@@ -110,11 +110,18 @@ def cpu_reference_rate(sample, reps, n=N_TRAIN, d=DIM):
     """the oracle port timed on the host cores: predict + EI + argmax over `sample` candidates in
     chunks of 4096 (sklearn materialises K* and V the same way); best of `reps`. -> (cand/s, threads)"""
     from oracle import gp_oracle as O
+    # torchrun exports OMP_NUM_THREADS=1 to every rank: lift the BLAS pools back to all host cores so the
+    # CPU figure is the same with and without torchrun
     try:
-        from threadpoolctl import threadpool_info
+        cores = len(os.sched_getaffinity(0))
+    except AttributeError:
+        cores = os.cpu_count() or 1
+    try:
+        from threadpoolctl import threadpool_info, threadpool_limits
+        threadpool_limits(limits=cores)
         threads = max([p.get("num_threads", 1) for p in threadpool_info()] + [1])
     except Exception:
-        threads = os.cpu_count() or 1
+        threads = 1
     X, y, theta = synthetic_problem(n, d)
     gp = O.FittedGP(O.KernelSpec(O.KIND_MATERN52, d, True), theta, X, y)
     Xc = np.random.default_rng(1).random((sample, d))
