@@ -273,3 +273,17 @@ def test_gpy_surrogate_arguments_follow_the_reference():
         ARD, variance, lengthscale = False, np.array([0.5]), np.array([2.0])
     spec, prefix, params = G._describe_kernel(Exponential(), 2)
     assert (spec.kind, prefix) == (1, 'Exponential') and list(params) == [0.5, 2.0]
+
+
+def test_reference_arm_uses_all_host_cores_under_torchrun_env():
+    """torchrun exports OMP_NUM_THREADS=1; bench.py's CPU leg lifts the BLAS pools back to every core it may run on"""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = ("import bench, os; r, t = bench.cpu_reference_rate(256, 1, n=128, d=3); "
+            "print('THREADS', t, len(os.sched_getaffinity(0)), r > 0)")
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    out = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    m = re.search(r"THREADS (\d+) (\d+) True", out.stdout + out.stderr)  # bench.py keeps stdout for its one JSON line
+    assert m, out.stdout + out.stderr
+    assert int(m.group(1)) == int(m.group(2))
