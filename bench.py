@@ -140,6 +140,18 @@ def cpu_reference_rate(sample, reps, n=N_TRAIN, d=DIM):
     return sample / best, threads
 
 
+def cpu_fit_ms(n=N_TRAIN, d=DIM):
+    """one log-marginal-likelihood + gradient evaluation of the oracle port on the host cores (the reference's sklearn
+    fit evaluates its restarts one after another: sklearn:_gpr.py:312-333, :584-651). -> (ms, lml)"""
+    from oracle import gp_oracle as O
+    X, y, theta = synthetic_problem(n, d)
+    y_n = (y - y.mean()) / y.std()
+    spec = O.KernelSpec(O.KIND_MATERN52, d, True)
+    t0 = time.perf_counter()
+    lml, _ = O.log_marginal_likelihood(spec, theta, X, y_n, eval_gradient=True)
+    return 1e3 * (time.perf_counter() - t0), float(lml)
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU implementation of the path on the host cores.
     The reference is pure Python over scikit-learn (nothing compiles into oracle/_ref), so this times
@@ -168,6 +180,12 @@ def run_reference(args):
                                        "(NumPy/SciPy; same LAPACK/BLAS calls as the reference's sklearn path)" % sample},
             "e2e": {"value": value, "unit": "candidates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
+    if args.cpu_fit:
+        c_ms, _ = cpu_fit_ms()
+        line["fit"] = {"cpu_lml_grad_ms_one_restart": c_ms, "cpu_cores": threads, "restarts": args.restarts,
+                       "cpu_lml_grad_ms_all_restarts_extrapolated": c_ms * args.restarts,
+                       "cpu_note": "ONE LML+gradient evaluation (n=4096, d=10) timed once outside the steps; the "
+                                   "reference evaluates its restarts sequentially (extrapolated, not measured)"}
     emit(line)
 
 
@@ -378,6 +396,13 @@ def run_ours(args):
         cpu = {"value": rate, "unit": "candidates/s", "cores": threads, "kind": "port",
                "sample": "%d of the step's candidates in chunks of 4096, best of 2; oracle/gp_oracle.py "
                          "(NumPy/SciPy port of the reference's sklearn path)" % args.cpu_sample}
+        if args.cpu_fit:
+            c_ms, _ = cpu_fit_ms(n, d)
+            fit.update({"cpu_lml_grad_ms_one_restart": c_ms, "cpu_cores": threads,
+                        "cpu_lml_grad_ms_all_restarts_extrapolated": c_ms * R,
+                        "cpu_note": "ONE LML+gradient evaluation of the oracle port timed on the host cores; the "
+                                    "reference evaluates its restarts sequentially, so R of them are R times that "
+                                    "(extrapolated, not measured)"})
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": "candidates/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -408,6 +433,7 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="candidate batch per kernel pass (0 = library default)")
     ap.add_argument("--restarts", type=int, default=64)
     ap.add_argument("--cpu-sample", type=int, default=1 << 14)
+    ap.add_argument("--cpu-fit", type=int, default=1, help="also time one LML+gradient evaluation of the CPU port")
     ap.add_argument("--engine", default=None, help="variance engine: auto (default) | dmma | i8 | i8x")
     ap.add_argument("--full-fit", type=int, default=1, help="also time one whole fit (R restarts, <= 30 iterations)")
     args = ap.parse_args()
