@@ -914,8 +914,8 @@ static int launch_panel(const FitBuffers& fb, int NP, int R, int k, cudaStream_t
 // high-priority side stream of the batched fit (look-ahead of the diagonal block), one per device
 struct FitStreams {
     bool ready = false;
-    cudaStream_t side;
-    cudaEvent_t fork, join;
+    cudaStream_t side, look;
+    cudaEvent_t fork, join, fork_look, look_done;
 };
 static FitStreams g_fit_streams[64];
 static int fit_streams_for_device(FitStreams** out) {
@@ -929,10 +929,37 @@ static int fit_streams_for_device(FitStreams** out) {
         TB_CUDA(cudaStreamCreateWithPriority(&f.side, cudaStreamNonBlocking, hi));
         TB_CUDA(cudaEventCreateWithFlags(&f.fork, cudaEventDisableTiming));
         TB_CUDA(cudaEventCreateWithFlags(&f.join, cudaEventDisableTiming));
+        TB_CUDA(cudaStreamCreateWithPriority(&f.look, cudaStreamNonBlocking, hi));
+        TB_CUDA(cudaEventCreateWithFlags(&f.fork_look, cudaEventDisableTiming));
+        TB_CUDA(cudaEventCreateWithFlags(&f.look_done, cudaEventDisableTiming));
         f.ready = true;
     }
     *out = &f;
     return 0;
+}
+
+// Update of diagonal tiles by ONE panel: A[j,j] -= L[j,k] L[j,k]^T for `count` block rows j = j0.. (one 128^3 DMMA
+// product per tile and restart).  Look-ahead schedule of the batched INT8 fit: the long-K left-looking product of
+// diagonal tile k+1 over the panels 0..k-1 runs on a third stream while block column k is still being worked on, so
+// after panel k only this single-panel update and the latency-bound 128x128 factorisation remain on the critical path.
+static int launch_diag_update(const FitBuffers& fb, int NP, int R, int k, int j0, int count, cudaStream_t st) {
+    const long sK = (long)NP * NP;
+    const double* rows = fb.K + (long)j0 * TILE * NP + (long)k * TILE;
+    double* c = fb.K + (long)j0 * TILE * NP + (long)j0 * TILE;
+    GemmParams p = gemm_params(rows, NP, rows, NP, c, NP, 1, 1, TILE, -1.0, 1.0);
+    p.sA1 = sK; p.sB1 = sK; p.sC1 = sK;
+    p.sA2 = (long)TILE * NP; p.sB2 = (long)TILE * NP; p.sC2 = (long)TILE * NP + TILE;
+    return launch_gemm<false, true>(p, R, count, st);
+}
+
+// TB200_FIT_DIAG_RL=0 keeps the diagonal tile's whole update in step k itself (A/B switch)
+static bool fit_diag_right_looking() {
+    static int on = -1;
+    if (on < 0) {
+        const char* e = getenv("TB200_FIT_DIAG_RL");
+        on = (e && e[0] == '0') ? 0 : 1;
+    }
+    return on != 0;
 }
 
 // blocked Cholesky of R matrices in fb.K (lower), Dinv blocks kept for trtri
@@ -943,9 +970,26 @@ static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStr
     const bool i8fit = fit_uses_i8(NP, R) && fb.sliced != nullptr;
     if (i8fit)
         TB_LAUNCH(rowscale_from_diag_kernel, dim3((NP + 255) / 256, R), dim3(256), 0, st, fb.K, NP, fb.scale);
+    FitStreams* rl = nullptr;  // side stream of the right-looking diagonal-tile schedule (batched INT8 fit only)
+    if (i8fit && NB > 1 && fit_diag_right_looking() && fit_streams_for_device(&rl)) rl = nullptr;
     for (int k = 0; k < NB; ++k) {
         bool diag_done = false;
-        if (i8fit && k > 0) {
+        if (rl && k > 0) {
+            // The diagonal tile (k,k) was completed and factorised on the side stream right after panel k-1; only the
+            // rows below take the long-K INT8 product here.
+            if (NB - k > 1) {
+                i8::GemmI8Params g{};
+                g.S = fb.sliced; g.restartStride = (long)i8::S * sK; g.sliceStride = sK;
+                g.scale = fb.scale; g.scaleStride = NP;
+                g.C = fb.K; g.ldc = NP; g.cStride = sK;
+                g.kblks = NP / i8::KB; g.tri = 0;
+                g.rowTile0 = k + 1; g.colTile0 = 2 * k; g.nColTiles = 2; g.kbLo = 0; g.kbHi = 2 * k;
+                g.alpha = -1.0; g.beta = 1.0;
+                if (launch_fit_gemm_i8(g, (NB - k - 1) * 2, R, st, FIT_POTRF)) return -1;
+            }
+            TB_CUDA(cudaStreamWaitEvent(st, rl->join, 0));
+            diag_done = true;
+        } else if (i8fit && k > 0) {
             // same block-column update on the INT8 tensor cores: rows of L are already sliced up to column k*128.
             // Look-ahead: the diagonal tile's update and its 128x128 factorisation (a latency-bound 64-CTA kernel) run
             // on a high-priority side stream while the main stream updates the rows below.
@@ -982,6 +1026,16 @@ static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStr
         const int rem = NB - k - 1;
         if (rem == 0) break;
         if (launch_panel(fb, NP, R, k, st)) return -1;
+        if (rl) {
+            // side stream: add panel k to diagonal tile k+1 (panels 0..k-1 came from the look-ahead product) and
+            // factorise it
+            TB_CUDA(cudaEventRecord(rl->fork, st));
+            TB_CUDA(cudaStreamWaitEvent(rl->side, rl->fork, 0));
+            if (k >= 1) TB_CUDA(cudaStreamWaitEvent(rl->side, rl->look_done, 0));
+            if (launch_diag_update(fb, NP, R, k, k + 1, 1, rl->side)) return -1;
+            if (launch_diag(fb, NP, R, k + 1, info, rl->side)) return -1;
+            TB_CUDA(cudaEventRecord(rl->join, rl->side));
+        }
         if (i8fit) {
             // slice the finished panel L[(k+1)*128:, k*128:(k+1)*128] (k-blocks 2k, 2k+1 of those rows)
             const int rg0 = (k + 1) * (TILE / 8), rg1 = NP / 8;
@@ -989,6 +1043,20 @@ static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStr
             TB_LAUNCH(slice_operand_kernel<false>, dim3((unsigned)((pieces + 7) / 8), R), dim3(256), 0, st, fb.K, NP, sK,
                       fb.scale, (const double*)nullptr, 0, rg0, rg1, 2 * k, 2 * k + 2, 0, 0, fb.sliced, sK,
                       (long)i8::S * sK, NP / i8::KB);
+        }
+        if (rl && k + 2 < NB) {
+            // look-ahead stream: diagonal tile k+2 -= L[k+2, 0:(k+1)*128] L[k+2, 0:(k+1)*128]^T (panels 0..k, all sliced)
+            TB_CUDA(cudaEventRecord(rl->fork_look, st));
+            TB_CUDA(cudaStreamWaitEvent(rl->look, rl->fork_look, 0));
+            i8::GemmI8Params g{};
+            g.S = fb.sliced; g.restartStride = (long)i8::S * sK; g.sliceStride = sK;
+            g.scale = fb.scale; g.scaleStride = NP;
+            g.C = fb.K; g.ldc = NP; g.cStride = sK;
+            g.kblks = NP / i8::KB; g.tri = 0;
+            g.rowTile0 = k + 2; g.colTile0 = 2 * (k + 2); g.nColTiles = 2; g.kbLo = 0; g.kbHi = 2 * (k + 1);
+            g.alpha = -1.0; g.beta = 1.0;
+            if (launch_fit_gemm_i8(g, 2, R, rl->look, FIT_POTRF)) return -1;
+            TB_CUDA(cudaEventRecord(rl->look_done, rl->look));
         }
         if (!left) {
             // trailing: A[i,j] -= A[i,k] A[j,k]^T  (k < j <= i)
