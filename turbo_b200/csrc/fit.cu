@@ -1099,6 +1099,11 @@ static int trtri_batched_i8(const FitBuffers& fb, double* Linv, int NP, int R, c
     TB_CUDA(cudaMemsetAsync(fb.smax, 0, sizeof(double) * (size_t)R * NP, st));
     const double* none = nullptr;
     double* tsc = fb.scale;  // column scales t_k of X as doubles (fb.scale is free between potrf and the K^-1 step)
+    // the byte slices of the finished X block column and the weighted L panel of this step only share their inputs:
+    // the former runs on the look-ahead stream next to the latter's column maxima, scales and slices
+    FitStreams* ov = nullptr;
+    static const bool overlap = !(getenv("TB200_FIT_TRTRI_OVERLAP") && getenv("TB200_FIT_TRTRI_OVERLAP")[0] == '0');
+    if (!overlap || fit_streams_for_device(&ov)) ov = nullptr;
     for (int c = NB - 2; c >= 0; --c) {
         const int c1 = c + 1, rem = NB - c1;
         // column scales of the finished block column c1 of X, then its byte slices (rows >= c1*128, k-blocks 2c1, 2c1+1)
@@ -1107,9 +1112,16 @@ static int trtri_batched_i8(const FitBuffers& fb, double* Linv, int NP, int R, c
         {
             const int rg0 = c1 * (TILE / 8), rg1 = NP / 8;
             const long pieces = (long)(rg1 - rg0) * 2;
-            TB_LAUNCH(slice_operand_kernel<false>, dim3((unsigned)((pieces + 7) / 8), R), dim3(256), 0, st, Linv, NP, sK,
+            cudaStream_t ss = st;
+            if (ov) {
+                TB_CUDA(cudaEventRecord(ov->fork_look, st));
+                TB_CUDA(cudaStreamWaitEvent(ov->look, ov->fork_look, 0));
+                ss = ov->look;
+            }
+            TB_LAUNCH(slice_operand_kernel<false>, dim3((unsigned)((pieces + 7) / 8), R), dim3(256), 0, ss, Linv, NP, sK,
                       none, (const double*)tsc, 2, rg0, rg1, 2 * c1, 2 * c1 + 2, 0, 0, fb.sliced, sK, (long)i8::S * sK,
                       kblks);
+            if (ov) TB_CUDA(cudaEventRecord(ov->look_done, ov->look));
         }
         // weighted panel L[k, c-block] * t_k (k >= c1*128): column scales, then transposed byte slices
         TB_LAUNCH(colmax_bits_kernel, dim3(rem, R), dim3(128), 0, st, fb.K, NP, sK, c * TILE, c1 * TILE,
@@ -1123,6 +1135,7 @@ static int trtri_batched_i8(const FitBuffers& fb, double* Linv, int NP, int R, c
                       bSlice, bRestart, kblks);
         }
         // T[i, c-block] = -sum_k (X[i,k]/t_k) (L[k,c] t_k), rows of block rows c1.., k-blocks [2c1, 2(it+1))
+        if (ov) TB_CUDA(cudaStreamWaitEvent(st, ov->look_done, 0));
         {
             i8::GemmI8Params g{};
             g.S = fb.sliced; g.restartStride = (long)i8::S * sK; g.sliceStride = sK;
