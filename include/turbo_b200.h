@@ -7,7 +7,12 @@
  *
  * Conventions
  *   - every pointer is a DEVICE pointer unless the name ends in _host; the caller owns all
- *     buffers (PyTorch tensors in the shipped host layer), the library allocates nothing;
+ *     DATA buffers (PyTorch tensors in the shipped host layer): the library allocates no device
+ *     memory.  It does own, per device it is used on, a handful of CUDA streams and events (two
+ *     internal streams of the acquisition pipeline, two of the batched fit; created on first use
+ *     under a mutex, released by tb200_shutdown()) and sets per-device function attributes once;
+ *   - calls may come from any host thread (turbo's Qt GUI runs the optimiser on a QThread,
+ *     turbo/gui/qt.py:139-147); a call is not re-entrant on the same workspace;
  *   - all reals are IEEE FP64, indices int64, matrices C-contiguous row-major;
  *   - NP = tb200_padded_n(n) = n rounded up to 128.  Padded rows/cols of a factor are the
  *     identity, padded vector entries are 0, so padding never changes a result;
@@ -73,6 +78,13 @@ typedef struct {
 int tb200_version(void);
 const char* tb200_last_error(void);
 int tb200_padded_n(int n);
+/* destroy the per-device streams and events the library created (they are re-created on the next use);
+ * synchronises them first.  Call before unloading the library or resetting a device. */
+int tb200_shutdown(void);
+/* the library's single debug hook is the environment variable TB200_DEBUG ("key=value,key=value": fit_engine=dmma,
+ * fit_gmax=7|8|9, fit_gmax_trtri, fit_gmax_kinv, acq_gmax; csrc/common.cuh), read ONCE on first use -- never on the
+ * call path.  tb200_debug_reload re-reads it (for tests that change it inside one process). */
+int tb200_debug_reload(void);
 
 /* bytes of scratch the calls below need */
 size_t tb200_fit_workspace_bytes(int n, int d, int R, int with_grad);
@@ -127,6 +139,7 @@ int tb200_min_sqdist(const double* Xq, int64_t m, const double* X, int n, int d,
  * V = L^-1 k* is assembled exactly from 7 byte slices per operand with INT32 accumulation.
  *   tb200_i8_prepare: slice the inverse factor once per model.  linvS: tb200_i8_factor_bytes(n) bytes;
  *     rowscale: 2*NP doubles (scale sf2*2^e_r per row, then the exponents e_r).
+ *   gmax = 7: 21 slice products of 6 digit planes (truncation ~2^-46 of row-max*sf2 per term);
  *   gmax = 8: 28 slice products (truncation ~2^-54 of row-max*sf2 per term, >= 40x inside the parity floor);
  *   gmax = 9: 34 products, indistinguishable from an FP64 GEMM.  INT32 accumulation is exact for 8192 training
  *   points per pass (balanced s8 digits of L^-1); rows longer than that are accumulated in several passes that are
@@ -156,6 +169,10 @@ int tb200_generate_candidates(const tb200_cand_spec* cand_host, int d, int64_t i
 /* measured FP64 peaks of this device (roofline denominators for the DMMA kernels):
  * runs register-resident DMMA.8x8x4 / DFMA loops on every SM for ~`ms` milliseconds each. */
 int tb200_fp64_peak(double ms, double* dmma_tflops_host, double* dfma_tflops_host);
+/* measured INT8 tensor-core peak of this device in TOP/s (2 operations per multiply-accumulate): the roofline
+ * denominator of the tcgen05.mma kind::i8 kernels (predictive variance, batched fit products).  One CTA per SM issues
+ * M128 x N256 x K32 MMAs on shared-memory-resident operands for ~`ms` milliseconds; best of 5 repetitions. */
+int tb200_i8_peak(double ms, double* int8_tops_host);
 
 /* Incremental refit at fixed hyper-parameters (the reference's `training_iterations` callable returning 0,
  * turbo/modules/surrogates.py:250-269, :306-310): append ONE training point to the factor in O(n^2).

@@ -87,7 +87,9 @@ def test_predict_matches_reference(golden):
     mu, sigma = model.predict(g["Xc"], return_std_dev=True)
     assert mu.shape == sigma.shape == (g["Xc"].shape[0],)
     np.testing.assert_allclose(mu, g["mu"], rtol=1e-8, atol=1e-8 * np.abs(g["y"]).max())
-    np.testing.assert_allclose(sigma ** 2, g["sigma"] ** 2, rtol=1e-8, atol=_var_floor(g, model))
+    from conftest import check_variance
+    prior = (np.exp(g["theta"][0]) if g["has_const"] else 1.0) * model.y_std ** 2
+    check_variance("golden/%s/auto" % g["name"], sigma ** 2, g["sigma"] ** 2, g["X"].shape[0], prior)
     mu_only = model.predict(g["Xc"][:5])
     np.testing.assert_array_equal(mu_only, mu[:5])
 

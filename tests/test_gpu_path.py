@@ -187,8 +187,9 @@ def test_full_size_properties(n, d, kind):
     omu, osd = og.predict(Xc)
     mu, sd = model.predict(Xc, return_std_dev=True)
     np.testing.assert_allclose(mu, omu, rtol=1e-8, atol=1e-8 * np.abs(y).max())
-    floor = 256 * np.finfo(float).eps * n * model.y_std ** 2
-    np.testing.assert_allclose(sd ** 2, osd ** 2, rtol=1e-8, atol=floor)
+    from conftest import check_variance
+    check_variance("full_size/n%d_d%d_kind%d" % (n, d, kind), sd ** 2, osd ** 2, n,
+                   (1.0 + np.exp(theta[-1])) * model.y_std ** 2)
     assert model.get_log_likelihood() == pytest.approx(og.lml(), rel=1e-6)
     # (4) sharding the candidate index range does not change the winner (what multi-GPU relies on)
     from turbo_b200 import _lib, device, dist

@@ -279,8 +279,10 @@ def test_reference_arm_uses_all_host_cores_under_torchrun_env():
     """torchrun exports OMP_NUM_THREADS=1; bench.py's CPU leg lifts the BLAS pools back to every core it may run on"""
     import subprocess
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    code = ("import bench, os; r, t = bench.cpu_reference_rate(256, 1, n=128, d=3); "
-            "print('THREADS', t, len(os.sched_getaffinity(0)), r > 0)")
+    code = ("import bench, os, numpy as np; cfg = dict(bench.CONFIGS['headline'], n=128, d=3); "
+            "X, y, th = bench.synthetic_problem(128, 3); arm = bench.CpuArm(cfg, X, y, th); "
+            "r, top = arm.rate(bench.step_candidates_host(cfg, 1 << 20, 256)); "
+            "print('THREADS', arm.threads, len(os.sched_getaffinity(0)), r > 0)")
     env = dict(os.environ, OMP_NUM_THREADS="1")
     out = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stderr[-2000:]

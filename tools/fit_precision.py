@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """diagnostic: accuracy and time of the batched LML+gradient under the per-stage slice-product switches
-(TB200_FIT_ENGINE, TB200_FIT_GMAX, TB200_FIT_GMAX_TRTRI, TB200_FIT_GMAX_KINV), n=4096, d=10, R=64.
-    TB200_FIT_...=.. python tools/fit_precision.py run <tag>     # writes gpurun_out/fitprec_<tag>.npz
+(TB200_DEBUG=fit_engine=dmma,fit_gmax=..,fit_gmax_trtri=..,fit_gmax_kinv=..; csrc/common.cuh), n=4096, d=10, R=64.
+    TB200_DEBUG=.. python tools/fit_precision.py run <tag>     # writes gpurun_out/fitprec_<tag>.npz
     python tools/fit_precision.py compare <ref_tag> <tag> [<tag> ..]"""
 import os
 import sys

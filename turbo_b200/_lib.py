@@ -12,7 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("TB200_LIB") or os.path.join(_HERE, "libturbo_b200.so")  # TB200_LIB: A/B builds
 MAX_D = 64
-I8_MAX_N = 32768  # TB200_I8_MAX_N
+I8_MAX_N = 32768  # TB200_I8_MAX_N (include/turbo_b200.h)
 
 KIND_RBF, KIND_MATERN12, KIND_MATERN32, KIND_MATERN52 = 0, 1, 2, 3
 ACQ_EI, ACQ_PI, ACQ_UCB = 0, 1, 2
@@ -43,6 +43,8 @@ _SIGNATURES = {
     "tb200_version": (C.c_int, []),
     "tb200_last_error": (C.c_char_p, []),
     "tb200_padded_n": (C.c_int, [C.c_int]),
+    "tb200_shutdown": (C.c_int, []),
+    "tb200_debug_reload": (C.c_int, []),
     "tb200_fit_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int, C.c_int]),
     "tb200_acquire_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int64]),
     "tb200_default_batch": (C.c_int64, [C.c_int]),
@@ -69,6 +71,7 @@ _SIGNATURES = {
     "tb200_min_sqdist": (C.c_int, [_P, C.c_int64, _P, C.c_int, C.c_int, _P, _P, _P]),
     "tb200_generate_candidates": (C.c_int, [C.POINTER(CandSpecC), C.c_int, C.c_int64, C.c_int64, _P, _P]),
     "tb200_fp64_peak": (C.c_int, [C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "tb200_i8_peak": (C.c_int, [C.c_double, C.POINTER(C.c_double)]),
     "tb200_append_workspace_bytes": (C.c_size_t, [C.c_int]),
     "tb200_factor_append": (C.c_int, [_P, _P, _P, _P, C.c_int, C.POINTER(KernelSpecC), _P, C.c_double, _P, _P,
                                       C.c_size_t, _P]),

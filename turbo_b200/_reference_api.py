@@ -2,19 +2,50 @@
 
 turbo.plotting / turbo.recorder decide what they can draw with ``isinstance`` checks against
 ``turbo.modules`` classes (plotting/surrogates.py:67-75, plotting/overview.py:53-61), so when
-mbway/turbo is importable our plugins SUBCLASS its classes.  On a machine without the reference
-(the GPU box) the same names are bound to minimal stand-ins with the same constructor arguments
-and method names, so the host layer and its tests run unchanged.
+mbway/turbo is importable our plugins SUBCLASS its classes.  ``turbo`` is looked for on the normal
+import path first, then in the directory named by ``TB200_TURBO_PATH``, then in ``baseline/_ref`` next to
+this package (the unmodified reference installed by ``baseline/install_reference.py``, which is how the
+GPU box gets it).  Only on a machine with none of those are the names bound to minimal stand-ins with the
+same constructor arguments and method names, so the host layer still imports.
 """
-try:  # pragma: no cover - depends on the environment
-    import turbo.modules as _tm
+import importlib
+import os
+import sys
+import warnings
 
+
+def _import_turbo_modules():
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore", SyntaxWarning)  # the reference's docstrings hold '\m' escapes
+        return _import_turbo_modules_impl()
+
+
+def _import_turbo_modules_impl():
+    try:
+        return importlib.import_module("turbo.modules")
+    except Exception:
+        pass
+    here = os.path.dirname(os.path.abspath(__file__))
+    for cand in (os.environ.get("TB200_TURBO_PATH"), os.path.join(os.path.dirname(here), "baseline", "_ref")):
+        if cand and os.path.isfile(os.path.join(cand, "turbo", "__init__.py")) and cand not in sys.path:
+            sys.path.append(cand)
+            for k in [k for k in sys.modules if k == "turbo" or k.startswith("turbo.")]:
+                del sys.modules[k]  # a half-imported package from the failed attempt
+            try:
+                return importlib.import_module("turbo.modules")
+            except Exception:
+                sys.path.remove(cand)
+    return None
+
+
+_tm = _import_turbo_modules()
+if _tm is not None:  # pragma: no cover - depends on the environment
     HAVE_TURBO = True
     Surrogate = _tm.Surrogate
     SciKitModelInstance = _tm.SciKitGPSurrogate.ModelInstance
     GPyModelInstance = _tm.GPySurrogate.ModelInstance  # defined even when GPy itself is missing
     EI, PI, UCB = _tm.EI, _tm.PI, _tm.UCB
-except Exception:  # turbo (or one of its imports) is not available
+else:  # turbo (or one of its imports) is not available
     HAVE_TURBO = False
 
     class Surrogate:

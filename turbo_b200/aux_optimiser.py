@@ -66,21 +66,38 @@ class GpuCandidateArgmax:
                 X = np.hstack(cols)
             else:
                 X = np.asarray(self.candidates(self.num_random, latent_bounds), dtype=np.float64)
+            if self.group is not None:
+                # host-drawn sets come from each process's own generator: argmax_over shards ONE set by index, so the
+                # set rank 0 drew is the set (every rank still consumes its generator, keeping the streams aligned)
+                from . import dist
+                X = dist.broadcast_array(X, self.group, src=0)
             res = acq.argmax_over(candidates=X, group=self.group, keep_top=keep, exclude=exclude)
         val, idx, x = res[:3]
         if keep:
             top = res[3]
         self._calls += 1
+        polished = False
         if self.grad_restarts > 0 and x is not None:
+            x_random = x
             val, x = self._polish(acq, lo, hi, val, idx, x, top, seed, maximisation_info)
+            polished = x is not x_random
         if self.release_model and hasattr(acq.model, 'release'):
             acq.model.release()
         if x is None:  # auxiliary_optimisers.py:117-118
             maximisation_info['max_acq'] = -math.inf
             return None, maximisation_info
         x = np.clip(x, lo, hi)  # :120-124
-        maximisation_info.update({'max_acq': float(val), 'argmax_index': int(idx), 'num_candidates': self.num_random})
+        maximisation_info.update({'max_acq': float(val), 'num_candidates': self.num_random})
+        # the index belongs to the random stage: a polished point is not a member of the candidate set
+        maximisation_info['random_stage_argmax_index' if polished else 'argmax_index'] = int(idx)
         return x, maximisation_info
+
+    def __getstate__(self):
+        """pickled with the optimiser by the Recorder (recorder.py:117-146): a process-group object does not pickle"""
+        s = dict(self.__dict__)
+        if not (s.get('group') is None or isinstance(s.get('group'), str)):
+            s['group'] = None
+        return s
 
     def _polish(self, acq, lo, hi, val, idx, x, top, seed, info):
         """gradient stage of auxiliary_optimisers.py:69-112 on the device: every start advances in lock step"""

@@ -213,7 +213,7 @@ __device__ __forceinline__ void slice_signed(double a, uint8_t (&u)[i8::S]) {
 constexpr int KS_THREADS = 128;  // 16 point groups x 8 candidates; small CTAs share an SM with a variance CTA
 constexpr int KS_JG = 16;        // training points per thread and pass
 constexpr int KS_CTAS_PER_SM = 4;  // persistent grid: 3 x 128 threads x 80 registers fit beside one variance CTA, a 4th
-                                   // where none is resident (measured: n=1024 +10 %, n=4096 unchanged; TB200_KS_CTAS)
+                                   // where none is resident (measured in round 1: n=1024 +10 %, n=4096 unchanged)
 
 template <int KIND>
 __global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_kernel(
@@ -579,12 +579,13 @@ static size_t msd_smem(int d) { return sizeof(double) * (size_t)d * (MSD_THREADS
 
 static int launch_min_sqdist(const double* Xc, int64_t m, const double* X, int n, int d, double* min_out,
                              int64_t* arg_out, cudaStream_t st) {
-    static bool configured = false;
-    if (!configured) {
-        TB_CUDA(cudaFuncSetAttribute(min_sqdist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)msd_smem(TB200_MAX_D)));
-        configured = true;
-    }
+    static DeviceOnce once;
+    if (device_once(once, [] {
+            TB_CUDA(cudaFuncSetAttribute(min_sqdist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)msd_smem(TB200_MAX_D)));
+            return 0;
+        }))
+        return -1;
     if (m <= 0) return 0;
     // few candidates (one pipeline batch): split the points over blockIdx.y so the launch fills the machine
     const int64_t ctas = (m + MSD_THREADS - 1) / MSD_THREADS;
@@ -871,6 +872,8 @@ static void trace_mark(int tag, cudaStream_t st) {
     g_trace_recs.push_back({e, tag});
 }
 
+int fit_streams_destroy();  // fit.cu
+
 struct AcqBuffers {
     double* cand;     // [batch][d]   generated candidates
     double* Ks;       // [batch][NP]
@@ -947,23 +950,22 @@ struct AcqStreams {
     cudaEvent_t fork, join_small, join_var;
     cudaEvent_t kdone[ACQ_SLOTS], vdone[ACQ_SLOTS];
 };
-static AcqStreams g_streams[64];
-static int g_acq_streams = -1;  // -1: read TB200_ACQ_STREAMS on first use
+static AcqStreams g_streams[MAX_DEVICES];
+static std::mutex g_streams_mutex;
 
 static int acq_streams_for_device(AcqStreams** out) {
     int dev = 0;
     TB_CUDA(cudaGetDevice(&dev));
-    TB_CHECK(dev >= 0 && dev < 64, "device ordinal out of range");
+    TB_CHECK(dev >= 0 && dev < MAX_DEVICES, "device ordinal out of range");
+    std::lock_guard<std::mutex> lock(g_streams_mutex);
     AcqStreams& a = g_streams[dev];
     if (!a.ready) {
         int lo = 0, hi = 0;  // numerically lower = higher priority
         TB_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
         // the small kernels get the high priority: their few CTAs are placed at once and the variance grid keeps
-        // filling the rest of each SM (TB200_ACQ_PRIORITY=var flips it, for experiments)
-        const char* flip = getenv("TB200_ACQ_PRIORITY");
-        const bool small_high = !(flip && flip[0] == 'v');
-        TB_CUDA(cudaStreamCreateWithPriority(&a.small, cudaStreamNonBlocking, small_high ? hi : lo));
-        TB_CUDA(cudaStreamCreateWithPriority(&a.var, cudaStreamNonBlocking, small_high ? lo : hi));
+        // filling the rest of each SM (the flipped assignment measured slower in round 1)
+        TB_CUDA(cudaStreamCreateWithPriority(&a.small, cudaStreamNonBlocking, hi));
+        TB_CUDA(cudaStreamCreateWithPriority(&a.var, cudaStreamNonBlocking, lo));
         for (int i = 0; i < ACQ_SLOTS; ++i) {
             TB_CUDA(cudaEventCreateWithFlags(&a.kdone[i], cudaEventDisableTiming));
             TB_CUDA(cudaEventCreateWithFlags(&a.vdone[i], cudaEventDisableTiming));
@@ -980,12 +982,10 @@ static int acq_streams_for_device(AcqStreams** out) {
 // All kernels that share the SMs with the variance kernel ask for the same (maximum) shared-memory carve-out: an SM
 // whose resident CTAs were launched with a small carve-out cannot take a 174 KB variance CTA until it has drained and
 // been reconfigured, which serialised the "concurrent" K* and variance kernels (tools/trace_acquire.py).
-static bool g_carveout_set[64] = {};
-static int configure_carveout() {
+static DeviceOnce g_carveout_once;
+static int configure_carveout_device() {
     int dev = 0;
     TB_CUDA(cudaGetDevice(&dev));
-    TB_CHECK(dev >= 0 && dev < 64, "device ordinal out of range");
-    if (g_carveout_set[dev]) return 0;
     TB_CUDA(cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev));
     const int mx = (int)cudaSharedmemCarveoutMaxShared;
     TB_CUDA(cudaFuncSetAttribute(kstar_mean_i8_kernel<TB200_RBF>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
@@ -1008,9 +1008,9 @@ static int configure_carveout() {
     TB_CUDA(cudaFuncSetAttribute(acquire_epilogue_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
     TB_CUDA(cudaFuncSetAttribute(generate_candidates_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
     TB_CUDA(cudaFuncSetAttribute(best_reset_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
-    g_carveout_set[dev] = true;
     return 0;
 }
+static int configure_carveout() { return device_once(g_carveout_once, configure_carveout_device); }
 
 }  // namespace tb200
 
@@ -1076,7 +1076,7 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
     TB_CHECK(spec->kind >= TB200_RBF && spec->kind <= TB200_MATERN52, "unknown kernel kind");
     TB_CHECK(spec->d >= 1 && spec->d <= TB200_MAX_D, "d out of range (1..64)");
     TB_CHECK(acq->acq >= TB200_EI && acq->acq <= TB200_UCB, "unknown acquisition function");
-    TB_CHECK(!use_i8 || (f8.gmax == 8 || f8.gmax == 9), "i8 engine: gmax must be 8 or 9");
+    TB_CHECK(!use_i8 || (f8.gmax >= 7 && f8.gmax <= 9), "i8 engine: gmax must be 7, 8 or 9");
     TB_CHECK(!use_i8 || pad_n(n) <= TB200_I8_MAX_N, "i8 engine: n above TB200_I8_MAX_N");
     const int mode = cand ? cand->mode : TB200_CAND_GIVEN;
     if (m <= 0) return 0;
@@ -1093,15 +1093,9 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
     const int ntiles = use_i8 ? NP / i8::TN : NB;  // row tiles of the variance partials
     const long slice_stride = (long)batch * NP;   // bytes between K* byte slices (i8 engine)
 
-    if (g_acq_streams < 0) {
-        const char* e = getenv("TB200_ACQ_STREAMS");
-        g_acq_streams = e ? atoi(e) : ACQ_SLOTS;  // number of buffer slots in flight (1 = serial)
-        if (g_acq_streams < 1) g_acq_streams = 1;
-        if (g_acq_streams > ACQ_SLOTS) g_acq_streams = ACQ_SLOTS;
-    }
-    // one batch, serial mode, or GEMM timing requested: everything on the caller's stream
+    // one batch, or GEMM timing requested: everything on the caller's stream
     const int64_t nbatches = (m + batch - 1) / batch;
-    const int slots = (nbatches < 2 || g_time_gemm) ? 1 : g_acq_streams;
+    const int slots = (nbatches < 2 || g_time_gemm) ? 1 : ACQ_SLOTS;
     if (configure_carveout()) return -1;
     AcqStreams* as = nullptr;
     cudaStream_t s_small = st, s_var = st;
@@ -1124,31 +1118,23 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
     if (use_i8 && jchunk < 2 * TILE) jchunk = 2 * TILE;
     ksplit = (NP + jchunk - 1) / jchunk;
     // staged K* kernel (training-point chunk in shared memory): 2048 <= n <= 4096 and at least two CTAs of it fit into
-    // the ~57 KB the variance kernel leaves on an SM; TB200_KS_STAGED=0 keeps the direct-load kernel.  Measured
+    // the ~57 KB the variance kernel leaves on an SM.  Measured
     // (profiles/r1_kstar_ncu_full.md): n=4096, d=10 (variance-bound step) 388.8 -> 376.2 ms per 2^21 candidates; at
     // n=1024, d=6 the step is K*-bound and four direct-load CTAs per SM beat three staged ones (5.49e7 vs 5.00e7 /s).
     int staged_ctas = 0, staged_nc = 8;
     if (use_i8 && NP >= 2048) {
-        static int allow = -1, cap = 0, force_nc = 0;
-        if (allow < 0) {
-            const char* e = getenv("TB200_KS_STAGED");
-            allow = (e && atoi(e) == 0) ? 0 : 1;
-            const char* c = getenv("TB200_KS_STAGED_CTAS");  // diagnostics: cap on staged CTAs per SM
-            cap = (c && atoi(c) > 0) ? atoi(c) : 2;          // measured: a third staged CTA costs the variance kernel more
-                                                             // than it gains (379.5 vs 375.5 ms per step, n=4096, d=10)
-            const char* f = getenv("TB200_KS_NC");           // diagnostics: candidates per item, 8 or 16
-            force_nc = (f && (atoi(f) == 8 || atoi(f) == 16)) ? atoi(f) : 0;
-        }
+        // at most two staged CTAs per SM: a third costs the variance kernel more than it gains (379.5 vs 375.5 ms per
+        // step at n=4096, d=10, round 1)
         auto fit_of = [&](int nc) {
             if ((NP + ks_chunk(nc) - 1) / ks_chunk(nc) > KS_STAGED_SPLITS) return 0;
             const int f = (int)((57 * 1024) / (kstar_staged_smem(d, nc) + 1024));
-            return f < cap ? f : cap;
+            return f < 2 ? f : 2;
         };
         const int f8 = fit_of(8), f16 = fit_of(16);
         // the 256-point chunk unless only the 128-point chunk fits twice (d = 11..21)
-        staged_nc = force_nc ? force_nc : ((f8 < 2 && f16 >= 2) ? 16 : 8);
+        staged_nc = (f8 < 2 && f16 >= 2) ? 16 : 8;
         const int f = staged_nc == 16 ? f16 : f8;
-        if (allow && f >= 2) staged_ctas = f;
+        if (f >= 2) staged_ctas = f;
     }
     const int staged_splits = (NP + ks_chunk(staged_nc) - 1) / ks_chunk(staged_nc);
     const int mean_splits = staged_ctas ? staged_splits : ksplit;
@@ -1182,12 +1168,7 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
         if (use_i8) {
             const size_t ksm8 = sizeof(double) * (CPB * d + (KS_THREADS / 32) * CPB);
             const int ngroups = (int)(q.mbp / CPB);
-            static int ks_per_sm = 0;
-            if (!ks_per_sm) {
-                const char* e = getenv("TB200_KS_CTAS");  // diagnostics: persistent K* CTAs per SM
-                ks_per_sm = (e && atoi(e) > 0) ? atoi(e) : KS_CTAS_PER_SM;
-            }
-            const int kctas = g_sm_count * (staged_ctas ? staged_ctas : ks_per_sm);
+            const int kctas = g_sm_count * (staged_ctas ? staged_ctas : KS_CTAS_PER_SM);
             const int st_groups = (int)(q.mbp / staged_nc);
             const int kitems = staged_ctas ? st_groups * staged_splits : ngroups * ksplit;
             const dim3 kgrid((unsigned)(kitems < kctas ? kitems : kctas));
@@ -1239,7 +1220,10 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
             ip.kblks = NP / i8::KB;
             ip.rowTiles = NP / i8::TN;
             ip.candTiles = (int)(q.mbp / i8::TM);
-            if (f8.gmax == 8 ? i8::launch_colsumsq_i8<8>(ip, s_var) : i8::launch_colsumsq_i8<9>(ip, s_var)) return -1;
+            const int rc = f8.gmax == 7   ? i8::launch_colsumsq_i8<7>(ip, s_var)
+                           : f8.gmax == 8 ? i8::launch_colsumsq_i8<8>(ip, s_var)
+                                          : i8::launch_colsumsq_i8<9>(ip, s_var);
+            if (rc) return -1;
         } else {
             GemmParams gp = gemm_params(Linv, NP, w.Ks, NP, w.partial, batch, NB, (int)(q.mbp / 128), NP, 1.0, 0.0);
             gp.order = ORDER_RECT_HEAVY_LAST_ROW_FIRST;
@@ -1267,26 +1251,37 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
         for (int64_t bno = 0; bno < nbatches; ++bno)
             if (front(bno) || variance(bno) || epilogue(bno)) return -1;
     } else {
-        for (int64_t bno = 0; bno < slots && bno < nbatches; ++bno) {
-            if (front(bno)) return -1;
-            TB_CUDA(cudaEventRecord(as->kdone[bno % slots], s_small));
-        }
-        for (int64_t bno = 0; bno < nbatches; ++bno) {
-            const int sl = (int)(bno % slots);
-            TB_CUDA(cudaStreamWaitEvent(s_var, as->kdone[sl], 0));
-            if (variance(bno)) return -1;
-            TB_CUDA(cudaEventRecord(as->vdone[sl], s_var));
-            TB_CUDA(cudaStreamWaitEvent(s_small, as->vdone[sl], 0));
-            if (epilogue(bno)) return -1;
-            if (bno + slots < nbatches) {
-                if (front(bno + slots)) return -1;
-                TB_CUDA(cudaEventRecord(as->kdone[sl], s_small));
+        auto pipeline = [&]() -> int {
+            for (int64_t bno = 0; bno < slots && bno < nbatches; ++bno) {
+                if (front(bno)) return -1;
+                TB_CUDA(cudaEventRecord(as->kdone[bno % slots], s_small));
             }
+            for (int64_t bno = 0; bno < nbatches; ++bno) {
+                const int sl = (int)(bno % slots);
+                TB_CUDA(cudaStreamWaitEvent(s_var, as->kdone[sl], 0));
+                if (variance(bno)) return -1;
+                TB_CUDA(cudaEventRecord(as->vdone[sl], s_var));
+                TB_CUDA(cudaStreamWaitEvent(s_small, as->vdone[sl], 0));
+                if (epilogue(bno)) return -1;
+                if (bno + slots < nbatches) {
+                    if (front(bno + slots)) return -1;
+                    TB_CUDA(cudaEventRecord(as->kdone[sl], s_small));
+                }
+            }
+            TB_CUDA(cudaEventRecord(as->join_small, s_small));
+            TB_CUDA(cudaEventRecord(as->join_var, s_var));
+            TB_CUDA(cudaStreamWaitEvent(st, as->join_small, 0));
+            TB_CUDA(cudaStreamWaitEvent(st, as->join_var, 0));
+            return 0;
+        };
+        if (pipeline()) {
+            // a failed launch or CUDA call part-way: the two internal streams were forked from the caller's stream and
+            // may still be reading the workspace the caller is about to free.  Drain them before reporting the error
+            // (the message of the first failure is already in g_err).
+            cudaStreamSynchronize(s_small);
+            cudaStreamSynchronize(s_var);
+            return -1;
         }
-        TB_CUDA(cudaEventRecord(as->join_small, s_small));
-        TB_CUDA(cudaEventRecord(as->join_var, s_var));
-        TB_CUDA(cudaStreamWaitEvent(st, as->join_small, 0));
-        TB_CUDA(cudaStreamWaitEvent(st, as->join_var, 0));
     }
     TB_LAUNCH(best_merge_kernel, dim3(1), dim3(32), 0, st, ab[0].best_val, ab[0].best_idx,
               (int)(ACQ_SLOTS * (batch / EPI_THREADS)), best_val, best_idx);
@@ -1431,6 +1426,69 @@ int tb200_acquire_grad(const double* Xp, int P, const double* XsT, const double*
     TB_LAUNCH(acq_grad_kernel, dim3(P), dim3(256), gsm, st, Xp, P, XsT, n, NP, *spec, theta, alpha, mean, ksplit,
               (long)GRAD_PMAX, V, W, Ag, Bg, *acq, val_out, grad_out, mu_out, sigma_out);
     return 0;
+}
+
+int tb200_i8_peak(double ms, double* int8_tops) {
+    TB_CHECK(int8_tops, "NULL pointer argument");
+    int dev = 0, sms = 0;
+    TB_CUDA(cudaGetDevice(&dev));
+    TB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    static DeviceOnce once;
+    if (device_once(once, [] {
+            TB_CUDA(cudaFuncSetAttribute(i8::i8_peak_kernel<i8::PEAK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)i8::PEAK_SMEM));
+            return 0;
+        }))
+        return -1;
+    cudaEvent_t e0, e1;
+    TB_CUDA(cudaEventCreate(&e0));
+    TB_CUDA(cudaEventCreate(&e1));
+    int batches = 64;
+    double best = 0.0;
+    for (int rep = 0; rep < 6; ++rep) {
+        TB_CUDA(cudaEventRecord(e0, 0));
+        TB_LAUNCH(i8::i8_peak_kernel<i8::PEAK_N>, dim3(sms), dim3(64), i8::PEAK_SMEM, 0, batches);
+        TB_CUDA(cudaEventRecord(e1, 0));
+        TB_CUDA(cudaEventSynchronize(e1));
+        float t = 0.f;
+        TB_CUDA(cudaEventElapsedTime(&t, e0, e1));
+        // one MMA = M128 x N256 x K32 multiply-accumulates, 2 operations each
+        const double ops = 2.0 * i8::TM * i8::PEAK_N * 32.0 * i8::PEAK_BATCH * (double)batches * sms;
+        const double tops = ops / (t * 1e-3) / 1e12;
+        if (rep > 0 && tops > best) best = tops;
+        if (t < ms) batches = (int)(batches * (ms / (t > 1e-3 ? t : 1e-3)) * 1.1) + 2;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *int8_tops = best;
+    return 0;
+}
+
+int tb200_shutdown(void) {
+    {
+        std::lock_guard<std::mutex> lock(g_streams_mutex);
+        int cur = 0;
+        cudaGetDevice(&cur);
+        for (int dev = 0; dev < MAX_DEVICES; ++dev) {
+            AcqStreams& a = g_streams[dev];
+            if (!a.ready) continue;
+            cudaSetDevice(dev);
+            cudaStreamSynchronize(a.small);
+            cudaStreamSynchronize(a.var);
+            cudaStreamDestroy(a.small);
+            cudaStreamDestroy(a.var);
+            for (int i = 0; i < ACQ_SLOTS; ++i) { cudaEventDestroy(a.kdone[i]); cudaEventDestroy(a.vdone[i]); }
+            cudaEventDestroy(a.fork); cudaEventDestroy(a.join_small); cudaEventDestroy(a.join_var);
+            a.ready = false;
+        }
+        cudaSetDevice(cur);
+    }
+    for (auto& e : g_events) cudaEventDestroy(e);
+    g_events.clear();
+    g_events_used = 0;
+    for (auto& r : g_trace_recs) cudaEventDestroy(r.e);
+    g_trace_recs.clear();
+    return fit_streams_destroy();
 }
 
 int tb200_trace_enable(int on) {

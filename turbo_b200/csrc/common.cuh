@@ -5,6 +5,9 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <atomic>
+#include <mutex>
+
 #include "../../include/turbo_b200.h"
 
 #if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
@@ -44,6 +47,49 @@ inline int fail(const char* what, const char* file, int line) {
     } while (0)
 
 inline int pad_n(int n) { return (n + TILE - 1) / TILE * TILE; }
+
+// ---------------------------------------------------------------------------------------------
+// once-per-DEVICE configuration.  cudaFuncSetAttribute (dynamic shared-memory opt-in, carve-out) acts on the current
+// device's context: a process that touches a second GPU must repeat it there.  One DeviceOnce per attribute group;
+// mutex-guarded because the caller may be any host thread (the reference's Qt GUI runs the optimiser on a QThread,
+// turbo/gui/qt.py:139-147).
+// ---------------------------------------------------------------------------------------------
+constexpr int MAX_DEVICES = 64;
+struct DeviceOnce {
+    std::mutex m;
+    bool done[MAX_DEVICES] = {};
+};
+template <class F>
+inline int device_once(DeviceOnce& o, F&& configure) {
+    int dev = 0;
+    TB_CUDA(cudaGetDevice(&dev));
+    TB_CHECK(dev >= 0 && dev < MAX_DEVICES, "device ordinal out of range");
+    std::lock_guard<std::mutex> lock(o.m);
+    if (!o.done[dev]) {
+        if (configure()) return -1;
+        o.done[dev] = true;
+    }
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// The ONE debug hook of the library: the environment variable TB200_DEBUG, a comma-separated list of key=value pairs,
+// parsed once on first use (never on the call path afterwards; tb200_debug_reload() re-reads it for tests).
+//   fit_engine=dmma      keep the batched fit on the FP64 DMMA GEMM (the cross-check the tests compare the INT8 fit with)
+//   fit_gmax=7|8|9       slice-pair cut-off of every INT8 fit stage (default 8/8/7: potrf, trtri, K^-1)
+//   fit_gmax_trtri=..    the inverse-factor recurrence alone;   fit_gmax_kinv=..  the K^-1 product alone
+//   acq_gmax=7|8|9       force the slice-pair cut-off of the predictive-variance engine (default: chosen per model from
+//                        an a-priori error bound, tb200_i8_prepare)
+// Everything else that used to be switchable (stream priorities, K* staging, look-ahead, schedule thresholds) was an
+// A/B question of round 1 and is settled; the measurements are under profiles/r1_*.
+// ---------------------------------------------------------------------------------------------
+struct DebugConfig {
+    bool fit_dmma = false;
+    int fit_gmax[3] = {8, 8, 7};
+    int acq_gmax = 0;  // 0 = automatic
+};
+const DebugConfig& debug_config();
+void debug_config_reload();
 
 // ---------------------------------------------------------------------------------------------
 // hyper-parameters: theta (log space, sklearn order) -> physical values

@@ -10,6 +10,9 @@
 //   grad  : 0.5 * sum_ij (alpha alpha^T - K^-1)_ij dK_ij/dtheta with dK recomputed on the fly
 //           (sklearn materialises an (n,n,p) tensor: kernels.py:1753-1771).
 #include <stdlib.h>
+#include <string.h>
+
+#include <string>
 
 #include "gemm_f64.cuh"
 #include "ozaki_gemm.cuh"
@@ -18,6 +21,41 @@ namespace tb200 {
 
 thread_local char g_err[512] = "";
 int64_t g_launches = 0;
+
+// TB200_DEBUG (see common.cuh): parsed once; the call paths only read the struct
+static DebugConfig g_debug;
+static std::once_flag g_debug_once;
+static void parse_debug_config() {
+    DebugConfig c;
+    const char* env = getenv("TB200_DEBUG");
+    std::string text = env ? env : "";
+    size_t pos = 0;
+    while (pos < text.size()) {
+        size_t end = text.find(',', pos);
+        if (end == std::string::npos) end = text.size();
+        const std::string item = text.substr(pos, end - pos);
+        pos = end + 1;
+        const size_t eq = item.find('=');
+        if (eq == std::string::npos) continue;
+        const std::string key = item.substr(0, eq), val = item.substr(eq + 1);
+        const int iv = atoi(val.c_str());
+        const bool g_ok = iv >= 7 && iv <= 9;
+        if (key == "fit_engine") c.fit_dmma = !val.empty() && val[0] == 'd';
+        else if (key == "fit_gmax" && g_ok) c.fit_gmax[0] = c.fit_gmax[1] = c.fit_gmax[2] = iv;
+        else if (key == "fit_gmax_trtri" && g_ok) c.fit_gmax[1] = iv;
+        else if (key == "fit_gmax_kinv" && g_ok) c.fit_gmax[2] = iv;
+        else if (key == "acq_gmax" && g_ok) c.acq_gmax = iv;
+    }
+    g_debug = c;
+}
+const DebugConfig& debug_config() {
+    std::call_once(g_debug_once, parse_debug_config);
+    return g_debug;
+}
+void debug_config_reload() {
+    debug_config();
+    parse_debug_config();
+}
 
 // ---------------------------------------------------------------------------------------------
 // XsT[r][k][j] = X[j][k] / length_scale_k(theta_r)   (j < n; 0 in the padding)
@@ -564,23 +602,6 @@ __global__ void rowscale_from_diag_kernel(const double* __restrict__ K, int NP, 
     scale[(size_t)rs * NP + r] = pow2_cover(sqrt(fabs(dg)));
 }
 
-// columns of the lower-triangular X = L^-1: max_{r >= c} |X[r,c]|  (threads of a warp read adjacent columns)
-__global__ void colscale_kernel(const double* __restrict__ X, int NP, double* __restrict__ scale) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x, rs = blockIdx.y;
-    if (c >= NP) return;
-    const double* x = X + (size_t)rs * NP * NP + c;
-    double m0 = 0.0, m1 = 0.0, m2 = 0.0, m3 = 0.0;
-    int r = c;
-    for (; r + 4 <= NP; r += 4) {
-        m0 = fmax(m0, fabs(x[(size_t)r * NP]));
-        m1 = fmax(m1, fabs(x[(size_t)(r + 1) * NP]));
-        m2 = fmax(m2, fabs(x[(size_t)(r + 2) * NP]));
-        m3 = fmax(m3, fabs(x[(size_t)(r + 3) * NP]));
-    }
-    for (; r < NP; ++r) m0 = fmax(m0, fabs(x[(size_t)r * NP]));
-    scale[(size_t)rs * NP + c] = pow2_cover(fmax(fmax(m0, m1), fmax(m2, m3)));
-}
-
 // column maxima of |M[r, c] * kmul(r)| for columns [col0, col0+128) over rows [row0, NP), kept as the bit pattern of a
 // non-negative double (order-preserving as an integer, so atomicMax works); `out` must be zero beforehand.
 // kscale != NULL: row r is weighted by kscale[r] (the X column scale t_r of the trtri recurrence).
@@ -782,25 +803,10 @@ struct FitBuffers {
 // products, 2^-56: the size of FP64 rounding itself) or 7 (21 products, 2^-48).  Defaults: Cholesky column update 8 (its
 // error is amplified by the rest of the factorisation: 7 costs three digits of the LML on ill-conditioned members),
 // inverse factor 8, K^-1 = Linv^T Linv 7 (feeds only the gradient: 1.7e-10 of max|grad|).  Measured against the FP64
-// DMMA path in profiles/r1_fit_precision.md.  TB200_FIT_GMAX sets all three stages, TB200_FIT_GMAX_TRTRI /
-// TB200_FIT_GMAX_KINV one stage.
+// DMMA path in profiles/r1_fit_precision.md.  TB200_DEBUG=fit_gmax=.. sets all three stages, fit_gmax_trtri /
+// fit_gmax_kinv one stage (common.cuh).
 enum FitStage { FIT_POTRF = 0, FIT_TRTRI = 1, FIT_KINV = 2 };
-static int fit_gmax(int stage) {
-    static int g[3] = {0, 0, 0};
-    if (!g[0]) {
-        const int dflt[3] = {8, 8, 7};
-        const char* names[3] = {nullptr, "TB200_FIT_GMAX_TRTRI", "TB200_FIT_GMAX_KINV"};
-        const char* all = getenv("TB200_FIT_GMAX");
-        for (int s = 2; s >= 0; --s) {
-            int v = dflt[s];
-            if (all && atoi(all) >= 7 && atoi(all) <= 9) v = atoi(all);
-            const char* e = names[s] ? getenv(names[s]) : nullptr;
-            if (e && atoi(e) >= 7 && atoi(e) <= 9) v = atoi(e);
-            g[s] = v;
-        }
-    }
-    return g[stage];
-}
+static int fit_gmax(int stage) { return debug_config().fit_gmax[stage]; }
 static int launch_fit_gemm_i8(const i8::GemmI8Params& g, int ntiles, int R, cudaStream_t st, int stage) {
     switch (fit_gmax(stage)) {
         case 7: return i8::launch_gemm_i8<7>(g, ntiles, R, st);
@@ -811,30 +817,18 @@ static int launch_fit_gemm_i8(const i8::GemmI8Params& g, int ntiles, int R, cuda
 
 static size_t align256(size_t b) { return (b + 255) / 256 * 256; }
 
-static bool fit_dmma_forced() {
-    static int forced = -1;
-    if (forced < 0) {
-        const char* e = getenv("TB200_FIT_ENGINE");
-        forced = (e && e[0] == 'd') ? 1 : 0;
-    }
-    return forced != 0;
-}
+static bool fit_dmma_forced() { return debug_config().fit_dmma; }
 
 static bool use_left_looking(int NB, int R) {
-    static long thr = -1, thr_few = -1;
-    if (thr < 0) {
-        const char* e = getenv("TB200_FIT_LEFT_MIN");  // R * (n/128) at which the batched schedule takes over
-        thr = e ? atol(e) : 128;  // measured at n = 4096: the batched INT8 schedule wins from R = 4 (profiles/r1_fit_schedule_threshold.md)
-        const char* f = getenv("TB200_FIT_LEFT_MIN_FEW");  // the same for one to three matrices (INT8 engine only)
-        thr_few = f ? atol(f) : 96;
-    }
-    // one to three matrices: a block column must offer about one CTA per SM by itself (n >= 12288 for a single
-    // matrix) and the products must be on the INT8 engine; otherwise the right-looking schedule has more tiles per step
-    return R >= 4 ? (long)R * NB >= thr : (!fit_dmma_forced() && (long)R * NB >= thr_few);
+    // R * (n/128) at which the batched schedule takes over: measured at n = 4096, the batched INT8 schedule wins from
+    // R = 4 (profiles/r1_fit_schedule_threshold.md).  One to three matrices: a block column must offer about one CTA
+    // per SM by itself (n >= 12288 for a single matrix) and the products must be on the INT8 engine; otherwise the
+    // right-looking schedule has more tiles per step
+    return R >= 4 ? (long)R * NB >= 128 : (!fit_dmma_forced() && (long)R * NB >= 96);
 }
 
 // The batched (left-looking) schedule runs its long-K products on the INT8 tensor cores (k-ranges above 8192 in
-// several exact INT32 windows, ozaki_gemm.cuh).  TB200_FIT_ENGINE=dmma keeps everything on the FP64 DMMA GEMM.
+// several exact INT32 windows, ozaki_gemm.cuh).  TB200_DEBUG=fit_engine=dmma keeps everything on the FP64 DMMA GEMM.
 static bool fit_uses_i8(int NP, int R) {
     return !fit_dmma_forced() && NP <= TB200_I8_MAX_N && use_left_looking(NP / TILE, R);
 }
@@ -890,12 +884,13 @@ size_t fit_workspace_layout(int n, int d, int R, int p, bool own_linv, bool own_
 static int launch_diag(const FitBuffers& fb, int NP, int R, int k, int* info, cudaStream_t st) {
     const int NB = NP / TILE;
     const long sK = (long)NP * NP, sD = (long)NB * TILE * TILE;
-    static bool configured = false;
-    if (!configured) {
-        TB_CUDA(cudaFuncSetAttribute(diag_potrf_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)DIAG_SMEM));
-        configured = true;
-    }
+    static DeviceOnce once;
+    if (device_once(once, [] {
+            TB_CUDA(cudaFuncSetAttribute(diag_potrf_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)DIAG_SMEM));
+            return 0;
+        }))
+        return -1;
     TB_LAUNCH(diag_potrf_inv_kernel, dim3(R), dim3(DIAG_THREADS), DIAG_SMEM, st, fb.K, (long)NP, sK, k, fb.Dinv, sD, info);
     return 0;
 }
@@ -917,11 +912,13 @@ struct FitStreams {
     cudaStream_t side, look;
     cudaEvent_t fork, join, fork_look, look_done;
 };
-static FitStreams g_fit_streams[64];
+static FitStreams g_fit_streams[MAX_DEVICES];
+static std::mutex g_fit_streams_mutex;
 static int fit_streams_for_device(FitStreams** out) {
     int dev = 0;
     TB_CUDA(cudaGetDevice(&dev));
-    TB_CHECK(dev >= 0 && dev < 64, "device ordinal out of range");
+    TB_CHECK(dev >= 0 && dev < MAX_DEVICES, "device ordinal out of range");
+    std::lock_guard<std::mutex> lock(g_fit_streams_mutex);
     FitStreams& f = g_fit_streams[dev];
     if (!f.ready) {
         int lo = 0, hi = 0;
@@ -952,16 +949,6 @@ static int launch_diag_update(const FitBuffers& fb, int NP, int R, int k, int j0
     return launch_gemm<false, true>(p, R, count, st);
 }
 
-// TB200_FIT_DIAG_RL=0 keeps the diagonal tile's whole update in step k itself (A/B switch)
-static bool fit_diag_right_looking() {
-    static int on = -1;
-    if (on < 0) {
-        const char* e = getenv("TB200_FIT_DIAG_RL");
-        on = (e && e[0] == '0') ? 0 : 1;
-    }
-    return on != 0;
-}
-
 // blocked Cholesky of R matrices in fb.K (lower), Dinv blocks kept for trtri
 static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStream_t st) {
     const int NB = NP / TILE;
@@ -971,7 +958,7 @@ static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStr
     if (i8fit)
         TB_LAUNCH(rowscale_from_diag_kernel, dim3((NP + 255) / 256, R), dim3(256), 0, st, fb.K, NP, fb.scale);
     FitStreams* rl = nullptr;  // side stream of the right-looking diagonal-tile schedule (batched INT8 fit only)
-    if (i8fit && NB > 1 && fit_diag_right_looking() && fit_streams_for_device(&rl)) rl = nullptr;
+    if (i8fit && NB > 1 && fit_streams_for_device(&rl)) rl = nullptr;
     for (int k = 0; k < NB; ++k) {
         bool diag_done = false;
         if (rl && k > 0) {
@@ -1102,8 +1089,7 @@ static int trtri_batched_i8(const FitBuffers& fb, double* Linv, int NP, int R, c
     // the byte slices of the finished X block column and the weighted L panel of this step only share their inputs:
     // the former runs on the look-ahead stream next to the latter's column maxima, scales and slices
     FitStreams* ov = nullptr;
-    static const bool overlap = !(getenv("TB200_FIT_TRTRI_OVERLAP") && getenv("TB200_FIT_TRTRI_OVERLAP")[0] == '0');
-    if (!overlap || fit_streams_for_device(&ov)) ov = nullptr;
+    if (fit_streams_for_device(&ov)) ov = nullptr;
     for (int c = NB - 2; c >= 0; --c) {
         const int c1 = c + 1, rem = NB - c1;
         // column scales of the finished block column c1 of X, then its byte slices (rows >= c1*128, k-blocks 2c1, 2c1+1)
@@ -1167,7 +1153,7 @@ static int trtri_batched_i8(const FitBuffers& fb, double* Linv, int NP, int R, c
 static int trtri_batched(const FitBuffers& fb, double* Linv, int NP, int R, cudaStream_t st) {
     const int NB = NP / TILE;
     const long sK = (long)NP * NP, sD = (long)NB * TILE * TILE;
-    if (fit_uses_i8(NP, R) && fb.sliced != nullptr && !getenv("TB200_TRTRI_DMMA")) return trtri_batched_i8(fb, Linv, NP, R, st);
+    if (fit_uses_i8(NP, R) && fb.sliced != nullptr) return trtri_batched_i8(fb, Linv, NP, R, st);
     if (use_left_looking(NB, R)) {
         // row block i:  X[i,c] = -Dinv_i * sum_{k=c}^{i-1} L[i,k] X[k,c]  (c < i),  X[i,i] = Dinv_i
         TB_CUDA(cudaMemsetAsync(Linv, 0, sizeof(double) * (size_t)R * NP * NP, st));
@@ -1225,16 +1211,17 @@ static int fit_pipeline(const double* X, const double* y_n, int n, const tb200_k
     const size_t gsm = sizeof(double) * 2 * d * GT;
     {
         // d up to TB200_MAX_D = 64 needs 64 KB (gram) / 70 KB (gradient) of dynamic shared memory: opt in once
-        static bool configured = false;
-        if (!configured) {
-            const int mx = (int)(sizeof(double) * (2 * TB200_MAX_D * GT + 8 * (TB200_MAX_D + 2)));
-            TB_CUDA(cudaFuncSetAttribute(gram_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
-            TB_CUDA(cudaFuncSetAttribute(lml_grad_kernel<TB200_RBF>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
-            TB_CUDA(cudaFuncSetAttribute(lml_grad_kernel<TB200_MATERN12>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
-            TB_CUDA(cudaFuncSetAttribute(lml_grad_kernel<TB200_MATERN32>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
-            TB_CUDA(cudaFuncSetAttribute(lml_grad_kernel<TB200_MATERN52>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
-            configured = true;
-        }
+        static DeviceOnce once;
+        if (device_once(once, [] {
+                const int mx = (int)(sizeof(double) * (2 * TB200_MAX_D * GT + 8 * (TB200_MAX_D + 2)));
+                TB_CUDA(cudaFuncSetAttribute(gram_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+                TB_CUDA(cudaFuncSetAttribute(lml_grad_kernel<TB200_RBF>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+                TB_CUDA(cudaFuncSetAttribute(lml_grad_kernel<TB200_MATERN12>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+                TB_CUDA(cudaFuncSetAttribute(lml_grad_kernel<TB200_MATERN32>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+                TB_CUDA(cudaFuncSetAttribute(lml_grad_kernel<TB200_MATERN52>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+                return 0;
+            }))
+            return -1;
     }
     TB_LAUNCH(gram_train_kernel, dim3(nt64, R), dim3(256), gsm, st, XsT, n, NP, spec, theta, p, jitter, fb.K);
     if (potrf_batched(fb, NP, R, info, st)) return -1;
@@ -1249,9 +1236,7 @@ static int fit_pipeline(const double* X, const double* y_n, int n, const tb200_k
             // INT8 tensor cores: operand rows = columns of Linv (K index = row), per-column power-of-two scales
             const long sK = (long)NP * NP;
             const int NB = NP / TILE;
-            // column scales of Linv: left in fb.scale by the INT8 trtri recurrence; measured here otherwise
-            if (getenv("TB200_TRTRI_DMMA"))
-                TB_LAUNCH(colscale_kernel, dim3((NP + 127) / 128, R), dim3(128), 0, st, Linv, NP, fb.scale);
+            // column scales of Linv: left in fb.scale by the INT8 trtri recurrence
             const long pieces = (long)(NP / 8) * (NP / i8::KB);
             TB_LAUNCH(slice_operand_kernel<true>, dim3((unsigned)((pieces + 7) / 8), R), dim3(256), 0, st, Linv, NP, sK,
                       fb.scale, (const double*)nullptr, 0, 0, NP / 8, 0, NP / i8::KB, 1, 0, fb.sliced, sK,
@@ -1286,13 +1271,39 @@ static int fit_pipeline(const double* X, const double* y_n, int n, const tb200_k
     return 0;
 }
 
+// tb200_shutdown: the fit path's side / look-ahead streams and events of every device
+int fit_streams_destroy() {
+    std::lock_guard<std::mutex> lock(g_fit_streams_mutex);
+    int cur = 0;
+    cudaGetDevice(&cur);
+    for (int dev = 0; dev < MAX_DEVICES; ++dev) {
+        FitStreams& f = g_fit_streams[dev];
+        if (!f.ready) continue;
+        cudaSetDevice(dev);
+        cudaStreamSynchronize(f.side);
+        cudaStreamSynchronize(f.look);
+        cudaStreamDestroy(f.side);
+        cudaStreamDestroy(f.look);
+        cudaEventDestroy(f.fork); cudaEventDestroy(f.join); cudaEventDestroy(f.fork_look); cudaEventDestroy(f.look_done);
+        f.ready = false;
+    }
+    cudaSetDevice(cur);
+    return 0;
+}
+
 }  // namespace tb200
 
 using namespace tb200;
 
 extern "C" {
 
-int tb200_version(void) { return 100; }
+int tb200_version(void) { return 200; }
+
+int tb200_debug_reload(void) {
+    debug_config_reload();
+    return 0;
+}
+
 const char* tb200_last_error(void) { return g_err; }
 int tb200_padded_n(int n) { return pad_n(n); }
 int64_t tb200_launch_count(void) { return g_launches; }

@@ -255,14 +255,15 @@ __global__ void __launch_bounds__(G_THREADS, 1) gemm_f64_kernel(const GemmParams
 
 template <bool TA, bool TB>
 inline int launch_gemm(const GemmParams& p, int batch1, int batch2, cudaStream_t stream) {
-    static bool configured = false;
-    if (!configured) {
-        TB_CUDA(cudaFuncSetAttribute(gemm_f64_kernel<TA, TB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)G_SMEM_BYTES));
-        TB_CUDA(cudaFuncSetAttribute(gemm_f64_kernel<TA, TB>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                     (int)cudaSharedmemCarveoutMaxShared));
-        configured = true;
-    }
+    static DeviceOnce once;
+    if (device_once(once, [] {
+            TB_CUDA(cudaFuncSetAttribute(gemm_f64_kernel<TA, TB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)G_SMEM_BYTES));
+            TB_CUDA(cudaFuncSetAttribute(gemm_f64_kernel<TA, TB>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                         (int)cudaSharedmemCarveoutMaxShared));
+            return 0;
+        }))
+        return -1;
     const long tiles = (p.order == ORDER_LOWER) ? (long)p.tilesM * (p.tilesM + 1) / 2 : (long)p.tilesM * p.tilesN;
     if (tiles <= 0 || batch1 <= 0 || batch2 <= 0) return 0;
     dim3 grid((unsigned)tiles, (unsigned)batch1, (unsigned)batch2);

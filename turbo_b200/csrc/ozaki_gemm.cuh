@@ -185,11 +185,13 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_i8_kernel(const GemmI8Params 
 
 template <int GMAX>
 inline int launch_gemm_i8(const GemmI8Params& p, int ntiles, int R, cudaStream_t stream) {
-    static bool configured = false;
-    if (!configured) {
-        TB_CUDA(cudaFuncSetAttribute(gemm_i8_kernel<GMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
-        configured = true;
-    }
+    static DeviceOnce once;
+    if (device_once(once, [] {
+            TB_CUDA(cudaFuncSetAttribute(gemm_i8_kernel<GMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)SMEM_BYTES));
+            return 0;
+        }))
+        return -1;
     if (ntiles <= 0 || R <= 0) return 0;
     // the longest k-range any CTA of this launch can have
     const int span = p.tri ? p.kblks : (p.kbHiByRow ? p.kblks : p.kbHi) - p.kbLo;

@@ -84,12 +84,24 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
-// bounded wait: a protocol bug traps instead of hanging the GPU
+// Production builds wait without a bound (try_wait suspends the thread in hardware between polls).  A development
+// build compiled with -DTB200_MBAR_TRAP_SECONDS=<s> traps after that many seconds of WALL-CLOCK time (%globaltimer), so
+// a protocol bug in a new kernel ends the launch instead of hanging the box; a bound counted in polls (round 1) could
+// fire under ncu replay or time-slicing and kill the context of a long optimisation run.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    uint32_t spins = 0;
+#ifdef TB200_MBAR_TRAP_SECONDS
+    if (mbar_try_wait(bar, parity)) return;
+    uint64_t t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
     while (!mbar_try_wait(bar, parity)) {
-        if (++spins > (1u << 24)) __trap();
+        uint64_t t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        if (t1 - t0 > (uint64_t)(TB200_MBAR_TRAP_SECONDS) * 1000000000ull) __trap();
     }
+#else
+    while (!mbar_try_wait(bar, parity)) {
+    }
+#endif
 }
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
@@ -192,9 +204,13 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
+// digit planes a kernel with cut-off GMAX reads: plane s pairs with planes 1..GMAX-s, so plane 7 is unused at GMAX = 7
+__host__ __device__ constexpr int planes_used(int gmax) { return gmax - 1 < S ? gmax - 1 : S; }
+
 template <int GMAX, bool MULTI>
 __global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p) {
     constexpr int NG = GMAX - 1;  // groups g = 2..GMAX, one 64-column INT32 accumulator each
+    constexpr int SU = planes_used(GMAX);
     static_assert(NG * TN <= TMEM_COLS, "accumulators exceed TMEM");
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -236,9 +252,9 @@ __global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p)
             if (kb >= STAGES) mbar_wait(&empty_bar[s], ((kb / STAGES) - 1) & 1);
             if (elect_one()) {
                 uint8_t* st = smem + (size_t)s * STAGE_BYTES;
-                mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                mbar_expect_tx(&full_bar[s], SU * (A_TILE + B_TILE));
 #pragma unroll
-                for (int sl = 0; sl < S; ++sl) {
+                for (int sl = 0; sl < SU; ++sl) {
                     bulk_g2s(st + sl * A_TILE, a_src + (size_t)sl * p.candSliceStride + (size_t)kb * A_TILE, A_TILE,
                              &full_bar[s]);
                     bulk_g2s(st + S * A_TILE + sl * B_TILE, b_src + (size_t)sl * p.linvSliceStride + (size_t)kb * B_TILE,
@@ -340,16 +356,17 @@ __global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p)
 
 template <int GMAX, bool MULTI>
 inline int launch_colsumsq_i8_impl(const Params& p, cudaStream_t stream) {
-    static bool configured = false;
-    if (!configured) {
-        TB_CUDA(cudaFuncSetAttribute(colsumsq_i8_kernel<GMAX, MULTI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)SMEM_BYTES));
-        // same (maximum) carve-out as the small kernels that share the SMs with it: CTAs launched under different
-        // shared-memory configurations cannot be resident on one SM at the same time
-        TB_CUDA(cudaFuncSetAttribute(colsumsq_i8_kernel<GMAX, MULTI>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                     (int)cudaSharedmemCarveoutMaxShared));
-        configured = true;
-    }
+    static DeviceOnce once;
+    if (device_once(once, [] {
+            TB_CUDA(cudaFuncSetAttribute(colsumsq_i8_kernel<GMAX, MULTI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)SMEM_BYTES));
+            // same (maximum) carve-out as the small kernels that share the SMs with it: CTAs launched under different
+            // shared-memory configurations cannot be resident on one SM at the same time
+            TB_CUDA(cudaFuncSetAttribute(colsumsq_i8_kernel<GMAX, MULTI>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                         (int)cudaSharedmemCarveoutMaxShared));
+            return 0;
+        }))
+        return -1;
     TB_LAUNCH((colsumsq_i8_kernel<GMAX, MULTI>), dim3((unsigned)(p.rowTiles * p.candTiles)), dim3(THREADS), SMEM_BYTES,
               stream, p);
     return 0;
@@ -360,6 +377,65 @@ inline int launch_colsumsq_i8(const Params& p, cudaStream_t stream) {
     // the heaviest tile spans rowTiles k-blocks
     return p.rowTiles <= PASS_KB ? launch_colsumsq_i8_impl<GMAX, false>(p, stream)
                                  : launch_colsumsq_i8_impl<GMAX, true>(p, stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// INT8 tensor peak of this device: the roofline denominator of the two kernels above, MEASURED instead of inferred from
+// the bf16 figure.  One CTA per SM; one elected lane issues tcgen05.mma kind::i8 M128 x N256 x K32 instructions on
+// operands that stay resident in shared memory (zero digits: the tensor pipe's rate does not depend on the values),
+// alternating between the two 256-column halves of TMEM.  Two mbarriers alternate so a batch is always queued behind the
+// one in flight and the pipe never drains.  No global traffic, no epilogue: nothing but the MMA rate is measured.
+// ---------------------------------------------------------------------------------------------
+constexpr int PEAK_N = 256, PEAK_BATCH = 16;
+constexpr size_t PEAK_SMEM = (size_t)(TM + PEAK_N) * KB + 1024;  // A: 128 x 64 B, B: 256 x 64 B (canonical K-major)
+
+template <int N_COLS>
+__global__ void __launch_bounds__(64, 1) i8_peak_kernel(int batches) {
+    static_assert(N_COLS == PEAK_N, "one instantiation (a template only so that both translation units may include it)");
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    __shared__ uint64_t bar[2];
+    __shared__ uint32_t tmem_base_s;
+    const int warp = threadIdx.x >> 5;
+    for (int e = threadIdx.x; e < (int)((TM + PEAK_N) * KB / 16); e += blockDim.x)
+        reinterpret_cast<uint4*>(smem)[e] = make_uint4(0u, 0u, 0u, 0u);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> tensor-core (async-proxy) reads
+    if (threadIdx.x == 0) {
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)),
+                     "r"(TMEM_COLS)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = tmem_base_s;
+    if (warp == 0) {
+        const uint64_t ad = make_desc(smem_u32(smem));
+        const uint64_t bd = make_desc(smem_u32(smem + TM * KB));
+        for (int b = 0; b < batches; ++b) {
+            if (b >= 2) mbar_wait(&bar[b & 1], ((b >> 1) - 1) & 1);  // the batch issued two rounds ago has retired
+            if (elect_one()) {
+#pragma unroll
+                for (int i = 0; i < PEAK_BATCH; ++i)
+                    umma_i8(tmem_base + (uint32_t)((i & 1) * PEAK_N), ad + (uint64_t)((i & 1) * ((2 * LBO) >> 4)),
+                            bd + (uint64_t)((i & 1) * ((2 * LBO) >> 4)), idesc(PEAK_N), (b > 0 || i > 1) ? 1u : 0u);
+                umma_commit(&bar[b & 1]);
+            }
+            __syncwarp();
+        }
+        for (int b = (batches > 2 ? batches - 2 : 0); b < batches; ++b) mbar_wait(&bar[b & 1], (b >> 1) & 1);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+    }
 }
 
 }  // namespace i8

@@ -153,24 +153,28 @@ class Factor:
         return sum(t.numel() * t.element_size() for t in ts)
 
 
+I8_GMAX = {"i8l": 7, "i8": 8, "i8x": 9}  # slice-pair cut-off of the INT8 variance engine: 21 / 28 / 34 products
+
+
 def resolve_engine(engine, NP):
-    """'auto' -> the INT8 tensor-core engine for n <= I8_MAX_N (INT32 accumulation is exact per pass of 8192 training points; longer rows take several passes)"""
-    engine = (engine or os.environ.get("TB200_ENGINE") or "auto").lower()
+    """'auto' -> the INT8 tensor-core engine for n <= I8_MAX_N (INT32 accumulation is exact per pass of 8192 training
+    points; longer rows take several passes).  'dmma' is the FP64 DMMA GEMM (small-n path and cross-check)."""
+    engine = (engine or "auto").lower()
     if engine == "auto":
         engine = "i8" if NP <= _lib.I8_MAX_N else "dmma"
-    if engine in ("i8", "i8x"):
+    if engine in I8_GMAX:
         if NP > _lib.I8_MAX_N:
             raise ValueError("the i8 variance engine needs n <= %d; use engine='dmma'" % _lib.I8_MAX_N)
         return engine
     if engine != "dmma":
-        raise ValueError("unknown variance engine %r (auto | dmma | i8 | i8x)" % engine)
+        raise ValueError("unknown variance engine %r (auto | dmma | i8l | i8 | i8x)" % engine)
     return engine
 
 
 class Acquirer:
     """runs tb200_acquire / tb200_acquire_i8 over device candidates or a generated set, keeping the running
     best on device.  engine: 'dmma' (FP64 tensor-core GEMM), 'i8' (INT8 tensor cores, 28 slice products),
-    'i8x' (34 slice products), 'auto' (i8 when n <= I8_MAX_N = 32768)."""
+    'i8x' (34 slice products), 'i8l' (21 slice products), 'auto' (i8 when n <= I8_MAX_N = 32768)."""
 
     def __init__(self, factor, acq_c, batch=0, engine=None, exclusion=None):
         """exclusion: None or (X_dev (n,d) device tensor of UNSCALED points, tol): candidates whose squared distance to
@@ -206,7 +210,7 @@ class Acquirer:
         if self.engine != "dmma":
             _lib.check(self.lib.tb200_acquire_i8_excl(
                 ex, _lib.ptr(Xc_dev), int(m), int(index_base), C.byref(cand_c) if cand_c is not None else None,
-                _lib.ptr(f.XsT), _lib.ptr(f.linvS), _lib.ptr(f.rowscale), 8 if self.engine == "i8" else 9,
+                _lib.ptr(f.XsT), _lib.ptr(f.linvS), _lib.ptr(f.rowscale), I8_GMAX[self.engine],
                 _lib.ptr(f.alpha), f.n, C.byref(self.spec_c), _lib.ptr(f.theta), C.byref(self.acq_c), _lib.ptr(mu),
                 _lib.ptr(sigma), _lib.ptr(acq), _lib.ptr(self.best_val), _lib.ptr(self.best_idx), self.batch,
                 _lib.ptr(self.work), self.nbytes, _lib.stream_ptr()))
@@ -297,6 +301,19 @@ def fp64_peak(ms=50.0):
     a, b = C.c_double(), C.c_double()
     _lib.check(_lib.load().tb200_fp64_peak(float(ms), C.byref(a), C.byref(b)))
     return a.value, b.value
+
+
+def i8_peak(ms=30.0):
+    """measured INT8 tensor-core peak (TOP/s) of the current device (tb200_i8_peak)"""
+    _require_cuda()
+    a = C.c_double()
+    _lib.check(_lib.load().tb200_i8_peak(float(ms), C.byref(a)))
+    return a.value
+
+
+def shutdown():
+    """release the library's per-device streams and events (tb200_shutdown); they are re-created on demand"""
+    _lib.check(_lib.load().tb200_shutdown())
 
 
 def dgemm(ta, tb, alpha, A, B, beta, Cm):

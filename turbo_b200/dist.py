@@ -121,3 +121,21 @@ def select_best_restart(thetas, neg_lmls, p, group):
         raise np.linalg.LinAlgError("no restart produced a positive-definite kernel matrix")
     b = int(np.argmin(table[:, 0]))
     return table[b, 1:].copy(), float(table[b, 0])
+
+
+def broadcast_array(a, group=None, src=0):
+    """the float64 array of rank ``src`` on every rank (shape included); identity when group is None"""
+    if group is None:
+        return a
+    import torch
+    td = _dist()
+    g = None if group == 'world' else group
+    dev = _comm_device(group)
+    src_global = td.get_global_rank(g, src) if g is not None else src
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    shape = torch.tensor(list(a.shape) + [-1] * (8 - a.ndim), dtype=torch.int64, device=dev)
+    td.broadcast(shape, src=src_global, group=g)
+    dims = [int(v) for v in shape.cpu().tolist() if v >= 0]
+    buf = torch.from_numpy(a).to(dev) if td.get_rank(g) == src else torch.empty(dims, dtype=torch.float64, device=dev)
+    td.broadcast(buf, src=src_global, group=g)
+    return buf.cpu().numpy()

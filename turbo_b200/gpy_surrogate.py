@@ -152,7 +152,7 @@ class GpuGPySurrogate(GpuGPSurrogate):
                                                   device_inputs=(X_dev, yn_dev), variance_engine=self.variance_engine,
                                                   factor=factor)
             model.kernel_prefix = prefix
-            self._live = (model, spec, theta.copy(), jitter)
+            self._remember(model, spec, theta, jitter)
         if len(ws) > 0:
             fitting_info['warnings'] = [w.message for w in ws]
         if iterations > 0:

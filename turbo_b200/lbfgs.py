@@ -31,6 +31,10 @@ def _single_threaded_blas():
         return contextlib.nullcontext()
 
 
+class _Aborted(Exception):
+    """raised inside a worker's objective when the coordinator of the threads driver has failed"""
+
+
 class _Instance:
     """one SciPy L-BFGS-B state driven through its reverse-communication routine `setulb`, exactly as
     scipy.optimize._lbfgsb_py._minimize_lbfgsb does (same workspace sizes, same task codes)"""
@@ -69,16 +73,37 @@ class _Instance:
                 return False
 
 
-def _minimize_reverse_communication(fun, x0, lo, hi, f0, g0, live, max_iter, history, pgtol, ftol, max_ls):
+_RC_AVAILABLE = None
+
+
+def _setulb_and_int_dtype():
     from scipy.optimize import _lbfgsb
     try:
         from scipy.optimize._lbfgsb_py import HAS_ILP64
     except ImportError:
         HAS_ILP64 = False
-    int_dtype = np.int64 if HAS_ILP64 else np.int32
+    return _lbfgsb.setulb, (np.int64 if HAS_ILP64 else np.int32)
+
+
+def _reverse_communication_available():
+    """True when SciPy's private `setulb` exists and accepts the argument list `_Instance` passes (probed once on a
+    one-dimensional quadratic: the routine must come back asking for f and g)."""
+    global _RC_AVAILABLE
+    if _RC_AVAILABLE is None:
+        try:
+            setulb, int_dtype = _setulb_and_int_dtype()
+            probe = _Instance(setulb, np.array([0.5]), np.array([0.0]), np.array([1.0]), 3, 1e7, 1e-5, 20, 5, int_dtype)
+            _RC_AVAILABLE = bool(probe.advance())
+        except (ImportError, AttributeError, TypeError, ValueError):
+            _RC_AVAILABLE = False
+    return _RC_AVAILABLE
+
+
+def _minimize_reverse_communication(fun, x0, lo, hi, f0, g0, live, max_iter, history, pgtol, ftol, max_ls):
+    setulb, int_dtype = _setulb_and_int_dtype()
     R, p = x0.shape
     factr = ftol / np.finfo(float).eps
-    inst = {r: _Instance(_lbfgsb.setulb, x0[r], lo, hi, int(history), factr, pgtol, int(max_ls), int(max_iter), int_dtype)
+    inst = {r: _Instance(setulb, x0[r], lo, hi, int(history), factr, pgtol, int(max_ls), int(max_iter), int_dtype)
             for r in live}
     x_out, f_out, n_iter = x0.copy(), f0.copy(), np.zeros(R, dtype=int)
     n_eval = 1
@@ -139,19 +164,21 @@ def minimize_batched(fun, x0, bounds, max_iter=200, history=10, pgtol=1e-5, ftol
     import os
     driver = os.environ.get("TB200_LBFGS_DRIVER", driver)  # diagnostics: threads | rc | rc-nolimit
     if driver in ("auto", "rc", "rc-nolimit"):
-        try:
+        # the guard covers the PROBE of SciPy's private routine only: an error raised by `fun` (the device call) or by
+        # the optimisation itself propagates instead of silently re-running the fit on the threads driver
+        if _reverse_communication_available():
             import contextlib
             with (contextlib.nullcontext() if driver == "rc-nolimit" else _single_threaded_blas()):
                 return _minimize_reverse_communication(fun, x0, lo, hi, f0, g0, live, max_iter, history, pgtol, ftol,
                                                        max_ls)
-        except (ImportError, AttributeError, TypeError, ValueError):
-            if driver == "rc":
-                raise
+        if driver == "rc":
+            raise RuntimeError("scipy.optimize._lbfgsb.setulb is missing or has an unexpected signature")
 
     cond = threading.Condition()  # only the coordinator waits on it; each worker sleeps on its own event
     requests, answers, finished = {}, {}, set()
     wake = {r: threading.Event() for r in live}
     errors = []
+    aborted = []
 
     def worker(r):
         first = [True]
@@ -166,6 +193,8 @@ def minimize_batched(fun, x0, bounds, max_iter=200, history=10, pgtol=1e-5, ftol
                 cond.notify()
             wake[r].wait()
             wake[r].clear()
+            if aborted:  # the coordinator failed (an error from `fun`): leave the optimisation, free the thread
+                raise _Aborted()
             return answers.pop(r)
 
         try:
@@ -176,6 +205,8 @@ def minimize_batched(fun, x0, bounds, max_iter=200, history=10, pgtol=1e-5, ftol
             if np.isfinite(res.fun) and res.fun <= f0[r]:
                 x_out[r], f_out[r] = np.clip(res.x, lo, hi), float(res.fun)
             n_iter[r] = int(res.nit)
+        except _Aborted:
+            pass
         except Exception as e:  # never leave the coordinator waiting
             errors.append(e)
         finally:
@@ -186,24 +217,34 @@ def minimize_batched(fun, x0, bounds, max_iter=200, history=10, pgtol=1e-5, ftol
     threads = [threading.Thread(target=worker, args=(r,), daemon=True) for r in live]
     for t in threads:
         t.start()
-    while True:
-        with cond:
-            while len(requests) + len(finished) < len(live):
-                cond.wait()
-            if not requests:
-                break
-            members = np.array(sorted(requests), dtype=int)
-            X = np.stack([requests[r] for r in members])
-            requests.clear()
-        f, g = fun(X, members)  # the one device call of this round, from the calling thread
-        n_eval += 1
-        f, g = np.asarray(f, dtype=np.float64), np.asarray(g, dtype=np.float64)
-        for k, r in enumerate(members):
-            if np.isfinite(f[k]) and np.all(np.isfinite(g[k])):
-                answers[int(r)] = (float(f[k]), g[k].copy())
-            else:
-                answers[int(r)] = (1e8 * max(1.0, abs(f0[r])), np.zeros(p))
-            wake[int(r)].set()
+    try:
+        while True:
+            with cond:
+                while len(requests) + len(finished) < len(live):
+                    cond.wait()
+                if not requests:
+                    break
+                members = np.array(sorted(requests), dtype=int)
+                X = np.stack([requests[r] for r in members])
+                requests.clear()
+            f, g = fun(X, members)  # the one device call of this round, from the calling thread
+            n_eval += 1
+            f, g = np.asarray(f, dtype=np.float64), np.asarray(g, dtype=np.float64)
+            for k, r in enumerate(members):
+                if np.isfinite(f[k]) and np.all(np.isfinite(g[k])):
+                    answers[int(r)] = (float(f[k]), g[k].copy())
+                else:
+                    answers[int(r)] = (1e8 * max(1.0, abs(f0[r])), np.zeros(p))
+                wake[int(r)].set()
+    except BaseException:
+        # an error from `fun`: every worker blocked in its objective is released with the abort flag set, so no thread
+        # is left waiting on its event forever
+        aborted.append(True)
+        for ev in wake.values():
+            ev.set()
+        for t in threads:
+            t.join()
+        raise
     for t in threads:
         t.join()
     if errors:

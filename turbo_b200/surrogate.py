@@ -86,8 +86,10 @@ class _DeviceModelInstance:
         return self._factor if self._factor is not None else self._build()
 
     def release(self):
-        """free the O(n^2) device buffers (rebuilt on demand); the Recorder keeps every trial's
-        model alive (optimiser.py:343), so the aux-optimiser calls this after choosing a point"""
+        """drop this model's reference to the O(n^2) device buffers (rebuilt on demand); the Recorder keeps every
+        trial's model alive (optimiser.py:343), so the aux-optimiser calls this after choosing a point.  The surrogate
+        that built the model keeps the LATEST factor alive on its own (`GpuGPSurrogate._live_factor`) so that the next
+        trial can extend it in O(n^2): at most one factor stays resident per surrogate."""
         self._factor = None
 
     def __getstate__(self):
@@ -165,6 +167,7 @@ class GpuGPSurrogate(Surrogate):
         # trials that only append rows at unchanged hyper-parameters extend the previous factor in O(n^2) (8f-2)
         self.incremental = bool(incremental)
         self._live = None
+        self._live_factor = None
         rs = self.model_params.get('random_state', seed)
         self._rng = rs if isinstance(rs, np.random.RandomState) else np.random.RandomState(rs)
         self._last_model_params = None
@@ -221,12 +224,26 @@ class GpuGPSurrogate(Surrogate):
             model = GpuGPSurrogate.ModelInstance(spec, theta, X, y_n, y_mean, y_std, jitter,
                                                  device_inputs=(X_dev, yn_dev), variance_engine=self.variance_engine,
                                                  factor=factor)
-            self._live = (model, spec, theta.copy(), float(jitter))
+            self._remember(model, spec, theta, jitter)
         if len(ws) > 0:
             fitting_info['warnings'] = [w.message for w in ws]
         if iterations > 0:
             self._last_model_params = np.exp(theta.copy())
         return model, fitting_info
+
+    def _remember(self, model, spec, theta, jitter):
+        """the latest model and ITS factor: the model may drop its own reference (`release`, the aux-optimiser's default)
+        while the surrogate keeps the factor for the next trial's incremental update"""
+        self._live = (model, spec, np.asarray(theta, dtype=np.float64).copy(), float(jitter))
+        self._live_factor = model._factor
+
+    def __getstate__(self):
+        """the Recorder pickles the optimiser with its modules (recorder.py:117-146): no device state, no process group"""
+        s = dict(self.__dict__)
+        s['_live'] = s['_live_factor'] = None
+        if not (s.get('group') is None or isinstance(s.get('group'), str)):
+            s['group'] = None
+        return s
 
     def _try_incremental(self, spec, theta, X, yn_dev, jitter):
         """when a trial only ADDS rows to the previous trial's X and theta, kernel and jitter are unchanged
@@ -237,12 +254,12 @@ class GpuGPSurrogate(Surrogate):
         if live is None:
             return None
         old, ospec, otheta, ojit = live
-        f = old._factor
+        f = old._factor if old._factor is not None else getattr(self, '_live_factor', None)
         n_old = old.X.shape[0]
         if (f is None or ospec != spec or ojit != float(jitter) or not np.allclose(otheta, theta, rtol=0.0, atol=1e-13)
                 or X.shape[0] <= n_old or X.shape[1] != old.X.shape[1] or not np.array_equal(X[:n_old], old.X)):
             return None
-        if not f.append(X[n_old:], yn_dev, X.shape[0], jitter):
+        if f.n != n_old or not f.append(X[n_old:], yn_dev, X.shape[0], jitter):
             return None
         old._factor = None
         return f
