@@ -4,4 +4,5 @@ set -e
 cd "$(dirname "$0")"
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC"
-$NVCC $FLAGS "$@" -shared -o ../libturbo_b200.so fit.cu acquire.cu
+OUT=${TB200_OUT:-../libturbo_b200.so}   # TB200_OUT: A/B builds next to the shipped library (loaded with TB200_LIB)
+$NVCC $FLAGS "$@" -shared -o "$OUT" fit.cu acquire.cu
