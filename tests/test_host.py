@@ -173,6 +173,9 @@ def _gloo_worker(rank, world, port, q):
         tv, ti = [([3.0, 1.0, 2.0], [40, 7, 9]), ([3.0, 2.5], [12, 900])][rank]
         out["top"] = dist.allgather_top(np.array(tv), np.array(ti), 3, "world")
         out["top_short"] = dist.allgather_top(np.array(tv[:rank]), np.array(ti[:rank]), 4, "world")
+        # host-drawn candidate sets: every rank draws its own, rank 0's is the set everybody shards
+        mine = np.random.default_rng(100 + rank).random((7 + rank, 3))
+        out["bcast"] = dist.broadcast_array(mine, "world", src=0)
         q.put((rank, out))
     finally:
         td.destroy_process_group()
@@ -202,6 +205,7 @@ def test_world_size_2_reductions_over_gloo():
         assert o["all_failed"] == "LinAlgError"
         assert o["top"][0].tolist() == [3.0, 3.0, 2.5] and o["top"][1].tolist() == [12, 40, 900]
         assert o["top_short"][0].tolist() == [3.0] and o["top_short"][1].tolist() == [12]
+        np.testing.assert_array_equal(o["bcast"], np.random.default_rng(100).random((7, 3)))  # rank 0's, shape included
 
 
 def test_host_candidate_mirror_properties():
@@ -289,3 +293,48 @@ def test_reference_arm_uses_all_host_cores_under_torchrun_env():
     m = re.search(r"THREADS (\d+) (\d+) True", out.stdout + out.stderr)  # bench.py keeps stdout for its one JSON line
     assert m, out.stdout + out.stderr
     assert int(m.group(1)) == int(m.group(2))
+
+
+def test_lbfgs_errors_from_the_objective_propagate_and_leave_no_threads():
+    """the guard around SciPy's private reverse-communication routine must cover the signature probe only --
+    a TypeError / ValueError raised by the objective (the device call) is an error, not a reason to re-run the fit on
+    the threads driver; and the threads driver must not leave workers blocked when the coordinator fails."""
+    import threading
+    from turbo_b200 import lbfgs
+    bounds = np.array([[0.0, 1.0]] * 3)
+
+    def good(X, members):
+        return ((X - 0.3) ** 2).sum(1), 2 * (X - 0.3)
+    x0 = np.random.default_rng(0).random((5, 3))
+    for drv in ("auto", "threads"):
+        x, f, it, n_eval = lbfgs.minimize_batched(good, x0, bounds, driver=drv)
+        assert np.abs(x - 0.3).max() < 1e-6 and n_eval < 12
+    assert lbfgs._reverse_communication_available() in (True, False)
+    for drv, exc in (("auto", TypeError), ("threads", ValueError)):
+        calls = []
+
+        def bad(X, members):
+            calls.append(len(members))
+            if len(calls) > 2:
+                raise exc("from the device call")
+            return good(X, members)
+        before = threading.active_count()
+        with pytest.raises(exc):
+            lbfgs.minimize_batched(bad, x0, bounds, driver=drv)
+        assert len(calls) == 3              # not re-run on another driver
+        assert threading.active_count() == before
+
+
+def test_reference_install_recipe_is_verbatim():
+    """baseline/_ref (git-ignored, shipped to the GPU box) holds the reference package byte for byte"""
+    ref = os.path.join(ROOT, "baseline", "_ref")
+    if not os.path.isfile(os.path.join(ref, "MANIFEST.json")):
+        pytest.skip("baseline/_ref not installed on this machine")
+    sys.path.insert(0, os.path.join(ROOT, "baseline"))
+    try:
+        import install_reference
+        install_reference.verify()
+    finally:
+        sys.path.pop(0)
+    from turbo_b200 import _reference_api
+    assert _reference_api.HAVE_TURBO

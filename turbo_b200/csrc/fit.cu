@@ -46,6 +46,7 @@ static void parse_debug_config() {
         else if (key == "fit_gmax_kinv" && g_ok) c.fit_gmax[2] = iv;
         else if (key == "acq_gmax" && g_ok) c.acq_gmax = iv;
         else if (key == "acq_pair") c.acq_pair = iv != 0;
+        else if (key == "fit_pair") c.fit_pair = iv != 0;
     }
     g_debug = c;
 }

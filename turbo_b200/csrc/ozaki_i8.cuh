@@ -55,7 +55,7 @@ constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_BYTES + 1024;
 // 3 x 896 cycles of MMAs instead of 1 x 1792 (the kernel measured 2336 cycles per 64 bytes of K against 1792 of MMAs).
 // The batched-fit GEMM (ozaki_gemm.cuh) keeps the 64-byte tiles above.
 #ifndef TB200_VAR_KB
-#define TB200_VAR_KB 32
+#define TB200_VAR_KB 64
 #endif
 namespace v {
 constexpr int KB = TB200_VAR_KB;
@@ -104,10 +104,11 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
-// Production builds wait without a bound (try_wait suspends the thread in hardware between polls).  A development
-// build compiled with -DTB200_MBAR_TRAP_SECONDS=<s> traps after that many seconds of WALL-CLOCK time (%globaltimer), so
-// a protocol bug in a new kernel ends the launch instead of hanging the box; a bound counted in polls (round 1) could
-// fire under ncu replay or time-slicing and kill the context of a long optimisation run.
+// try_wait suspends the thread in hardware between polls.  The bound is a compile-time option and it is in WALL-CLOCK
+// time (%globaltimer): -DTB200_MBAR_TRAP_SECONDS=<s> traps after <s> seconds in one wait, so a protocol bug ends the
+// launch instead of hanging the device; without the macro the wait is unbounded.  build.sh passes 30 s: no wait of a
+// correct launch is within four orders of magnitude of that (the longest kernel runs for milliseconds), so neither ncu
+// replay nor time-slicing can trip it -- unlike round 1's bound of 2^24 POLLS, which could.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 #ifdef TB200_MBAR_TRAP_SECONDS
     if (mbar_try_wait(bar, parity)) return;
