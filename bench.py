@@ -63,7 +63,7 @@ if ROOT not in sys.path:
 N_TRAIN, DIM = 4096, 10
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel at the headline shape, from the
 # committed `ncu --set full` captures under profiles/ (None until captured for that engine / shape)
-TRAFFIC = {"dmma": 197.2e6, "i8": 163.9e6}  # profiles/r1_gemm_ncu_full.md, r1_i8v2_ncu_full.md
+TRAFFIC = {"dmma": 197.2e6, "i8g8": 163.9e6}  # profiles/r1_gemm_ncu_full.md, r1_i8v2_ncu_full.md
 METRIC = "EI candidates/sec (n=4096,d=10)"
 KIND_RBF, KIND_MATERN52 = 0, 3
 
@@ -506,7 +506,9 @@ def run_ours(args):
     fp64_equiv = fp64_flop / (avg_ms * 1e-3) / 1e12
     timed_in = ("a separate single-stream pass of the same step (%.1f ms/step); the headline pass overlaps consecutive "
                 "batches on two internal streams" % (ms_serial / ser_steps))
-    traffic = TRAFFIC.get(engine) if (n, d) == (N_TRAIN, DIM) and batch == 2048 else None
+    traffic = None
+    if (n, d) == (N_TRAIN, DIM) and batch == 2048:
+        traffic = TRAFFIC.get("dmma" if engine == "dmma" else "i8g%d" % a_list[0].gmax)
     if engine == "dmma":
         roofline = {"bound": "tensor", "achieved": fp64_equiv, "peak": dmma_tf, "unit": "TFLOP/s",
                     "frac": fp64_equiv / dmma_tf if dmma_tf else None, "traffic": traffic,
@@ -516,13 +518,14 @@ def run_ours(args):
                     "peak_source": "tb200_fp64_peak DMMA microbenchmark on this device (MEASURED_PEAKS.json has no "
                                    "FP64 figure); DFMA vector peak %.2f TFLOP/s" % dfma_tf}
     else:
-        gmax = device.I8_GMAX[engine]
+        gmax = a_list[0].gmax
         pairs = {7: 21, 8: 28, 9: 34}[gmax]
         NP = (n + 127) // 128 * 128
         int8_ops = 2.0 * pairs * 0.5 * NP * (NP + 64) * batch  # 2 ops per INT8 MAC, lower-triangular k-range
         achieved = int8_ops / (avg_ms * 1e-3) / 1e12
-        i8_burst = device.i8_peak(30.0)
-        i8_sustained = device.i8_peak(1500.0)
+        i8_burst = device.i8_peak(30.0)           # pseudo-random digits, ~30 ms per repetition
+        i8_sustained = device.i8_peak(1500.0)     # the same for ~1.5 s per repetition
+        i8_zero = device.i8_peak(30.0, random_digits=False)
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -538,9 +541,13 @@ def run_ours(args):
                     "gemm_share_of_step": g_ms / ms_serial, "timed_in": timed_in,
                     "fp64_equivalent_tflops": fp64_equiv, "fp64_dmma_peak_tflops": dmma_tf,
                     "peak_source": "tb200_i8_peak on this device: tcgen05.mma kind::i8 M128xN256xK32 on resident "
-                                   "shared-memory operands, one CTA per SM, ~30 ms burst, best of 5 (of measured)",
+                                   "shared-memory operands holding pseudo-random digits, one CTA per SM, ~30 ms burst, "
+                                   "best of 5 (of measured)",
                     "peak_sustained": i8_sustained, "frac_of_sustained": achieved / i8_sustained if i8_sustained else None,
                     "peak_sustained_source": "the same loop for ~1.5 s per repetition (power-capped clocks)",
+                    "peak_zero_operands": i8_zero, "frac_of_zero_operand_peak": achieved / i8_zero if i8_zero else None,
+                    "peak_zero_operands_note": "the same loop on all-zero operands: nothing toggles, the power limit is "
+                                               "not reached, the SMs run at the maximum clock (the instruction-rate ceiling)",
                     "cross_check_2x_bf16_burst": 2.0 * bf16 or None, "cross_check_2x_bf16_sustained": 2.0 * bf16_s or None,
                     "step_level_achieved": (int8_ops * (m / batch) * npass * args.steps / (ms * 1e-3) / 1e12)}
 
@@ -615,6 +622,11 @@ def run_ours(args):
                 "config": {"workload": workload_text(cfg), "name": args.config,
                            "candidates_total_per_pass": m_total, "candidates_per_gpu_per_pass": m,
                            "acquisition_passes_per_step": npass, "candidate_batch": batch, "variance_engine": engine,
+                           "slice_products": None if engine == "dmma" else {7: 21, 8: 28, 9: 34}[a_list[0].gmax],
+                           "slice_cutoff_probe": None if engine != "i8a" else
+                           "gmax %d chosen for this model: 21- and 34-product variances differ by %.2f units of "
+                           "eps*n*prior_var on 256 probe points (threshold %.0f, parity floor 64)"
+                           % (a_list[0].gmax, model.factor.gmax_probe, model.factor.GMAX7_UNITS),
                            "l2": "candidate set %.0f MB per GPU vs 126 MB L2" % (m * d * 8 / 1e6),
                            "parallelism": "candidates sharded x%d, model replicated" % world},
                 "e2e": {"value": e2e, "unit": "candidates/s", "h2d_bytes_per_step": npass * m * d * 8 * world,
@@ -708,7 +720,7 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=1 << 14)
     ap.add_argument("--parity-n", type=int, default=1 << 14, help="candidates of the step checked against the oracle (0 = off)")
     ap.add_argument("--cpu-fit", type=int, default=1, help="also time one LML+gradient evaluation of the CPU path")
-    ap.add_argument("--engine", default=None, help="variance engine: auto (default) | dmma | i8l | i8 | i8x")
+    ap.add_argument("--engine", default=None, help="variance engine: auto (default) | dmma | i8a | i8l | i8 | i8x")
     ap.add_argument("--fit", type=int, default=1, help="headline: also time the batched fit")
     ap.add_argument("--full-fit", type=int, default=1, help="also time one whole fit (R restarts, <= 30 iterations)")
     args = ap.parse_args()

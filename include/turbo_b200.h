@@ -82,7 +82,7 @@ int tb200_padded_n(int n);
  * synchronises them first.  Call before unloading the library or resetting a device. */
 int tb200_shutdown(void);
 /* the library's single debug hook is the environment variable TB200_DEBUG ("key=value,key=value": fit_engine=dmma,
- * fit_gmax=7|8|9, fit_gmax_trtri, fit_gmax_kinv, acq_gmax; csrc/common.cuh), read ONCE on first use -- never on the
+ * fit_gmax=7|8|9, fit_gmax_trtri, fit_gmax_kinv; csrc/common.cuh), read ONCE on first use -- never on the
  * call path.  tb200_debug_reload re-reads it (for tests that change it inside one process). */
 int tb200_debug_reload(void);
 
@@ -171,8 +171,10 @@ int tb200_generate_candidates(const tb200_cand_spec* cand_host, int d, int64_t i
 int tb200_fp64_peak(double ms, double* dmma_tflops_host, double* dfma_tflops_host);
 /* measured INT8 tensor-core peak of this device in TOP/s (2 operations per multiply-accumulate): the roofline
  * denominator of the tcgen05.mma kind::i8 kernels (predictive variance, batched fit products).  One CTA per SM issues
- * M128 x N256 x K32 MMAs on shared-memory-resident operands for ~`ms` milliseconds; best of 5 repetitions. */
-int tb200_i8_peak(double ms, double* int8_tops_host);
+ * M128 x N256 x K32 MMAs on shared-memory-resident operands for ~`ms` milliseconds; best of 5 repetitions.
+ * random_digits = 0: zero operands (the rate at the maximum clock: nothing toggles, the power limit is never reached);
+ * random_digits = 1: pseudo-random digits (the rate at the clock the power limit allows for real data). */
+int tb200_i8_peak(double ms, int random_digits, double* int8_tops_host);
 
 /* Incremental refit at fixed hyper-parameters (the reference's `training_iterations` callable returning 0,
  * turbo/modules/surrogates.py:250-269, :306-310): append ONE training point to the factor in O(n^2).

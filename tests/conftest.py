@@ -46,8 +46,14 @@ def golden(request):
 # the reference goes through check_variance(): it asserts the tolerance AND records the error actually achieved, in
 # units of eps * n * prior_var; the session summary (gpurun_out/variance_error.json, committed per round under
 # profiles/) is what the constant is tightened to.
+# Round 2 (profiles/r2_variance_error_first.json, profiles/r2_predict_precision.md), error where 1e-8 relative does not
+# already hold: FP64 DMMA and the 28- / 34-product INT8 engines <= 0.24 units on every fixture and size (VAR_FLOOR_EXACT
+# = 4 leaves 16x); the 21-product engine, which 'auto' uses where its probe allows, <= 5.2 units at the BASELINE shapes
+# and 35 on an ill-conditioned factor -- inside VAR_FLOOR_C = 64, the constant the ORACLE needs against the reference
+# (tests/test_oracle.py); round 1 asserted 256.
 # ---------------------------------------------------------------------------------------------
-VAR_FLOOR_C = 256.0
+VAR_FLOOR_C = 64.0
+VAR_FLOOR_EXACT = 4.0
 _VAR_RECORDS = []
 
 

@@ -30,16 +30,15 @@ def _model(g, engine):
 
 def test_i8l_precision_is_recorded(golden):
     """21 slice products (6 digit planes, truncation ~2^-46 per term): NOT the default engine.  The variance error it
-    achieves on every fixture is recorded next to the default engine's (gpurun_out/variance_error.json); the assertion
-    is only a gross-error bound (16x the default engine's floor)."""
-    from conftest import check_variance, VAR_FLOOR_C
+    achieves on every fixture is recorded next to the other engines' (gpurun_out/variance_error.json) and must stay
+    inside the 64-unit floor; 'auto' uses this engine only for models whose probe shows <= 8 units."""
+    from conftest import check_variance
     g = golden
     model = _model(g, "i8l")
     mu, sd = model.predict(g["Xc"], return_std_dev=True)
     prior = np.exp(g["theta"][0]) if g["has_const"] else 1.0
     np.testing.assert_allclose(mu, g["mu"], rtol=1e-8, atol=1e-8 * np.abs(g["mu"]).max())
-    check_variance("golden/%s/i8l" % g["name"], sd ** 2, g["sigma"] ** 2, g["X"].shape[0], prior * model.y_std ** 2,
-                   c=16 * VAR_FLOOR_C)
+    check_variance("golden/%s/i8l" % g["name"], sd ** 2, g["sigma"] ** 2, g["X"].shape[0], prior * model.y_std ** 2)
 
 
 @pytest.mark.parametrize("engine", ["i8", "i8x"])
@@ -49,11 +48,11 @@ def test_i8_predict_and_acquisition_match_reference(golden, engine):
     model = _model(g, engine)
     mu, sd = model.predict(g["Xc"], return_std_dev=True)
     prior = np.exp(g["theta"][0]) if g["has_const"] else 1.0
-    floor = 256 * EPS * g["X"].shape[0] * prior * model.y_std ** 2
+    floor = 4 * EPS * g["X"].shape[0] * prior * model.y_std ** 2
     np.testing.assert_allclose(mu, g["mu"], rtol=1e-8, atol=1e-8 * np.abs(g["mu"]).max())
-    from conftest import check_variance
+    from conftest import check_variance, VAR_FLOOR_EXACT
     check_variance("golden/%s/%s" % (g["name"], engine), sd ** 2, g["sigma"] ** 2, g["X"].shape[0],
-                   prior * model.y_std ** 2)
+                   prior * model.y_std ** 2, c=VAR_FLOOR_EXACT)
     acq, _ = tb.GpuEI(g["xi"]).construct_function(0, model, g["extremum"], g["incumbent"])
     vals = acq(g["Xc"])
     ref = g["ei"]
@@ -91,7 +90,7 @@ def test_i8_matches_dmma_at_size(n, d, kind, noise):
         acq, _ = tb.GpuEI(0.01).construct_function(0, model, 'min', float(y.min()))
         val, idx, _ = acq.argmax_over(candidates=Xc)
         out[engine] = (mu, sd ** 2, idx, model.y_std)
-    floor = 256 * EPS * n * out["dmma"][3] ** 2
+    floor = 4 * EPS * n * out["dmma"][3] ** 2  # conftest.VAR_FLOOR_EXACT: engines with >= 28 slice products
     og = O.FittedGP(O.KernelSpec(kind, d, True), theta, X, y)
     # mu = y_std * sum_j K*_j alpha_j + y_mean: the engines add the n terms in different orders, so they agree to the
     # rounding of that sum, eps * sum_j |K*_j alpha_j| <= eps * sf2 * |alpha|_1 (1e-8 absolute for the ill-conditioned
@@ -112,7 +111,7 @@ def test_i8_rejects_large_n():
     from turbo_b200 import device
     with pytest.raises(ValueError):
         device.resolve_engine("i8", 65536)
-    assert device.resolve_engine("auto", 65536) == "dmma" and device.resolve_engine("auto", 16384) == "i8"
+    assert device.resolve_engine("auto", 65536) == "dmma" and device.resolve_engine("auto", 16384) == "i8a"
 
 
 def test_max_dimension_and_slot_reuse_over_many_small_batches():
@@ -137,7 +136,7 @@ def test_max_dimension_and_slot_reuse_over_many_small_batches():
         model = sur.construct_model(0, X, y)[0]
         mu, sd = model.predict(Xc, return_std_dev=True)
         np.testing.assert_allclose(mu, mu_o, rtol=1e-8, atol=1e-8 * np.abs(mu_o).max())
-        np.testing.assert_allclose(sd ** 2, sd_o ** 2, rtol=1e-8, atol=256 * EPS * n * model.y_std ** 2)
+        np.testing.assert_allclose(sd ** 2, sd_o ** 2, rtol=1e-8, atol=4 * EPS * n * model.y_std ** 2)
         acq = tb.GpuEI(0.01).construct_function(0, model, 'min', float(y.min()))[0]
         val, idx, x = acq.argmax_over(candidates=Xc, batch=256)
         assert idx == O.argmax_first(ei_o) and np.array_equal(x[0], Xc[idx])

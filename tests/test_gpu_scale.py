@@ -33,7 +33,7 @@ def test_cfg5_shape_predict_and_ei_match_oracle():
     spec = tb.KernelSpec(cfg["kind"], d, True)
     sur = tb.GpuGPSurrogate(model_params=dict(kernel=(spec, theta), normalize_y=True), training_iterations=0)
     model, _ = sur.construct_model(0, X, y)
-    assert tb.device.resolve_engine(None, model.factor.NP) == "i8"
+    assert tb.device.resolve_engine(None, model.factor.NP) == "i8a"
     mu, sd = model.predict(Xc, return_std_dev=True)
     acq = tb.GpuEI(0.01).construct_function(0, model, "min", float(y.min()))[0]
     vals = acq(Xc)

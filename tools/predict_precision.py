@@ -61,7 +61,7 @@ def main():
         prior = (np.exp(theta[0]) + np.exp(theta[-1])) * og.y_std ** 2
         unit = eps * n * prior
         spec = tb.KernelSpec(kind, d, True)
-        for engine in ("dmma", "i8l", "i8", "i8x"):
+        for engine in ("dmma", "i8l", "i8", "i8x", "auto"):
             sur = tb.GpuGPSurrogate(model_params=dict(kernel=(spec, theta), normalize_y=True), training_iterations=0,
                                     variance_engine=engine)
             model, _ = sur.construct_model(0, X, y)
@@ -71,6 +71,8 @@ def main():
             _v, idx, _x = acq.argmax_over(candidates=Xc)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a = device.Acquirer(model.factor, acq._spec_c(), engine=engine)
+            if engine == "auto":
+                engine = "auto -> gmax %d (probe %.2f units)" % (a.gmax, model.factor.gmax_probe)
             Xd = device.to_device(Xc)
             a.run(Xd, args.m, 0, None)
             torch.cuda.synchronize()
@@ -82,7 +84,7 @@ def main():
             need = dv > 1e-8 * var_o
             print("| %s | %d | %s | %.2f | %.2f | %.2e | %.2e | %s | %.3f |" % (
                 name, n, engine, dv.max() / unit, (dv[need] / unit).max() if need.any() else 0.0,
-                (dv / np.maximum(var_o, 1e-300)).max(), np.abs(vals - ref).max() / np.abs(ref).max(),
+                (dv / np.maximum(var_o, 1e-300)).max(), np.abs(vals - ref).max() / max(np.abs(ref).max(), 1e-300),
                 "yes" if idx == k_o else "NO (%d vs %d)" % (idx, k_o), e0.elapsed_time(e1) * 2048.0 / args.m))
             del model, a
         print("<!-- %s: oracle %.1f s, max |mu| err vs oracle %.2e -->" % (name, t_or, np.abs(mu - mu_o).max()))

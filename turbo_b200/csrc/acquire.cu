@@ -228,7 +228,7 @@ __global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_kernel(
     const double sf2 = unpack_hyper(spec, theta).sf2;
     const int c = threadIdx.x & 7, jg = threadIdx.x >> 3;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int kblks = NP / i8::v::KB;
+    const int kblks = NP / i8::KB;
     // persistent: a few CTAs per SM walk the (candidate group, point split) items.  The block scheduler places a
     // later grid only after every CTA of the grids ahead of it; a small grid is placed at once next to the resident
     // variance CTAs instead of holding back (or being held back by) the 1024-CTA variance grid.
@@ -244,7 +244,7 @@ __global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_kernel(
         }
         __syncthreads();
         const int ct = (int)(c0 / i8::TM), rg = (int)((c0 % i8::TM) >> 3);
-        uint8_t* const tile_base = KsS + (size_t)ct * kblks * i8::v::A_TILE + (size_t)rg * i8::v::SBO + c * 16;
+        uint8_t* const tile_base = KsS + (size_t)ct * kblks * i8::A_TILE + (size_t)rg * i8::SBO + c * 16;
         double msum = 0.0;
         const int jlo = split * jchunk, jhi = min(NP, jlo + jchunk);
         for (int j0 = jlo + jg * KS_JG; j0 < jhi; j0 += (KS_THREADS / 8) * KS_JG) {
@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_kernel(
                 lo[q] = (uint32_t)x0; hi[q] = (uint32_t)(x0 >> 32);
                 lo[q + 1] = (uint32_t)x1; hi[q + 1] = (uint32_t)(x1 >> 32);
             }
-            uint8_t* dst = tile_base + (size_t)(j0 / i8::v::KB) * i8::v::A_TILE + ((j0 % i8::v::KB) >> 4) * i8::LBO;
+            uint8_t* dst = tile_base + (size_t)(j0 / i8::KB) * i8::A_TILE + ((j0 % i8::KB) >> 4) * i8::LBO;
 #pragma unroll
             for (int sl = 0; sl < i8::S; ++sl) {
                 // digit sl = byte (6 - sl) of the fixed-point value: bytes 2,1,0 of hi, then 3,2,1,0 of lo
@@ -345,7 +345,7 @@ __global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_staged_kernel(
     const double sf2 = unpack_hyper(spec, theta).sf2;
     const int c = threadIdx.x % NC, jg = threadIdx.x / NC;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int kblks = NP / i8::v::KB;
+    const int kblks = NP / i8::KB;
     const int total = ngroups * nsplit;
     const int per = (total + (int)gridDim.x - 1) / (int)gridDim.x;
     const int lo_item = (int)blockIdx.x * per, hi_item = min(total, lo_item + per);
@@ -373,7 +373,7 @@ __global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_staged_kernel(
         __syncthreads();
         // candidate c of the item: row group (c0 % 128) / 8 + c / 8 of candidate tile c0 / 128, row c % 8 in the group
         const int ct = (int)(c0 / i8::TM), rg = (int)((c0 % i8::TM) >> 3) + (c >> 3);
-        uint8_t* const tile_base = KsS + (size_t)ct * kblks * i8::v::A_TILE + (size_t)rg * i8::v::SBO + (c & 7) * 16;
+        uint8_t* const tile_base = KsS + (size_t)ct * kblks * i8::A_TILE + (size_t)rg * i8::SBO + (c & 7) * 16;
         double msum = 0.0;
         const int j0 = jlo + jg * KS_JG;
         if (j0 < NP) {
@@ -410,7 +410,7 @@ __global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_staged_kernel(
                 lo[q] = (uint32_t)x0; hi[q] = (uint32_t)(x0 >> 32);
                 lo[q + 1] = (uint32_t)x1; hi[q + 1] = (uint32_t)(x1 >> 32);
             }
-            uint8_t* dst = tile_base + (size_t)(j0 / i8::v::KB) * i8::v::A_TILE + ((j0 % i8::v::KB) >> 4) * i8::LBO;
+            uint8_t* dst = tile_base + (size_t)(j0 / i8::KB) * i8::A_TILE + ((j0 % i8::KB) >> 4) * i8::LBO;
 #pragma unroll
             for (int sl = 0; sl < i8::S; ++sl) {
                 const int byte = (sl < 3) ? 2 - sl : 6 - sl;
@@ -465,10 +465,8 @@ __global__ void __launch_bounds__(256) linv_slice_kernel(const double* __restric
     const long e = (long)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= (long)NP * chunks_per_row) return;
     const int r = (int)(e / chunks_per_row), kc = (int)(e % chunks_per_row);
-    const int rt = r / i8::TN, kb = (kc * 16) / i8::v::KB;
-    // tiles above the diagonal are never read -- except the first one of an even row tile, which the paired variance
-    // kernel multiplies like its odd neighbour's diagonal tile: it is written (as zero digits, Linv being lower triangular)
-    if (kb * i8::v::KB >= ((rt | 1) + 1) * i8::TN) return;
+    const int rt = r / i8::TN, kb = (kc * 16) / i8::KB;
+    if (kb > rt) return;  // tiles above the diagonal are never read
     const double sc = ldexp(1.0, -(int)rowscale[NP + r]);
     __align__(16) uint8_t bytes[i8::S][16];
 #pragma unroll
@@ -478,9 +476,9 @@ __global__ void __launch_bounds__(256) linv_slice_kernel(const double* __restric
 #pragma unroll
         for (int s = 0; s < i8::S; ++s) bytes[s][q] = u[s];
     }
-    const int kblks = NP / i8::v::KB;
-    const size_t off = ((size_t)rt * kblks + kb) * i8::v::B_TILE + (size_t)((r % i8::TN) >> 3) * i8::v::SBO +
-                       (((kc * 16) % i8::v::KB) >> 4) * i8::LBO + (r & 7) * 16;
+    const int kblks = NP / i8::KB;
+    const size_t off = ((size_t)rt * kblks + kb) * i8::B_TILE + (size_t)((r % i8::TN) >> 3) * i8::SBO +
+                       (((kc * 16) % i8::KB) >> 4) * i8::LBO + (r & 7) * 16;
 #pragma unroll
     for (int s = 0; s < i8::S; ++s)
         *reinterpret_cast<uint4*>(out + (size_t)s * slice_stride + off) = *reinterpret_cast<const uint4*>(bytes[s]);
@@ -1219,13 +1217,12 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
             ip.ldp = batch;
             ip.candSliceStride = slice_stride;
             ip.linvSliceStride = (long)NP * NP;
-            ip.kblks = NP / i8::v::KB;
+            ip.kblks = NP / i8::KB;
             ip.rowTiles = NP / i8::TN;
             ip.candTiles = (int)(q.mbp / i8::TM);
-            const bool pair = debug_config().acq_pair != 0;
-            const int rc = f8.gmax == 7   ? i8::launch_colsumsq_i8<7>(ip, s_var, pair)
-                           : f8.gmax == 8 ? i8::launch_colsumsq_i8<8>(ip, s_var, pair)
-                                          : i8::launch_colsumsq_i8<9>(ip, s_var, pair);
+            const int rc = f8.gmax == 7   ? i8::launch_colsumsq_i8<7>(ip, s_var)
+                           : f8.gmax == 8 ? i8::launch_colsumsq_i8<8>(ip, s_var)
+                                          : i8::launch_colsumsq_i8<9>(ip, s_var);
             if (rc) return -1;
         } else {
             GemmParams gp = gemm_params(Linv, NP, w.Ks, NP, w.partial, batch, NB, (int)(q.mbp / 128), NP, 1.0, 0.0);
@@ -1431,7 +1428,7 @@ int tb200_acquire_grad(const double* Xp, int P, const double* XsT, const double*
     return 0;
 }
 
-int tb200_i8_peak(double ms, double* int8_tops) {
+int tb200_i8_peak(double ms, int random_digits, double* int8_tops) {
     TB_CHECK(int8_tops, "NULL pointer argument");
     int dev = 0, sms = 0;
     TB_CUDA(cudaGetDevice(&dev));
@@ -1450,7 +1447,7 @@ int tb200_i8_peak(double ms, double* int8_tops) {
     double best = 0.0;
     for (int rep = 0; rep < 6; ++rep) {
         TB_CUDA(cudaEventRecord(e0, 0));
-        TB_LAUNCH(i8::i8_peak_kernel<i8::PEAK_N>, dim3(sms), dim3(64), i8::PEAK_SMEM, 0, batches);
+        TB_LAUNCH(i8::i8_peak_kernel<i8::PEAK_N>, dim3(sms), dim3(64), i8::PEAK_SMEM, 0, batches, random_digits);
         TB_CUDA(cudaEventRecord(e1, 0));
         TB_CUDA(cudaEventSynchronize(e1));
         float t = 0.f;

@@ -78,19 +78,12 @@ inline int device_once(DeviceOnce& o, F&& configure) {
 //   fit_engine=dmma      keep the batched fit on the FP64 DMMA GEMM (the cross-check the tests compare the INT8 fit with)
 //   fit_gmax=7|8|9       slice-pair cut-off of every INT8 fit stage (default 8/8/7: potrf, trtri, K^-1)
 //   fit_gmax_trtri=..    the inverse-factor recurrence alone;   fit_gmax_kinv=..  the K^-1 product alone
-//   acq_gmax=7|8|9       force the slice-pair cut-off of the predictive-variance engine (default: chosen per model from
-//                        an a-priori error bound, tb200_i8_prepare)
-//   acq_pair=0|1         variance kernel as single CTAs / as two-CTA clusters with a multicast candidate operand
-//   fit_pair=0|1         the same for the batched fit's INT8 GEMM (multicast row operand)
 // Everything else that used to be switchable (stream priorities, K* staging, look-ahead, schedule thresholds) was an
 // A/B question of round 1 and is settled; the measurements are under profiles/r1_*.
 // ---------------------------------------------------------------------------------------------
 struct DebugConfig {
     bool fit_dmma = false;
     int fit_gmax[3] = {8, 8, 7};
-    int acq_gmax = 0;  // 0 = automatic
-    int acq_pair = 0;  // variance kernel in clusters of two row tiles with a multicast candidate operand (A/B: 0 = off)
-    int fit_pair = 0;  // fit GEMM in clusters of two column tiles with a multicast row operand (A/B: 0 = off)
 };
 const DebugConfig& debug_config();
 void debug_config_reload();

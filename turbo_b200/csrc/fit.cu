@@ -44,9 +44,6 @@ static void parse_debug_config() {
         else if (key == "fit_gmax" && g_ok) c.fit_gmax[0] = c.fit_gmax[1] = c.fit_gmax[2] = iv;
         else if (key == "fit_gmax_trtri" && g_ok) c.fit_gmax[1] = iv;
         else if (key == "fit_gmax_kinv" && g_ok) c.fit_gmax[2] = iv;
-        else if (key == "acq_gmax" && g_ok) c.acq_gmax = iv;
-        else if (key == "acq_pair") c.acq_pair = iv != 0;
-        else if (key == "fit_pair") c.fit_pair = iv != 0;
     }
     g_debug = c;
 }
@@ -113,12 +110,15 @@ __global__ void __launch_bounds__(256) gram_train_kernel(const double* __restric
     for (int a = 0; a < 4; ++a)
 #pragma unroll
         for (int b = 0; b < 4; ++b) r2[a][b] = 0.0;
+    // thread (ty, tx) owns rows ty*4 + a and columns tx + 16*b: the 16 tx of a half-warp read 16 CONSECUTIVE doubles of
+    // xj per load (conflict-free; the tx*4 + b mapping of round 1 was a 4-way bank conflict on every xj load:
+    // 21 M conflicts per lml_grad launch, profiles/r2_fit_small_kernels_ncu.md) and write 128 contiguous bytes of K
     for (int k = 0; k < d; ++k) {
         double va[4], vb[4];
 #pragma unroll
         for (int a = 0; a < 4; ++a) va[a] = xi[k * GT + ty * 4 + a];
 #pragma unroll
-        for (int b = 0; b < 4; ++b) vb[b] = xj[k * GT + tx * 4 + b];
+        for (int b = 0; b < 4; ++b) vb[b] = xj[k * GT + tx + 16 * b];
 #pragma unroll
         for (int a = 0; a < 4; ++a)
 #pragma unroll
@@ -131,10 +131,9 @@ __global__ void __launch_bounds__(256) gram_train_kernel(const double* __restric
 #pragma unroll
     for (int a = 0; a < 4; ++a) {
         const int i = ti * GT + ty * 4 + a;
-        double out[4];
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
-            const int j = tj * GT + tx * 4 + b;
+            const int j = tj * GT + tx + 16 * b;
             double v;
             if (i >= n || j >= n) {
                 v = (i == j) ? 1.0 : 0.0;
@@ -144,11 +143,8 @@ __global__ void __launch_bounds__(256) gram_train_kernel(const double* __restric
             } else {
                 v = h.sf2 * shape_fn(spec.kind, r2[a][b]);
             }
-            out[b] = v;
+            Kr[(long)i * NP + j] = v;
         }
-        double2* dst = reinterpret_cast<double2*>(Kr + (long)i * NP + tj * GT + tx * 4);
-        dst[0] = make_double2(out[0], out[1]);
-        dst[1] = make_double2(out[2], out[3]);
     }
 }
 
@@ -465,7 +461,7 @@ __global__ void __launch_bounds__(256) lml_grad_kernel(const double* __restrict_
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nl = spec.ard ? d : 1;
     const int off_ls = spec.has_const ? 1 : 0;
-    const int i0 = ti * GT + ty * 4, j0 = tj * GT + tx * 4;
+    const int i0 = ti * GT + ty * 4, j0 = tj * GT + tx;  // columns j0 + 16 b (see gram_train_kernel)
 
     // w = alpha_i alpha_j - Kinv_ij for the valid lower pairs (loads first: they overlap the distance loop)
     double w[4][4];
@@ -475,7 +471,7 @@ __global__ void __launch_bounds__(256) lml_grad_kernel(const double* __restrict_
         const double ai = i < n ? al[i] : 0.0;
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
-            const int j = j0 + b;
+            const int j = j0 + 16 * b;
             w[a][b] = (i < n && j <= i) ? ai * al[j] - Kr[(long)i * NP + j] : 0.0;
         }
     }
@@ -487,7 +483,7 @@ __global__ void __launch_bounds__(256) lml_grad_kernel(const double* __restrict_
     for (int k = 0; k < d; ++k) {
         double xa[4], xb[4];
 #pragma unroll
-        for (int a = 0; a < 4; ++a) { xa[a] = xi[k * GT + ty * 4 + a]; xb[a] = xj[k * GT + tx * 4 + a]; }
+        for (int a = 0; a < 4; ++a) { xa[a] = xi[k * GT + ty * 4 + a]; xb[a] = xj[k * GT + tx + 16 * a]; }
 #pragma unroll
         for (int a = 0; a < 4; ++a)
 #pragma unroll
@@ -502,7 +498,7 @@ __global__ void __launch_bounds__(256) lml_grad_kernel(const double* __restrict_
     for (int a = 0; a < 4; ++a)
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
-            const int i = i0 + a, j = j0 + b;
+            const int i = i0 + a, j = j0 + 16 * b;
             f[a][b] = 0.0;
             if (!(i < n && j <= i)) continue;
             if (i == j) {
@@ -529,7 +525,7 @@ __global__ void __launch_bounds__(256) lml_grad_kernel(const double* __restrict_
         for (int k = 0; k < d; ++k) {
             double xa[4], xb[4];
 #pragma unroll
-            for (int a = 0; a < 4; ++a) { xa[a] = xi[k * GT + ty * 4 + a]; xb[a] = xj[k * GT + tx * 4 + a]; }
+            for (int a = 0; a < 4; ++a) { xa[a] = xi[k * GT + ty * 4 + a]; xb[a] = xj[k * GT + tx + 16 * a]; }
             double acc = 0.0;
 #pragma unroll
             for (int a = 0; a < 4; ++a)

@@ -37,11 +37,7 @@ struct GemmI8Params {
     int kbWinLo, kbWinHi;
 };
 
-// PAIR = true: clusters of two CTAs with consecutive blockIdx.x.  Every launch enumerates its output tiles so that such
-// a pair has the same 128-row A tile `it` and the same k-range (two column tiles per row tile in rectangle mode, an even
-// number of them per row tile in triangular mode): the A operand -- two thirds of a stage -- is fetched once per pair,
-// each CTA loading every other digit plane and multicasting it into both shared memories (see colsumsq_i8_kernel).
-template <int GMAX, bool PAIR = false>
+template <int GMAX>
 __global__ void __launch_bounds__(THREADS, 1) gemm_i8_kernel(const GemmI8Params p) {
     constexpr int NG = GMAX - 1;
     static_assert(NG * TN <= TMEM_COLS, "accumulators exceed TMEM");
@@ -72,15 +68,13 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_i8_kernel(const GemmI8Params 
         if (kb_hi > p.kbWinHi) kb_hi = p.kbWinHi;
     }
     const int nkb = kb_hi - kb_lo;
-    if (nkb <= 0) return;  // uniform over the CTA (and over a pair: same `it`), before any barrier or TMEM allocation
+    if (nkb <= 0) return;  // uniform over the CTA, before any barrier or TMEM allocation
     const int rs = (int)blockIdx.y;  // restart
-    uint32_t crank = 0;
-    if constexpr (PAIR) crank = cluster_ctarank();
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(&full_bar[s], 1);
-            mbar_init(&empty_bar[s], PAIR ? 2 : 1);
+            mbar_init(&empty_bar[s], 1);
         }
         mbar_init(&done_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -93,7 +87,6 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_i8_kernel(const GemmI8Params 
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if constexpr (PAIR) cluster_sync_all();  // the peer's barriers exist before anything is multicast to them
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = tmem_base_s;
 
@@ -115,15 +108,8 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_i8_kernel(const GemmI8Params 
 #pragma unroll
                 for (int sl = 0; sl < S; ++sl) {
                     const size_t so = (size_t)sl * p.sliceStride + kb * B_TILE;
-                    if constexpr (PAIR) {
-                        if ((uint32_t)(sl & 1) == crank) {  // my half of the planes, for both CTAs
-                            bulk_g2s_multicast(st + sl * A_TILE, a0_src + so, B_TILE, &full_bar[s], (uint16_t)3);
-                            bulk_g2s_multicast(st + sl * A_TILE + B_TILE, a1_src + so, B_TILE, &full_bar[s], (uint16_t)3);
-                        }
-                    } else {
-                        bulk_g2s(st + sl * A_TILE, a0_src + so, B_TILE, &full_bar[s]);
-                        bulk_g2s(st + sl * A_TILE + B_TILE, a1_src + so, B_TILE, &full_bar[s]);
-                    }
+                    bulk_g2s(st + sl * A_TILE, a0_src + so, B_TILE, &full_bar[s]);
+                    bulk_g2s(st + sl * A_TILE + B_TILE, a1_src + so, B_TILE, &full_bar[s]);
                     bulk_g2s(st + S * A_TILE + sl * B_TILE, b_src + (size_t)sl * b_slice + kb * B_TILE, B_TILE,
                              &full_bar[s]);
                 }
@@ -147,8 +133,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_i8_kernel(const GemmI8Params 
                 }
                 issue_step<GMAX, 1, false, 0, 1>(tmem_base, ad0 + (uint64_t)((2 * LBO) >> 4),
                                                  bd0 + (uint64_t)((2 * LBO) >> 4));
-                if constexpr (PAIR) umma_commit_multicast(&empty_bar[s], (uint16_t)3);
-                else umma_commit(&empty_bar[s]);
+                umma_commit(&empty_bar[s]);
                 if (i == nkb - 1) umma_commit(&done_bar);
             }
             __syncwarp();
@@ -193,61 +178,33 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_i8_kernel(const GemmI8Params 
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if constexpr (PAIR) cluster_sync_all();  // no CTA leaves while its peer may still signal its barriers
     if (warp == 1) {
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
     }
 }
 
-template <int GMAX, bool PAIR>
-inline int launch_gemm_i8_one(const GemmI8Params& p, int ntiles, int R, cudaStream_t stream) {
+template <int GMAX>
+inline int launch_gemm_i8(const GemmI8Params& p, int ntiles, int R, cudaStream_t stream) {
     static DeviceOnce once;
     if (device_once(once, [] {
-            TB_CUDA(cudaFuncSetAttribute(gemm_i8_kernel<GMAX, PAIR>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+            TB_CUDA(cudaFuncSetAttribute(gemm_i8_kernel<GMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)SMEM_BYTES));
             return 0;
         }))
         return -1;
-    if constexpr (PAIR) {
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3((unsigned)ntiles, (unsigned)R);
-        cfg.blockDim = dim3(THREADS);
-        cfg.dynamicSmemBytes = SMEM_BYTES;
-        cfg.stream = stream;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = 2;
-        attr[0].val.clusterDim.y = 1;
-        attr[0].val.clusterDim.z = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
-        TB_CUDA(cudaLaunchKernelEx(&cfg, gemm_i8_kernel<GMAX, PAIR>, p));
-        ++g_launches;
-    } else {
-        TB_LAUNCH((gemm_i8_kernel<GMAX, PAIR>), dim3((unsigned)ntiles, (unsigned)R), dim3(THREADS), SMEM_BYTES, stream, p);
-    }
-    return 0;
-}
-
-template <int GMAX>
-inline int launch_gemm_i8(const GemmI8Params& p, int ntiles, int R, cudaStream_t stream) {
     if (ntiles <= 0 || R <= 0) return 0;
-    // pairs need an even number of tiles whose consecutive members share the A row tile: two column tiles per row tile
-    // (rectangle) or 2 it + 2 of them (triangle)
-    const bool pair = debug_config().fit_pair != 0 && ntiles % 2 == 0 && (p.tri || p.nColTiles % 2 == 0);
     // the longest k-range any CTA of this launch can have
     const int span = p.tri ? p.kblks : (p.kbHiByRow ? p.kblks : p.kbHi) - p.kbLo;
-    if (span <= PASS_KB)
-        return pair ? launch_gemm_i8_one<GMAX, true>(p, ntiles, R, stream)
-                    : launch_gemm_i8_one<GMAX, false>(p, ntiles, R, stream);
+    if (span <= PASS_KB) {
+        TB_LAUNCH((gemm_i8_kernel<GMAX>), dim3((unsigned)ntiles, (unsigned)R), dim3(THREADS), SMEM_BYTES, stream, p);
+        return 0;
+    }
     const int lo0 = p.tri ? 0 : p.kbLo, hi0 = p.tri ? p.kblks : (p.kbHiByRow ? p.kblks : p.kbHi);
     for (int w = lo0; w < hi0; w += PASS_KB) {
         GemmI8Params q = p;
         q.kbWinLo = w;
         q.kbWinHi = (w + PASS_KB < hi0) ? w + PASS_KB : hi0;
-        if (pair ? launch_gemm_i8_one<GMAX, true>(q, ntiles, R, stream)
-                 : launch_gemm_i8_one<GMAX, false>(q, ntiles, R, stream))
-            return -1;
+        TB_LAUNCH((gemm_i8_kernel<GMAX>), dim3((unsigned)ntiles, (unsigned)R), dim3(THREADS), SMEM_BYTES, stream, q);
     }
     return 0;
 }

@@ -49,26 +49,6 @@ constexpr int LBO = 128;             // bytes between the two 16-byte K chunks o
 constexpr int SBO = (KB / 16) * 128; // bytes between groups of 8 rows
 constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_BYTES + 1024;
 
-// Layout of the VARIANCE kernel's operands (K* digit planes, Linv digit planes) and its pipeline granularity: one stage
-// = one tile of V_KB bytes of K per plane.  64: 2 stages of 84 KB (round 1).  32: 4 stages of 42 KB -- the same shared
-// memory, but a stage is refilled while THREE others are consumed, so the L2 round trip of a refill is covered by
-// 3 x 896 cycles of MMAs instead of 1 x 1792 (the kernel measured 2336 cycles per 64 bytes of K against 1792 of MMAs).
-// The batched-fit GEMM (ozaki_gemm.cuh) keeps the 64-byte tiles above.
-#ifndef TB200_VAR_KB
-#define TB200_VAR_KB 64
-#endif
-namespace v {
-constexpr int KB = TB200_VAR_KB;
-static_assert(KB == 32 || KB == 64, "variance tiles hold 32 or 64 bytes of K");
-constexpr int A_TILE = TM * KB;
-constexpr int B_TILE = TN * KB;
-constexpr int SBO = (KB / 16) * 128;
-constexpr int STAGE_BYTES = S * (A_TILE + B_TILE);
-constexpr int STAGES = (2 * 86016) / STAGE_BYTES;
-constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_BYTES + 1024;
-constexpr int PASS_KB = 8192 / KB;  // k-blocks of one exact INT32 accumulation pass
-}  // namespace v
-
 // byte offset of element (row r, k in [0,64)) inside a canonical K-major no-swizzle tile
 __host__ __device__ inline int tile_offset(int r, int k) {
     return (r >> 3) * SBO + (k >> 4) * LBO + (r & 7) * 16 + (k & 15);
@@ -81,7 +61,7 @@ struct Params {
     double* partial;         // [rowTiles][ldp]
     long ldp;
     long candSliceStride, linvSliceStride;  // bytes
-    int kblks;               // K / v::KB (tiles per row of tiles)
+    int kblks;               // K / 64 (tiles per row of tiles)
     int rowTiles, candTiles;
 };
 
@@ -130,36 +110,9 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32
                  "l"(src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
-// multicast variants (thread-block clusters): the copy lands at the same CTA-relative offset in every CTA of `mask` and
-// signals the mbarrier at the same offset in each of them; the commit arrives on that barrier in every CTA of `mask`
-__device__ __forceinline__ void bulk_g2s_multicast(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar,
-                                                   uint16_t mask) {
-    asm volatile(
-        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;" ::"r"(
-            smem_u32(dst_smem)),
-        "l"(src), "r"(bytes), "r"(smem_u32(bar)), "h"(mask)
-        : "memory");
-}
-__device__ __forceinline__ void umma_commit_multicast(uint64_t* bar, uint16_t mask) {
-    asm volatile(
-        "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
-            smem_u32(bar)),
-        "h"(mask)
-        : "memory");
-}
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-    uint32_t r;
-    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-    return r;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-
-__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, int sbo = SBO) {
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
     // K-major, SWIZZLE_NONE: start>>4 [0,14), LBO>>4 [16,30), SBO>>4 [32,46), version=1 [46,48)
-    return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)(LBO >> 4) << 16) | ((uint64_t)(sbo >> 4) << 32) |
+    return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)(LBO >> 4) << 16) | ((uint64_t)(SBO >> 4) << 32) |
            (1ull << 46);
 }
 __device__ __forceinline__ void umma_i8(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
@@ -203,42 +156,41 @@ __device__ __forceinline__ bool elect_one() {
 // of row 0 = `bd0`; 8 rows further = +SBO bytes = +SBO/16 in the descriptor's address field) -> TMEM columns
 // d_tmem + [N_LO, N_HI).  Balanced chunks of <= 256 columns (multiples of 16), all resolved at compile time so the
 // issuing lane executes a handful of uniform-register adds per MMA.
-template <int N_LO, int N_HI, int ACC, int ASGN = 0, int KBT = KB>
+template <int N_LO, int N_HI, int ACC, int ASGN = 0>
 __device__ __forceinline__ void issue_range(uint32_t d_tmem, uint64_t ad, uint64_t bd0) {
     if constexpr (N_HI > N_LO) {
         constexpr int width = N_HI - N_LO;
         constexpr int nchunks = (width + 255) / 256;
         constexpr int chunk = ((width / nchunks) + 15) & ~15;
         constexpr int nc = chunk < width ? chunk : width;
-        constexpr int sbo = (KBT / 16) * 128;
-        umma_i8(d_tmem + N_LO, ad, bd0 + (uint64_t)((N_LO >> 3) * (sbo >> 4)), idesc(nc, ASGN), (uint32_t)ACC);
-        issue_range<N_LO + nc, N_HI, ACC, ASGN, KBT>(d_tmem, ad, bd0);
+        umma_i8(d_tmem + N_LO, ad, bd0 + (uint64_t)((N_LO >> 3) * (SBO >> 4)), idesc(nc, ASGN), (uint32_t)ACC);
+        issue_range<N_LO + nc, N_HI, ACC, ASGN>(d_tmem, ad, bd0);
     }
 }
 
 // all slice products of one K = 32 step.  FIRST: no accumulator holds a value yet -- groups [0, COVERED) have been
 // written by earlier slices of this step, the rest are overwritten (accumulate = 0).
-template <int GMAX, int I, bool FIRST, int COVERED, int ASGN = 0, int KBT = KB>
+template <int GMAX, int I, bool FIRST, int COVERED, int ASGN = 0>
 __device__ __forceinline__ void issue_step(uint32_t tmem_base, uint64_t ad0, uint64_t bd0) {
     if constexpr (I <= S) {
         constexpr int J = (GMAX - I < S) ? GMAX - I : S;  // Linv slices j = 1..J pair with a_I
         if constexpr (J > 0) {
             // a_I * b_j lands in group I+j-2: columns (I-1)*TN + (j-1)*TN of the accumulator block
             const uint32_t d = tmem_base + (I - 1) * TN;
-            const uint64_t ad = ad0 + (uint64_t)((I - 1) * ((TM * KBT) >> 4));
+            const uint64_t ad = ad0 + (uint64_t)((I - 1) * (A_TILE >> 4));
             if constexpr (!FIRST) {
-                issue_range<0, J * TN, 1, ASGN, KBT>(d, ad, bd0);
-                issue_step<GMAX, I + 1, false, 0, ASGN, KBT>(tmem_base, ad0, bd0);
+                issue_range<0, J * TN, 1, ASGN>(d, ad, bd0);
+                issue_step<GMAX, I + 1, false, 0, ASGN>(tmem_base, ad0, bd0);
             } else {
                 constexpr int split0 = (COVERED - (I - 1)) * TN;  // columns below `split` are initialised
                 constexpr int split = split0 < 0 ? 0 : (split0 > J * TN ? J * TN : split0);
-                issue_range<0, split, 1, ASGN, KBT>(d, ad, bd0);
-                issue_range<split, J * TN, 0, ASGN, KBT>(d, ad, bd0);
+                issue_range<0, split, 1, ASGN>(d, ad, bd0);
+                issue_range<split, J * TN, 0, ASGN>(d, ad, bd0);
                 constexpr int cov = (I - 1 + J > COVERED) ? I - 1 + J : COVERED;
-                issue_step<GMAX, I + 1, true, cov, ASGN, KBT>(tmem_base, ad0, bd0);
+                issue_step<GMAX, I + 1, true, cov, ASGN>(tmem_base, ad0, bd0);
             }
         } else {
-            issue_step<GMAX, I + 1, FIRST, COVERED, ASGN, KBT>(tmem_base, ad0, bd0);
+            issue_step<GMAX, I + 1, FIRST, COVERED, ASGN>(tmem_base, ad0, bd0);
         }
     }
 }
@@ -256,44 +208,26 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 // digit planes a kernel with cut-off GMAX reads: plane s pairs with planes 1..GMAX-s, so plane 7 is unused at GMAX = 7
 __host__ __device__ constexpr int planes_used(int gmax) { return gmax - 1 < S ? gmax - 1 : S; }
 
-// PAIR = true: launched in clusters of two CTAs that work on the SAME candidate tile and on two ADJACENT Linv row tiles
-// (2q, 2q+1).  Both need the same K* digit planes: each CTA fetches every other plane and multicasts it into both shared
-// memories, so a pair reads the candidate operand -- two thirds of a stage -- from L2 once instead of twice (84 KB -> 56
-// KB per CTA and 64 bytes of K).  The two k-ranges differ by one 64-byte block; the shorter one is extended by the first
-// tile above the diagonal of its row tile, which tb200_i8_prepare writes as zero digits (Linv is lower triangular), so
-// both CTAs run the same loop and every barrier has a fixed number of arrivals: a stage is refilled once BOTH CTAs'
-// MMAs have released it (their commits arrive on both CTAs' empty barriers).
-template <int GMAX, bool MULTI, bool PAIR = false>
+template <int GMAX, bool MULTI>
 __global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p) {
     constexpr int NG = GMAX - 1;  // groups g = 2..GMAX, one 64-column INT32 accumulator each
     constexpr int SU = planes_used(GMAX);
     static_assert(NG * TN <= TMEM_COLS, "accumulators exceed TMEM");
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    __shared__ uint64_t full_bar[v::STAGES], empty_bar[v::STAGES], done_bar, tfree_bar;
+    __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], done_bar, tfree_bar;
     __shared__ uint32_t tmem_base_s;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     // heavy row tiles first (k-range grows with the row tile)
-    int rt, ct, nkb;
-    uint32_t crank = 0;
-    if constexpr (PAIR) {
-        crank = cluster_ctarank();  // = blockIdx.x & 1 (cluster dimensions 2 x 1 x 1)
-        const int idx = (int)(blockIdx.x >> 1);
-        const int rp = p.rowTiles / 2 - 1 - idx / p.candTiles;
-        rt = 2 * rp + (int)crank;
-        ct = idx % p.candTiles;
-        nkb = (2 * rp + 2) * (TN / v::KB);  // the k-range of the pair's longer row tile
-    } else {
-        rt = p.rowTiles - 1 - (int)(blockIdx.x / p.candTiles);
-        ct = blockIdx.x % p.candTiles;
-        nkb = (rt + 1) * (TN / v::KB);  // k-blocks covering columns [0, 64 (rt + 1))
-    }
+    const int rt = p.rowTiles - 1 - (int)(blockIdx.x / p.candTiles);
+    const int ct = blockIdx.x % p.candTiles;
+    const int nkb = rt + 1;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < v::STAGES; ++s) {
+        for (int s = 0; s < STAGES; ++s) {
             mbar_init(&full_bar[s], 1);
-            mbar_init(&empty_bar[s], PAIR ? 2 : 1);
+            mbar_init(&empty_bar[s], 1);
         }
         mbar_init(&done_bar, 1);
         mbar_init(&tfree_bar, TM);  // every epilogue thread arrives once it has drained its TMEM lane
@@ -307,33 +241,25 @@ __global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p)
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if constexpr (PAIR) cluster_sync_all();  // the peer's barriers exist before anything is multicast to them
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = tmem_base_s;
 
     if (warp == 0) {
         // ===== producer: 14 bulk copies per k-block, issued by one elected lane of a converged warp =====
-        const uint8_t* a_src = p.candS + ((size_t)ct * p.kblks) * v::A_TILE;
-        const uint8_t* b_src = p.linvS + ((size_t)rt * p.kblks) * v::B_TILE;
+        const uint8_t* a_src = p.candS + ((size_t)ct * p.kblks) * A_TILE;
+        const uint8_t* b_src = p.linvS + ((size_t)rt * p.kblks) * B_TILE;
         for (int kb = 0; kb < nkb; ++kb) {
-            const int s = kb % v::STAGES;
-            if (kb >= v::STAGES) mbar_wait(&empty_bar[s], ((kb / v::STAGES) - 1) & 1);
+            const int s = kb % STAGES;
+            if (kb >= STAGES) mbar_wait(&empty_bar[s], ((kb / STAGES) - 1) & 1);
             if (elect_one()) {
-                uint8_t* st = smem + (size_t)s * v::STAGE_BYTES;
-                mbar_expect_tx(&full_bar[s], SU * (v::A_TILE + v::B_TILE));
+                uint8_t* st = smem + (size_t)s * STAGE_BYTES;
+                mbar_expect_tx(&full_bar[s], SU * (A_TILE + B_TILE));
 #pragma unroll
                 for (int sl = 0; sl < SU; ++sl) {
-                    if constexpr (PAIR) {
-                        if ((uint32_t)(sl & 1) == crank)  // my half of the planes, for both CTAs
-                            bulk_g2s_multicast(st + sl * v::A_TILE,
-                                               a_src + (size_t)sl * p.candSliceStride + (size_t)kb * v::A_TILE, v::A_TILE,
-                                               &full_bar[s], (uint16_t)3);
-                    } else {
-                        bulk_g2s(st + sl * v::A_TILE, a_src + (size_t)sl * p.candSliceStride + (size_t)kb * v::A_TILE,
-                                 v::A_TILE, &full_bar[s]);
-                    }
-                    bulk_g2s(st + S * v::A_TILE + sl * v::B_TILE,
-                             b_src + (size_t)sl * p.linvSliceStride + (size_t)kb * v::B_TILE, v::B_TILE, &full_bar[s]);
+                    bulk_g2s(st + sl * A_TILE, a_src + (size_t)sl * p.candSliceStride + (size_t)kb * A_TILE, A_TILE,
+                             &full_bar[s]);
+                    bulk_g2s(st + S * A_TILE + sl * B_TILE, b_src + (size_t)sl * p.linvSliceStride + (size_t)kb * B_TILE,
+                             B_TILE, &full_bar[s]);
                 }
             }
             __syncwarp();
@@ -341,31 +267,27 @@ __global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p)
     } else if (warp == 1) {
         // ===== MMA issuer: the warp stays converged, one elected lane issues =====
         for (int kb = 0; kb < nkb; ++kb) {
-            const int s = kb % v::STAGES;
-            const bool pass_start = MULTI ? (kb % v::PASS_KB == 0) : (kb == 0);
+            const int s = kb % STAGES;
+            const bool pass_start = MULTI ? (kb % PASS_KB == 0) : (kb == 0);
             if (MULTI && pass_start && kb > 0) {
-                mbar_wait(&tfree_bar, ((kb / v::PASS_KB) - 1) & 1);  // accumulators of the previous pass drained
+                mbar_wait(&tfree_bar, ((kb / PASS_KB) - 1) & 1);  // accumulators of the previous pass drained
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             }
-            mbar_wait(&full_bar[s], (kb / v::STAGES) & 1);
+            mbar_wait(&full_bar[s], (kb / STAGES) & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint32_t a0 = smem_u32(smem + (size_t)s * v::STAGE_BYTES);
-            const uint64_t ad0 = make_desc(a0, v::SBO);
-            const uint64_t bd0 = make_desc(a0 + S * v::A_TILE, v::SBO);
+            const uint32_t a0 = smem_u32(smem + (size_t)s * STAGE_BYTES);
+            const uint64_t ad0 = make_desc(a0);
+            const uint64_t bd0 = make_desc(a0 + S * A_TILE);
             if (elect_one()) {
+                // K = 32 per MMA: the second half of the 64-byte k-block is 2 LBO further (descriptor units of 16 B)
                 if (pass_start) {
-                    issue_step<GMAX, 1, true, 0, 0, v::KB>(tmem_base, ad0, bd0);
+                    issue_step<GMAX, 1, true, 0>(tmem_base, ad0, bd0);
                 } else {
-                    issue_step<GMAX, 1, false, 0, 0, v::KB>(tmem_base, ad0, bd0);
+                    issue_step<GMAX, 1, false, 0>(tmem_base, ad0, bd0);
                 }
-                // K = 32 per MMA: the second half of a 64-byte k-block is 2 LBO further (descriptor units of 16 B)
-                if constexpr (v::KB == 64)
-                    issue_step<GMAX, 1, false, 0, 0, v::KB>(tmem_base, ad0 + (uint64_t)((2 * LBO) >> 4),
-                                                            bd0 + (uint64_t)((2 * LBO) >> 4));
-                // frees the stage once these MMAs have read it (PAIR: in both CTAs, whose producers write into it)
-                if constexpr (PAIR) umma_commit_multicast(&empty_bar[s], (uint16_t)3);
-                else umma_commit(&empty_bar[s]);
-                if (kb == nkb - 1 || (MULTI && (kb + 1) % v::PASS_KB == 0)) umma_commit(&done_bar);
+                issue_step<GMAX, 1, false, 0>(tmem_base, ad0 + (uint64_t)((2 * LBO) >> 4), bd0 + (uint64_t)((2 * LBO) >> 4));
+                umma_commit(&empty_bar[s]);  // frees the stage once these MMAs have read it
+                if (kb == nkb - 1 || (MULTI && (kb + 1) % PASS_KB == 0)) umma_commit(&done_bar);
             }
             __syncwarp();
         }
@@ -395,7 +317,7 @@ __global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p)
             }
         } else {
             double vrow[TN];  // V[candidate, 64 rows] / rowscale, summed over the passes (registers: fully unrolled)
-            const int npass = (nkb + v::PASS_KB - 1) / v::PASS_KB;
+            const int npass = (nkb + PASS_KB - 1) / PASS_KB;
             for (int pass = 0; pass < npass; ++pass) {
                 mbar_wait(&done_bar, pass & 1);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -428,78 +350,68 @@ __global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p)
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if constexpr (PAIR) cluster_sync_all();  // no CTA leaves while its peer may still signal its barriers
     if (warp == 1) {
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
     }
 }
 
-template <int GMAX, bool MULTI, bool PAIR>
+template <int GMAX, bool MULTI>
 inline int launch_colsumsq_i8_impl(const Params& p, cudaStream_t stream) {
     static DeviceOnce once;
     if (device_once(once, [] {
-            TB_CUDA(cudaFuncSetAttribute(colsumsq_i8_kernel<GMAX, MULTI, PAIR>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v::SMEM_BYTES));
+            TB_CUDA(cudaFuncSetAttribute(colsumsq_i8_kernel<GMAX, MULTI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)SMEM_BYTES));
             // same (maximum) carve-out as the small kernels that share the SMs with it: CTAs launched under different
             // shared-memory configurations cannot be resident on one SM at the same time
-            TB_CUDA(cudaFuncSetAttribute(colsumsq_i8_kernel<GMAX, MULTI, PAIR>,
-                                         cudaFuncAttributePreferredSharedMemoryCarveout,
+            TB_CUDA(cudaFuncSetAttribute(colsumsq_i8_kernel<GMAX, MULTI>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                          (int)cudaSharedmemCarveoutMaxShared));
             return 0;
         }))
         return -1;
-    if constexpr (PAIR) {
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3((unsigned)(p.rowTiles * p.candTiles));  // rowTiles is even (n is padded to 128)
-        cfg.blockDim = dim3(THREADS);
-        cfg.dynamicSmemBytes = v::SMEM_BYTES;
-        cfg.stream = stream;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = 2;
-        attr[0].val.clusterDim.y = 1;
-        attr[0].val.clusterDim.z = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
-        TB_CUDA(cudaLaunchKernelEx(&cfg, colsumsq_i8_kernel<GMAX, MULTI, PAIR>, p));
-        ++g_launches;
-    } else {
-        TB_LAUNCH((colsumsq_i8_kernel<GMAX, MULTI, PAIR>), dim3((unsigned)(p.rowTiles * p.candTiles)), dim3(THREADS),
-                  v::SMEM_BYTES, stream, p);
-    }
+    TB_LAUNCH((colsumsq_i8_kernel<GMAX, MULTI>), dim3((unsigned)(p.rowTiles * p.candTiles)), dim3(THREADS), SMEM_BYTES,
+              stream, p);
     return 0;
 }
 
 template <int GMAX>
-inline int launch_colsumsq_i8(const Params& p, cudaStream_t stream, bool pair) {
-    // the heaviest tile spans 64 * rowTiles bytes of K; one exact INT32 pass covers 8192
-    const bool multi = p.rowTiles * TN > 8192;
-    if (pair) return multi ? launch_colsumsq_i8_impl<GMAX, true, true>(p, stream)
-                           : launch_colsumsq_i8_impl<GMAX, false, true>(p, stream);
-    return multi ? launch_colsumsq_i8_impl<GMAX, true, false>(p, stream)
-                 : launch_colsumsq_i8_impl<GMAX, false, false>(p, stream);
+inline int launch_colsumsq_i8(const Params& p, cudaStream_t stream) {
+    // the heaviest tile spans rowTiles k-blocks
+    return p.rowTiles <= PASS_KB ? launch_colsumsq_i8_impl<GMAX, false>(p, stream)
+                                 : launch_colsumsq_i8_impl<GMAX, true>(p, stream);
 }
 
 // ---------------------------------------------------------------------------------------------
 // INT8 tensor peak of this device: the roofline denominator of the two kernels above, MEASURED instead of inferred from
 // the bf16 figure.  One CTA per SM; one elected lane issues tcgen05.mma kind::i8 M128 x N256 x K32 instructions on
-// operands that stay resident in shared memory (zero digits: the tensor pipe's rate does not depend on the values),
-// alternating between the two 256-column halves of TMEM.  Two mbarriers alternate so a batch is always queued behind the
+// operands that stay resident in shared memory, alternating between the two 256-column halves of TMEM.  `random`
+// fills the operands with pseudo-random digits: the instruction rate does not depend on the values, but the POWER does,
+// and on a 1 kW part the clock the power limit allows is what sets the sustained rate (zero digits ran at 1.90 GHz and
+// 4.60 POP/s in round 2; the variance kernel's step runs at 1.65-1.70 GHz).  Two mbarriers alternate so a batch is always queued behind the
 // one in flight and the pipe never drains.  No global traffic, no epilogue: nothing but the MMA rate is measured.
 // ---------------------------------------------------------------------------------------------
 constexpr int PEAK_N = 256, PEAK_BATCH = 16;
 constexpr size_t PEAK_SMEM = (size_t)(TM + PEAK_N) * KB + 1024;  // A: 128 x 64 B, B: 256 x 64 B (canonical K-major)
 
 template <int N_COLS>
-__global__ void __launch_bounds__(64, 1) i8_peak_kernel(int batches) {
+__global__ void __launch_bounds__(64, 1) i8_peak_kernel(int batches, int random) {
     static_assert(N_COLS == PEAK_N, "one instantiation (a template only so that both translation units may include it)");
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     __shared__ uint64_t bar[2];
     __shared__ uint32_t tmem_base_s;
     const int warp = threadIdx.x >> 5;
-    for (int e = threadIdx.x; e < (int)((TM + PEAK_N) * KB / 16); e += blockDim.x)
-        reinterpret_cast<uint4*>(smem)[e] = make_uint4(0u, 0u, 0u, 0u);
+    for (int e = threadIdx.x; e < (int)((TM + PEAK_N) * KB / 16); e += blockDim.x) {
+        uint32_t w[4] = {0u, 0u, 0u, 0u};
+        if (random) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {  // a 32-bit mix of (CTA, word index): every byte is a uniform digit
+                uint32_t x = (uint32_t)(e * 4 + q) * 2654435761u + blockIdx.x * 40503u + 12345u;
+                x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+                w[q] = x;
+            }
+        }
+        reinterpret_cast<uint4*>(smem)[e] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> tensor-core (async-proxy) reads
     if (threadIdx.x == 0) {
         mbar_init(&bar[0], 1);

@@ -3,7 +3,7 @@
 Every function raises if CUDA or libturbo_b200.so is unavailable; there is no CPU path.
 """
 import ctypes as C
-import os
+import math
 
 import numpy as np
 import torch
@@ -98,7 +98,9 @@ class Factor:
         self.lml = float(lml.item())
         del work
 
+        self.X_dev = X_dev  # unscaled training inputs (n, d): the probe of auto_gmax() is built from them
         self.linvS = self.rowscale = None
+        self.gmax_auto = self.gmax_probe = None
 
     def prepare_i8(self):
         """byte-slice the inverse factor for the INT8 tensor-core variance engine (once per model)"""
@@ -111,6 +113,39 @@ class Factor:
             _lib.check(lib.tb200_i8_prepare(_lib.ptr(self.Linv), self.n, C.byref(cs), _lib.ptr(self.theta),
                                             _lib.ptr(self.linvS), _lib.ptr(self.rowscale), _lib.stream_ptr()))
         return self
+
+    # slice-pair cut-off of the INT8 variance engine, chosen PER MODEL from a measurement on the model itself.
+    # 21 products (gmax 7, six digit planes) truncate every term of V = Linv k* at ~2^-46 of (row scale x sf2) instead of
+    # ~2^-54 (gmax 8).  profiles/r2_predict_precision.md: against the oracle that is 2.7-5.2 units of eps*n*prior_var at
+    # the BASELINE shapes (the parity floor is 64 of them, the same constant the oracle itself needs against the
+    # reference), EI within 3e-11, argmax identical -- and 35 units on an ill-conditioned factor (noise 1e-8).  So the
+    # cheaper cut-off is used only where THIS factor shows it is safe: 256 probe points -- 128 training points (where
+    # k** - v.v cancels completely and |v| is largest) and 128 midpoints of neighbouring training points -- are
+    # evaluated with 21 and with 34 products; gmax 7 is taken when the two variances differ by at most GMAX7_UNITS
+    # (= 1/8 of the floor), otherwise gmax 8.
+    GMAX7_UNITS = 8.0
+
+    def auto_gmax(self):
+        if self.gmax_auto is None:
+            self.prepare_i8()
+            n, d = self.n, self.spec.d
+            X = self.X_dev[:n]
+            idx = torch.linspace(0, n - 1, steps=min(n, 128), device=X.device).round().long()
+            pts = X[idx]
+            probe = torch.cat([pts, 0.5 * (pts + X[(idx + 1) % n])]).contiguous()
+            m = probe.shape[0]
+            th = self.theta.cpu().numpy()
+            prior = (math.exp(th[0]) if self.spec.has_const else 1.0) + (math.exp(th[-1]) if self.spec.has_white else 0.0)
+            var = {}
+            for eng in ("i8l", "i8x"):
+                sg = torch.empty(m, dtype=torch.float64, device=X.device)
+                a = Acquirer(self, acq_spec(_lib.ACQ_UCB, 1.0, 0.0, 0.0, 0.0, 1.0), batch=256, engine=eng)
+                a.run(probe, m, 0, None, sigma=sg)
+                var[eng] = sg * sg
+            unit = np.finfo(np.float64).eps * n * prior
+            self.gmax_probe = float((var["i8l"] - var["i8x"]).abs().max().item() / unit)
+            self.gmax_auto = 7 if self.gmax_probe <= self.GMAX7_UNITS else 8
+        return self.gmax_auto
 
     def append(self, X_new, yn_dev, n_total, jitter):
         """incremental refit at fixed theta (tb200_factor_append): append the rows of X_new (k,d) one by
@@ -140,6 +175,8 @@ class Factor:
                     self.XsT[:, r] = 0.0
                 return False
         self.n = n_total
+        self.X_dev = torch.cat([self.X_dev[:n0], xd])
+        self.gmax_auto = self.gmax_probe = None
         lml = torch.empty(1, dtype=torch.float64, device=dev)
         _lib.check(lib.tb200_alpha_lml(_lib.ptr(yn_dev), n_total, _lib.ptr(self.Linv), _lib.ptr(self.Ldiag),
                                        _lib.ptr(self.alpha), _lib.ptr(lml), _lib.ptr(work), nbytes, _lib.stream_ptr()))
@@ -158,16 +195,17 @@ I8_GMAX = {"i8l": 7, "i8": 8, "i8x": 9}  # slice-pair cut-off of the INT8 varian
 
 def resolve_engine(engine, NP):
     """'auto' -> the INT8 tensor-core engine for n <= I8_MAX_N (INT32 accumulation is exact per pass of 8192 training
-    points; longer rows take several passes).  'dmma' is the FP64 DMMA GEMM (small-n path and cross-check)."""
+    points; longer rows take several passes) with the cut-off Factor.auto_gmax() picks for the model ('i8a');
+    'i8l' / 'i8' / 'i8x' fix it at 21 / 28 / 34 products.  'dmma' is the FP64 DMMA GEMM (small-n path and cross-check)."""
     engine = (engine or "auto").lower()
     if engine == "auto":
-        engine = "i8" if NP <= _lib.I8_MAX_N else "dmma"
-    if engine in I8_GMAX:
+        engine = "i8a" if NP <= _lib.I8_MAX_N else "dmma"
+    if engine in I8_GMAX or engine == "i8a":
         if NP > _lib.I8_MAX_N:
             raise ValueError("the i8 variance engine needs n <= %d; use engine='dmma'" % _lib.I8_MAX_N)
         return engine
     if engine != "dmma":
-        raise ValueError("unknown variance engine %r (auto | dmma | i8l | i8 | i8x)" % engine)
+        raise ValueError("unknown variance engine %r (auto | dmma | i8a | i8l | i8 | i8x)" % engine)
     return engine
 
 
@@ -192,6 +230,7 @@ class Acquirer:
             self.nbytes = lib.tb200_acquire_workspace_bytes(factor.n, factor.spec.d, self.batch)
         else:
             factor.prepare_i8()
+            self.gmax = factor.auto_gmax() if self.engine == "i8a" else I8_GMAX[self.engine]
             self.nbytes = lib.tb200_acquire_i8_workspace_bytes(factor.n, factor.spec.d, self.batch)
         self.work = _workspace(self.nbytes)
         dev = device()
@@ -210,7 +249,7 @@ class Acquirer:
         if self.engine != "dmma":
             _lib.check(self.lib.tb200_acquire_i8_excl(
                 ex, _lib.ptr(Xc_dev), int(m), int(index_base), C.byref(cand_c) if cand_c is not None else None,
-                _lib.ptr(f.XsT), _lib.ptr(f.linvS), _lib.ptr(f.rowscale), I8_GMAX[self.engine],
+                _lib.ptr(f.XsT), _lib.ptr(f.linvS), _lib.ptr(f.rowscale), self.gmax,
                 _lib.ptr(f.alpha), f.n, C.byref(self.spec_c), _lib.ptr(f.theta), C.byref(self.acq_c), _lib.ptr(mu),
                 _lib.ptr(sigma), _lib.ptr(acq), _lib.ptr(self.best_val), _lib.ptr(self.best_idx), self.batch,
                 _lib.ptr(self.work), self.nbytes, _lib.stream_ptr()))
@@ -303,11 +342,12 @@ def fp64_peak(ms=50.0):
     return a.value, b.value
 
 
-def i8_peak(ms=30.0):
-    """measured INT8 tensor-core peak (TOP/s) of the current device (tb200_i8_peak)"""
+def i8_peak(ms=30.0, random_digits=True):
+    """measured INT8 tensor-core peak (TOP/s) of the current device (tb200_i8_peak): with pseudo-random digits (the
+    power the real kernels draw) or with zero operands (the ceiling at the maximum clock)"""
     _require_cuda()
     a = C.c_double()
-    _lib.check(_lib.load().tb200_i8_peak(float(ms), C.byref(a)))
+    _lib.check(_lib.load().tb200_i8_peak(float(ms), int(bool(random_digits)), C.byref(a)))
     return a.value
 
 
