@@ -162,6 +162,15 @@ int tb200_acquire_i8_excl(const tb200_exclusion* excl_host, const double* Xc, in
                           double* mu_out, double* sigma_out, double* acq_out, double* best_val, int64_t* best_idx,
                           int64_t batch, void* work, size_t work_bytes, void* stream);
 
+/* Choosing the slice cut-off per model (the host layer's variance engine 'auto'): tb200_i8_probe_points writes 2P probe
+ * points -- P training points evenly spaced through X (n x d, unscaled), where k** - v.v cancels completely, then the P
+ * midpoints between each of them and its successor -- into out (2P x d); tb200_max_sqdiff returns max |a_i^2 - b_i^2| of
+ * two standard-deviation vectors (one double; +inf if either holds a NaN).  The host evaluates the probe with gmax 7 and
+ * gmax 9 (tb200_acquire_i8 with sigma_out) and uses 21 products only when the two variances agree to 1/8 of the parity
+ * floor (8 eps n prior_var); profiles/r2_predict_precision.md. */
+int tb200_i8_probe_points(const double* X, int n, int d, int P, double* out, void* stream);
+int tb200_max_sqdiff(const double* a, const double* b, int64_t m, double* out_max, void* stream);
+
 /* write candidates [index_base, index_base+m) of a generated set into out (m x d) */
 int tb200_generate_candidates(const tb200_cand_spec* cand_host, int d, int64_t index_base, int64_t m,
                               double* out, void* stream);
@@ -175,6 +184,9 @@ int tb200_fp64_peak(double ms, double* dmma_tflops_host, double* dfma_tflops_hos
  * random_digits = 0: zero operands (the rate at the maximum clock: nothing toggles, the power limit is never reached);
  * random_digits = 1: pseudo-random digits (the rate at the clock the power limit allows for real data). */
 int tb200_i8_peak(double ms, int random_digits, double* int8_tops_host);
+/* the same loop with MMAs of N = n_cols columns (a multiple of 16, <= 256): the rate as a function of N, which decides
+ * how the kernels cut their stacked operands into instructions (csrc/ozaki_i8.cuh issue_range) */
+int tb200_i8_mma_rate(double ms, int random_digits, int n_cols, double* int8_tops_host);
 
 /* Incremental refit at fixed hyper-parameters (the reference's `training_iterations` callable returning 0,
  * turbo/modules/surrogates.py:250-269, :306-310): append ONE training point to the factor in O(n^2).

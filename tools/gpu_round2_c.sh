@@ -3,7 +3,7 @@
 # kernels): whole GPU suite, smoke, every bench configuration on one GPU, precision study incl. n=16384, ncu.
 set -u
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -q -p no:cacheprovider > gpurun_out/r2c_pytest_gpu.txt 2>&1
+python -m pytest tests -m gpu -q -rs -p no:cacheprovider > gpurun_out/r2c_pytest_gpu.txt 2>&1
 echo "pytest exit $?" >> gpurun_out/r2c_pytest_gpu.txt; tail -4 gpurun_out/r2c_pytest_gpu.txt
 cp gpurun_out/variance_error.json gpurun_out/r2c_variance_error.json 2>/dev/null
 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r2c_smoke.txt 2>&1; echo "smoke exit $?"; tail -1 gpurun_out/r2c_smoke.txt

@@ -69,9 +69,12 @@ _SIGNATURES = {
                                         _P, C.c_int, _P, C.c_int, C.POINTER(KernelSpecC), _P, C.POINTER(AcqSpecC), _P,
                                         _P, _P, _P, _P, C.c_int64, _P, C.c_size_t, _P]),
     "tb200_min_sqdist": (C.c_int, [_P, C.c_int64, _P, C.c_int, C.c_int, _P, _P, _P]),
+    "tb200_i8_probe_points": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "tb200_max_sqdiff": (C.c_int, [_P, _P, C.c_int64, _P, _P]),
     "tb200_generate_candidates": (C.c_int, [C.POINTER(CandSpecC), C.c_int, C.c_int64, C.c_int64, _P, _P]),
     "tb200_fp64_peak": (C.c_int, [C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "tb200_i8_peak": (C.c_int, [C.c_double, C.c_int, C.POINTER(C.c_double)]),
+    "tb200_i8_mma_rate": (C.c_int, [C.c_double, C.c_int, C.c_int, C.POINTER(C.c_double)]),
     "tb200_append_workspace_bytes": (C.c_size_t, [C.c_int]),
     "tb200_factor_append": (C.c_int, [_P, _P, _P, _P, C.c_int, C.POINTER(KernelSpecC), _P, C.c_double, _P, _P,
                                       C.c_size_t, _P]),

@@ -805,6 +805,39 @@ __global__ void __launch_bounds__(256) acq_grad_kernel(
     }
 }
 
+// probe of the per-model slice cut-off (tb200_i8_probe_points): P training points evenly spaced through X, then the
+// midpoints between each of them and its successor
+__global__ void probe_points_kernel(const double* __restrict__ X, int n, int d, int P, double* __restrict__ out) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= 2 * P * d) return;
+    const int q = e / d, k = e - q * d;
+    const int pnt = q < P ? q : q - P;
+    const long i0 = P > 1 ? ((long)pnt * (n - 1) + (P - 1) / 2) / (P - 1) : 0;
+    const long i1 = (i0 + 1) % n;
+    const double a = X[i0 * d + k];
+    out[e] = q < P ? a : 0.5 * (a + X[i1 * d + k]);
+}
+
+// out[0] = max_i |a_i^2 - b_i^2|  (one CTA; NaN propagates as +inf so a broken probe never selects the cheap engine)
+__global__ void __launch_bounds__(256) max_sqdiff_kernel(const double* __restrict__ a, const double* __restrict__ b,
+                                                         int64_t m, double* __restrict__ out) {
+    __shared__ double red[8];
+    double mx = 0.0;
+    for (int64_t i = threadIdx.x; i < m; i += blockDim.x) {
+        const double dv = fabs(a[i] * a[i] - b[i] * b[i]);
+        mx = (dv != dv) ? INFINITY : fmax(mx, dv);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mx;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < 8; ++w) t = fmax(t, red[w]);
+        out[0] = t;
+    }
+}
+
 __global__ void best_reset_kernel(double* best_val, int64_t* best_idx, int count) {
     for (int i = threadIdx.x; i < count; i += blockDim.x) {
         best_val[i] = -INFINITY;
@@ -1428,8 +1461,28 @@ int tb200_acquire_grad(const double* Xp, int P, const double* XsT, const double*
     return 0;
 }
 
+int tb200_i8_probe_points(const double* X, int n, int d, int P, double* out, void* stream) {
+    TB_CHECK(X && out, "NULL pointer argument");
+    TB_CHECK(n >= 1 && d >= 1 && d <= TB200_MAX_D && P >= 1 && P <= n, "tb200_i8_probe_points: 1 <= P <= n required");
+    const int total = 2 * P * d;
+    TB_LAUNCH(probe_points_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, (cudaStream_t)stream, X, n, d, P,
+              out);
+    return 0;
+}
+
+int tb200_max_sqdiff(const double* a, const double* b, int64_t m, double* out, void* stream) {
+    TB_CHECK(a && b && out && m >= 0, "NULL pointer argument");
+    TB_LAUNCH(max_sqdiff_kernel, dim3(1), dim3(256), 0, (cudaStream_t)stream, a, b, m, out);
+    return 0;
+}
+
 int tb200_i8_peak(double ms, int random_digits, double* int8_tops) {
+    return tb200_i8_mma_rate(ms, random_digits, i8::PEAK_N, int8_tops);
+}
+
+int tb200_i8_mma_rate(double ms, int random_digits, int n_cols, double* int8_tops) {
     TB_CHECK(int8_tops, "NULL pointer argument");
+    TB_CHECK(n_cols >= 16 && n_cols <= i8::PEAK_N && n_cols % 16 == 0, "n_cols: a multiple of 16 in 16..256");
     int dev = 0, sms = 0;
     TB_CUDA(cudaGetDevice(&dev));
     TB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
@@ -1447,13 +1500,13 @@ int tb200_i8_peak(double ms, int random_digits, double* int8_tops) {
     double best = 0.0;
     for (int rep = 0; rep < 6; ++rep) {
         TB_CUDA(cudaEventRecord(e0, 0));
-        TB_LAUNCH(i8::i8_peak_kernel<i8::PEAK_N>, dim3(sms), dim3(64), i8::PEAK_SMEM, 0, batches, random_digits);
+        TB_LAUNCH(i8::i8_peak_kernel<i8::PEAK_N>, dim3(sms), dim3(64), i8::PEAK_SMEM, 0, batches, random_digits, n_cols);
         TB_CUDA(cudaEventRecord(e1, 0));
         TB_CUDA(cudaEventSynchronize(e1));
         float t = 0.f;
         TB_CUDA(cudaEventElapsedTime(&t, e0, e1));
-        // one MMA = M128 x N256 x K32 multiply-accumulates, 2 operations each
-        const double ops = 2.0 * i8::TM * i8::PEAK_N * 32.0 * i8::PEAK_BATCH * (double)batches * sms;
+        // one MMA = M128 x N x K32 multiply-accumulates, 2 operations each
+        const double ops = 2.0 * i8::TM * n_cols * 32.0 * i8::PEAK_BATCH * (double)batches * sms;
         const double tops = ops / (t * 1e-3) / 1e12;
         if (rep > 0 && tops > best) best = tops;
         if (t < ms) batches = (int)(batches * (ms / (t > 1e-3 ? t : 1e-3)) * 1.1) + 2;

@@ -154,15 +154,26 @@ __device__ __forceinline__ bool elect_one() {
 
 // MMAs of one candidate-slice tile (descriptor `ad`) against rows [N_LO, N_HI) of the stacked Linv slices (descriptor
 // of row 0 = `bd0`; 8 rows further = +SBO bytes = +SBO/16 in the descriptor's address field) -> TMEM columns
-// d_tmem + [N_LO, N_HI).  Balanced chunks of <= 256 columns (multiples of 16), all resolved at compile time so the
-// issuing lane executes a handful of uniform-register adds per MMA.
+// d_tmem + [N_LO, N_HI).  All resolved at compile time so the issuing lane executes a handful of uniform-register adds
+// per MMA.  Chunking: an M128 kind::i8 MMA costs ceil(N / 128) x 64 cycles, NOT N / 2 (tb200_i8_mma_rate,
+// profiles/r2_i8_mma_rate.md: N = 160, 192, 224 take as long as N = 256, N = 64 as long as 128), so a range is cut into
+// chunks of 256 columns plus ONE remainder.  Round 1 cut it into equal chunks (448 -> 224 + 224, 384 -> 192 + 192,
+// 320 -> 160 + 160), each of which was billed as 256: 2304 cycles per 64 bytes of K where this order pays 2048 (28
+// products), 1792 -> 1536 (21 products) -- the whole gap between the measured 2336 cycles and the 1792 "of MMAs".
+#ifndef TB200_CHUNK_BALANCED
+#define TB200_CHUNK_BALANCED 0
+#endif
 template <int N_LO, int N_HI, int ACC, int ASGN = 0>
 __device__ __forceinline__ void issue_range(uint32_t d_tmem, uint64_t ad, uint64_t bd0) {
     if constexpr (N_HI > N_LO) {
         constexpr int width = N_HI - N_LO;
+#if TB200_CHUNK_BALANCED
         constexpr int nchunks = (width + 255) / 256;
         constexpr int chunk = ((width / nchunks) + 15) & ~15;
         constexpr int nc = chunk < width ? chunk : width;
+#else
+        constexpr int nc = width > 256 ? 256 : width;
+#endif
         umma_i8(d_tmem + N_LO, ad, bd0 + (uint64_t)((N_LO >> 3) * (SBO >> 4)), idesc(nc, ASGN), (uint32_t)ACC);
         issue_range<N_LO + nc, N_HI, ACC, ASGN>(d_tmem, ad, bd0);
     }
@@ -393,7 +404,7 @@ constexpr int PEAK_N = 256, PEAK_BATCH = 16;
 constexpr size_t PEAK_SMEM = (size_t)(TM + PEAK_N) * KB + 1024;  // A: 128 x 64 B, B: 256 x 64 B (canonical K-major)
 
 template <int N_COLS>
-__global__ void __launch_bounds__(64, 1) i8_peak_kernel(int batches, int random) {
+__global__ void __launch_bounds__(64, 1) i8_peak_kernel(int batches, int random, int n_cols) {
     static_assert(N_COLS == PEAK_N, "one instantiation (a template only so that both translation units may include it)");
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -437,7 +448,7 @@ __global__ void __launch_bounds__(64, 1) i8_peak_kernel(int batches, int random)
 #pragma unroll
                 for (int i = 0; i < PEAK_BATCH; ++i)
                     umma_i8(tmem_base + (uint32_t)((i & 1) * PEAK_N), ad + (uint64_t)((i & 1) * ((2 * LBO) >> 4)),
-                            bd + (uint64_t)((i & 1) * ((2 * LBO) >> 4)), idesc(PEAK_N), (b > 0 || i > 1) ? 1u : 0u);
+                            bd + (uint64_t)((i & 1) * ((2 * LBO) >> 4)), idesc(n_cols), (b > 0 || i > 1) ? 1u : 0u);
                 umma_commit(&bar[b & 1]);
             }
             __syncwarp();

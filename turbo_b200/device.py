@@ -128,22 +128,23 @@ class Factor:
     def auto_gmax(self):
         if self.gmax_auto is None:
             self.prepare_i8()
+            lib, dev = _lib.load(), self.X_dev.device
             n, d = self.n, self.spec.d
-            X = self.X_dev[:n]
-            idx = torch.linspace(0, n - 1, steps=min(n, 128), device=X.device).round().long()
-            pts = X[idx]
-            probe = torch.cat([pts, 0.5 * (pts + X[(idx + 1) % n])]).contiguous()
-            m = probe.shape[0]
+            P = min(n, 128)
+            probe = torch.empty((2 * P, d), dtype=torch.float64, device=dev)
+            _lib.check(lib.tb200_i8_probe_points(_lib.ptr(self.X_dev), n, d, P, _lib.ptr(probe), _lib.stream_ptr()))
             th = self.theta.cpu().numpy()
             prior = (math.exp(th[0]) if self.spec.has_const else 1.0) + (math.exp(th[-1]) if self.spec.has_white else 0.0)
-            var = {}
+            sg = {}
             for eng in ("i8l", "i8x"):
-                sg = torch.empty(m, dtype=torch.float64, device=X.device)
+                sg[eng] = torch.empty(2 * P, dtype=torch.float64, device=dev)
                 a = Acquirer(self, acq_spec(_lib.ACQ_UCB, 1.0, 0.0, 0.0, 0.0, 1.0), batch=256, engine=eng)
-                a.run(probe, m, 0, None, sigma=sg)
-                var[eng] = sg * sg
+                a.run(probe, 2 * P, 0, None, sigma=sg[eng])
+            worst = torch.empty(1, dtype=torch.float64, device=dev)
+            _lib.check(lib.tb200_max_sqdiff(_lib.ptr(sg["i8l"]), _lib.ptr(sg["i8x"]), 2 * P, _lib.ptr(worst),
+                                            _lib.stream_ptr()))
             unit = np.finfo(np.float64).eps * n * prior
-            self.gmax_probe = float((var["i8l"] - var["i8x"]).abs().max().item() / unit)
+            self.gmax_probe = float(worst.item()) / unit
             self.gmax_auto = 7 if self.gmax_probe <= self.GMAX7_UNITS else 8
         return self.gmax_auto
 
