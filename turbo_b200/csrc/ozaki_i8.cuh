@@ -155,25 +155,18 @@ __device__ __forceinline__ bool elect_one() {
 // MMAs of one candidate-slice tile (descriptor `ad`) against rows [N_LO, N_HI) of the stacked Linv slices (descriptor
 // of row 0 = `bd0`; 8 rows further = +SBO bytes = +SBO/16 in the descriptor's address field) -> TMEM columns
 // d_tmem + [N_LO, N_HI).  All resolved at compile time so the issuing lane executes a handful of uniform-register adds
-// per MMA.  Chunking: an M128 kind::i8 MMA costs ceil(N / 128) x 64 cycles, NOT N / 2 (tb200_i8_mma_rate,
-// profiles/r2_i8_mma_rate.md: N = 160, 192, 224 take as long as N = 256, N = 64 as long as 128), so a range is cut into
-// chunks of 256 columns plus ONE remainder.  Round 1 cut it into equal chunks (448 -> 224 + 224, 384 -> 192 + 192,
-// 320 -> 160 + 160), each of which was billed as 256: 2304 cycles per 64 bytes of K where this order pays 2048 (28
-// products), 1792 -> 1536 (21 products) -- the whole gap between the measured 2336 cycles and the 1792 "of MMAs".
-#ifndef TB200_CHUNK_BALANCED
-#define TB200_CHUNK_BALANCED 0
-#endif
+// per MMA.  Chunking: BALANCED chunks of <= 256 columns (multiples of 16).  Measured cost of one M128 x N x K32 kind::i8
+// MMA (tb200_i8_mma_rate, profiles/r2_i8_mma_rate.md): ~N/2 cycles from N = 128 up (72 / 84 / 98 / 114 / 129 cycles at
+// N = 128 / 160 / 192 / 224 / 256) over a floor of ~50 cycles per instruction (58 at N = 64), so 384 columns are
+// cheaper as 192 + 192 (196 cycles) than as 256 + 128 (201), 320 as 160 + 160 (168) than as 256 + 64 (187): an A/B of
+// the two orders on the variance kernel gave 0.2541 vs 0.2555 ms (profiles/r2_ab_chunking.md).
 template <int N_LO, int N_HI, int ACC, int ASGN = 0>
 __device__ __forceinline__ void issue_range(uint32_t d_tmem, uint64_t ad, uint64_t bd0) {
     if constexpr (N_HI > N_LO) {
         constexpr int width = N_HI - N_LO;
-#if TB200_CHUNK_BALANCED
         constexpr int nchunks = (width + 255) / 256;
         constexpr int chunk = ((width / nchunks) + 15) & ~15;
         constexpr int nc = chunk < width ? chunk : width;
-#else
-        constexpr int nc = width > 256 ? 256 : width;
-#endif
         umma_i8(d_tmem + N_LO, ad, bd0 + (uint64_t)((N_LO >> 3) * (SBO >> 4)), idesc(nc, ASGN), (uint32_t)ACC);
         issue_range<N_LO + nc, N_HI, ACC, ASGN>(d_tmem, ad, bd0);
     }
