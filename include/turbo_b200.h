@@ -187,6 +187,12 @@ int tb200_i8_peak(double ms, int random_digits, double* int8_tops_host);
 /* the same loop with MMAs of N = n_cols columns (a multiple of 16, <= 256): the rate as a function of N, which decides
  * how the kernels cut their stacked operands into instructions (csrc/ozaki_i8.cuh issue_range) */
 int tb200_i8_mma_rate(double ms, int random_digits, int n_cols, double* int8_tops_host);
+/* diagnostic: SM cycles per k-block (two K = 32 steps) of one of the compile-time MMA lists of csrc/ozaki_i8.cuh
+ * (MmaList<variant>: the variance kernel's own instruction list and re-ordered / re-chunked / re-aligned variants of
+ * it) issued back to back on resident shared-memory operands.  Separates what the instruction mix costs on the tensor
+ * pipe from what loads and the epilogue cost (tools/i8_mma_list.py). */
+int tb200_i8_mma_list(int variant, int kblocks, double* cycles_per_kblock_host, int* mmas_per_step_host,
+                      int* columns_per_step_host);
 
 /* Incremental refit at fixed hyper-parameters (the reference's `training_iterations` callable returning 0,
  * turbo/modules/surrogates.py:250-269, :306-310): append ONE training point to the factor in O(n^2).

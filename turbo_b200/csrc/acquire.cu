@@ -915,6 +915,7 @@ struct AcqBuffers {
     double* best_val; // [1] running best of this slot
     int64_t* best_idx;
     double* mind;     // [batch]      smallest squared distance to an excluded point (tb200_exclusion)
+    unsigned* sched;  // [2]          tile / finished-CTA counters of the persistent variance kernel (shared by the slots)
 };
 
 static size_t a256(size_t b) { return (b + 255) / 256 * 256; }
@@ -951,8 +952,13 @@ static size_t acquire_layout(int n, int d, int64_t batch, AcqBuffers* ab, char* 
     const size_t nb = (size_t)(batch / EPI_THREADS);
     double* bv = take(sizeof(double) * ACQ_SLOTS * nb);
     int64_t* bi = reinterpret_cast<int64_t*>(take(sizeof(int64_t) * ACQ_SLOTS * nb));
+    unsigned* sched = reinterpret_cast<unsigned*>(take(256));
     if (ab)
-        for (int s = 0; s < ACQ_SLOTS; ++s) { ab[s].best_val = bv + s * nb; ab[s].best_idx = bi + s * nb; }
+        for (int s = 0; s < ACQ_SLOTS; ++s) {
+            ab[s].best_val = bv + s * nb;
+            ab[s].best_idx = bi + s * nb;
+            ab[s].sched = sched;
+        }
     return off;
 }
 
@@ -1044,6 +1050,19 @@ static int configure_carveout_device() {
     return 0;
 }
 static int configure_carveout() { return device_once(g_carveout_once, configure_carveout_device); }
+
+template <int V>
+static int run_mma_list(int kblocks, int sms, long long* d_cyc) {
+    static DeviceOnce once;
+    if (device_once(once, [] {
+            TB_CUDA(cudaFuncSetAttribute(i8::i8_mma_list_kernel<V>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)(i8::STAGE_BYTES + 1024)));
+            return 0;
+        }))
+        return -1;
+    TB_LAUNCH(i8::i8_mma_list_kernel<V>, dim3(sms), dim3(64), i8::STAGE_BYTES + 1024, 0, kblocks, d_cyc);
+    return 0;
+}
 
 }  // namespace tb200
 
@@ -1142,6 +1161,8 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
     }
     TB_LAUNCH(best_reset_kernel, dim3(1), dim3(64), 0, s_small, ab[0].best_val, ab[0].best_idx,
               (int)(ACQ_SLOTS * (batch / EPI_THREADS)));
+    // the persistent variance kernel leaves its counters zeroed for the next launch; the workspace is the caller's
+    if (use_i8) TB_CUDA(cudaMemsetAsync(ab[0].sched, 0, 2 * sizeof(unsigned), s_var));
 
     const size_t ksm = sizeof(double) * (CPB * d + 8 * CPB);
     // split the training points so one K* launch is ~2k CTAs (3 resident per SM): NB/ksplit tiles each
@@ -1253,9 +1274,10 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
             ip.kblks = NP / i8::KB;
             ip.rowTiles = NP / i8::TN;
             ip.candTiles = (int)(q.mbp / i8::TM);
-            const int rc = f8.gmax == 7   ? i8::launch_colsumsq_i8<7>(ip, s_var)
-                           : f8.gmax == 8 ? i8::launch_colsumsq_i8<8>(ip, s_var)
-                                          : i8::launch_colsumsq_i8<9>(ip, s_var);
+            ip.sched = w.sched;
+            const int rc = f8.gmax == 7   ? i8::launch_colsumsq_i8<7>(ip, g_sm_count, s_var)
+                           : f8.gmax == 8 ? i8::launch_colsumsq_i8<8>(ip, g_sm_count, s_var)
+                                          : i8::launch_colsumsq_i8<9>(ip, g_sm_count, s_var);
             if (rc) return -1;
         } else {
             GemmParams gp = gemm_params(Linv, NP, w.Ks, NP, w.partial, batch, NB, (int)(q.mbp / 128), NP, 1.0, 0.0);
@@ -1515,6 +1537,47 @@ int tb200_i8_mma_rate(double ms, int random_digits, int n_cols, double* int8_top
     cudaEventDestroy(e1);
     *int8_tops = best;
     return 0;
+}
+
+int tb200_i8_mma_list(int variant, int kblocks, double* cycles_per_kblock, int* mmas_per_step, int* columns_per_step) {
+    TB_CHECK(cycles_per_kblock && mmas_per_step && columns_per_step, "NULL pointer argument");
+    TB_CHECK(variant >= 0 && variant < i8::MMA_LIST_VARIANTS && kblocks >= 4, "tb200_i8_mma_list: variant 0..11, >= 4 k-blocks");
+    int dev = 0, sms = 0;
+    TB_CUDA(cudaGetDevice(&dev));
+    TB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    long long* d_cyc = nullptr;
+    TB_CUDA(cudaMalloc(&d_cyc, sizeof(long long) * sms));
+    double best = 0.0;
+    int rc = 0;
+    for (int rep = 0; rep < 3 && rc == 0; ++rep) {
+        int n = 0, cols = 0;
+#define TB_RUN(V)                                                                \
+    case V:                                                                      \
+        rc = run_mma_list<V>(kblocks, sms, d_cyc);                               \
+        n = i8::MmaList<V>::n;                                                   \
+        for (int i = 0; i < n; ++i) cols += i8::MmaList<V>::ops[i].n;            \
+        break
+        switch (variant) {
+            TB_RUN(0); TB_RUN(1); TB_RUN(2); TB_RUN(3); TB_RUN(4); TB_RUN(5);
+            TB_RUN(6); TB_RUN(7); TB_RUN(8); TB_RUN(9); TB_RUN(10); TB_RUN(11);
+        }
+#undef TB_RUN
+        if (rc) break;
+        *mmas_per_step = n;
+        *columns_per_step = cols;
+        std::vector<long long> h(sms);
+        if (cudaMemcpy(h.data(), d_cyc, sizeof(long long) * sms, cudaMemcpyDeviceToHost) != cudaSuccess) {
+            rc = fail(cudaGetErrorString(cudaGetLastError()), __FILE__, __LINE__);
+            break;
+        }
+        double sum = 0.0;
+        for (int i = 0; i < sms; ++i) sum += (double)h[i];
+        const double per = sum / sms / (double)(kblocks - 2);
+        if (rep == 0 || per < best) best = per;
+    }
+    cudaFree(d_cyc);
+    *cycles_per_kblock = best;
+    return rc;
 }
 
 int tb200_shutdown(void) {

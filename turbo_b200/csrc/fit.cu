@@ -795,6 +795,7 @@ struct FitBuffers {
     unsigned long long* smax;  // [R][NP] column maxima of the weighted L panels
     double* sigma;   // [R][NP] power-of-two scales of the weighted L panels
     uint8_t* bpanel; // [R][7][2][NP/64][4096] byte slices of one weighted L panel (B operand of the trtri step)
+    mutable i8::SchedPool sched;  // scheduler counters of the persistent INT8 GEMM launches (zeroed per fit call)
 };
 
 // slice products kept by the fit GEMMs, per stage: 9 (34 products, truncation 2^-64: below FP64 rounding), 8 (28
@@ -805,11 +806,24 @@ struct FitBuffers {
 // fit_gmax_kinv one stage (common.cuh).
 enum FitStage { FIT_POTRF = 0, FIT_TRTRI = 1, FIT_KINV = 2 };
 static int fit_gmax(int stage) { return debug_config().fit_gmax[stage]; }
-static int launch_fit_gemm_i8(const i8::GemmI8Params& g, int ntiles, int R, cudaStream_t st, int stage) {
+static int fit_sm_count() {  // CTAs of a persistent grid: one per SM of the current device
+    static int sms[MAX_DEVICES] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEVICES) return 0;
+    if (sms[dev] == 0) {
+        int v = 0;
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+        sms[dev] = v;  // racing threads write the same value
+    }
+    return sms[dev];
+}
+static int launch_fit_gemm_i8(const FitBuffers& fb, const i8::GemmI8Params& g, int ntiles, int R, cudaStream_t st,
+                              int stage) {
+    const int sms = fit_sm_count();
     switch (fit_gmax(stage)) {
-        case 7: return i8::launch_gemm_i8<7>(g, ntiles, R, st);
-        case 8: return i8::launch_gemm_i8<8>(g, ntiles, R, st);
-        default: return i8::launch_gemm_i8<9>(g, ntiles, R, st);
+        case 7: return i8::launch_gemm_i8<7>(g, ntiles, R, fb.sched, sms, st);
+        case 8: return i8::launch_gemm_i8<8>(g, ntiles, R, fb.sched, sms, st);
+        default: return i8::launch_gemm_i8<9>(g, ntiles, R, fb.sched, sms, st);
     }
 }
 
@@ -858,13 +872,16 @@ size_t fit_workspace_layout(int n, int d, int R, int p, bool own_linv, bool own_
         scale = take(sizeof(double) * R * NP);
     }
     unsigned long long* tmax = nullptr; unsigned long long* smax = nullptr; double* sigma = nullptr; uint8_t* bpanel = nullptr;
+    unsigned* sched = nullptr;
     if (i8fit) {
         tmax = reinterpret_cast<unsigned long long*>(take(sizeof(double) * R * NP));
         smax = reinterpret_cast<unsigned long long*>(take(sizeof(double) * R * NP));
         sigma = take(sizeof(double) * R * NP);
         bpanel = reinterpret_cast<uint8_t*>(take((size_t)i8::S * R * 2 * (NP / i8::KB) * i8::B_TILE));
+        sched = reinterpret_cast<unsigned*>(take(sizeof(unsigned) * 2 * i8::SCHED_POOL));
     }
     if (fb) {
+        fb->sched.base = sched; fb->sched.next = 0;
         fb->sliced = sliced; fb->scale = scale; fb->tmax = tmax; fb->smax = smax; fb->sigma = sigma; fb->bpanel = bpanel;
         fb->K = K; fb->Linv = Linv; fb->Dinv = Dinv; fb->XsT = XsT; fb->ypad = ypad; fb->z = z;
         fb->alpha = alpha; fb->logdet = logdet; fb->partial = partial;
@@ -970,7 +987,7 @@ static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStr
                 g.kblks = NP / i8::KB; g.tri = 0;
                 g.rowTile0 = k + 1; g.colTile0 = 2 * k; g.nColTiles = 2; g.kbLo = 0; g.kbHi = 2 * k;
                 g.alpha = -1.0; g.beta = 1.0;
-                if (launch_fit_gemm_i8(g, (NB - k - 1) * 2, R, st, FIT_POTRF)) return -1;
+                if (launch_fit_gemm_i8(fb, g, (NB - k - 1) * 2, R, st, FIT_POTRF)) return -1;
             }
             TB_CUDA(cudaStreamWaitEvent(st, rl->join, 0));
             diag_done = true;
@@ -989,15 +1006,15 @@ static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStr
             if (NB - k > 1 && !fit_streams_for_device(&fs)) {
                 TB_CUDA(cudaEventRecord(fs->fork, st));
                 TB_CUDA(cudaStreamWaitEvent(fs->side, fs->fork, 0));
-                if (launch_fit_gemm_i8(g, 2, R, fs->side, FIT_POTRF)) return -1;           // diagonal tile (it = k)
+                if (launch_fit_gemm_i8(fb, g, 2, R, fs->side, FIT_POTRF)) return -1;           // diagonal tile (it = k)
                 if (launch_diag(fb, NP, R, k, info, fs->side)) return -1;
                 TB_CUDA(cudaEventRecord(fs->join, fs->side));
                 g.rowTile0 = k + 1;
-                if (launch_fit_gemm_i8(g, (NB - k - 1) * 2, R, st, FIT_POTRF)) return -1;  // rows below
+                if (launch_fit_gemm_i8(fb, g, (NB - k - 1) * 2, R, st, FIT_POTRF)) return -1;  // rows below
                 TB_CUDA(cudaStreamWaitEvent(st, fs->join, 0));
                 diag_done = true;
             } else {
-                if (launch_fit_gemm_i8(g, (NB - k) * 2, R, st, FIT_POTRF)) return -1;
+                if (launch_fit_gemm_i8(fb, g, (NB - k) * 2, R, st, FIT_POTRF)) return -1;
             }
         } else if (left && k > 0) {
             // block column k: A[i,k] -= L[i,0:k] L[k,0:k]^T  (i >= k), K = k*128 accumulated in registers
@@ -1040,7 +1057,7 @@ static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStr
             g.kblks = NP / i8::KB; g.tri = 0;
             g.rowTile0 = k + 2; g.colTile0 = 2 * (k + 2); g.nColTiles = 2; g.kbLo = 0; g.kbHi = 2 * (k + 1);
             g.alpha = -1.0; g.beta = 1.0;
-            if (launch_fit_gemm_i8(g, 2, R, rl->look, FIT_POTRF)) return -1;
+            if (launch_fit_gemm_i8(fb, g, 2, R, rl->look, FIT_POTRF)) return -1;
             TB_CUDA(cudaEventRecord(rl->look_done, rl->look));
         }
         if (!left) {
@@ -1129,7 +1146,7 @@ static int trtri_batched_i8(const FitBuffers& fb, double* Linv, int NP, int R, c
             g.kblks = kblks; g.tri = 0;
             g.rowTile0 = c1; g.colTile0 = 2 * c; g.nColTiles = 2; g.kbLo = 2 * c1; g.kbHi = kblks; g.kbHiByRow = 1;
             g.alpha = -1.0; g.beta = 0.0;
-            if (launch_fit_gemm_i8(g, rem * 2, R, st, FIT_TRTRI)) return -1;
+            if (launch_fit_gemm_i8(fb, g, rem * 2, R, st, FIT_TRTRI)) return -1;
         }
         // X[i, c-block] = T[i, c-block] * Dinv_c  (in place, 128-deep DMMA GEMM)
         {
@@ -1204,6 +1221,7 @@ static int fit_pipeline(const double* X, const double* y_n, int n, const tb200_k
     const int NP = pad_n(n), d = spec.d, p = spec_p(spec);
     const int nt64 = (NP / GT) * (NP / GT + 1) / 2;
     TB_CUDA(cudaMemsetAsync(info, 0, sizeof(int) * R, st));
+    if (fb.sched.base) TB_CUDA(cudaMemsetAsync(fb.sched.base, 0, sizeof(unsigned) * 2 * i8::SCHED_POOL, st));
     TB_LAUNCH(pad_vector_kernel, dim3((NP + 255) / 256), dim3(256), 0, st, y_n, n, NP, fb.ypad);
     TB_LAUNCH(scale_points_kernel, dim3((NP + 255) / 256, R), dim3(256), 0, st, X, n, NP, spec, theta, p, XsT);
     const size_t gsm = sizeof(double) * 2 * d * GT;
@@ -1245,7 +1263,7 @@ static int fit_pipeline(const double* X, const double* y_n, int n, const tb200_k
             g.C = fb.K; g.ldc = NP; g.cStride = sK;
             g.kblks = NP / i8::KB; g.tri = 1;
             g.alpha = 1.0; g.beta = 0.0;
-            if (launch_fit_gemm_i8(g, NB * (NB + 1), R, st, FIT_KINV)) return -1;
+            if (launch_fit_gemm_i8(fb, g, NB * (NB + 1), R, st, FIT_KINV)) return -1;
         } else {
             GemmParams q = gemm_params(Linv, NP, Linv, NP, fb.K, NP, NP / TILE, NP / TILE, NP, 1.0, 0.0);
             q.order = ORDER_LOWER;

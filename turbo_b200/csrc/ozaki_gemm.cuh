@@ -35,41 +35,63 @@ struct GemmI8Params {
     // a window that does not contain the start of the CTA's range accumulates onto C (beta = 1) instead of applying
     // the caller's beta.  kbWinHi = 0: no window.
     int kbWinLo, kbWinHi;
+    int ntiles, R;         // tiles per restart and restarts (filled by launch_gemm_i8)
+    unsigned* sched;       // [2] tile counter + finished-CTA counter of this launch (zero at launch, left zero)
 };
 
+// tile t of a launch (restart-major; inside a restart the tiles with the longest k-range come first, so the dynamic
+// scheduler ends a launch on its cheapest tiles) -> restart, row tile, column tile, k-range and beta
+struct GemmTile {
+    int rs, it, jt, kb_lo, nkb;
+    double beta;
+};
+__device__ __forceinline__ GemmTile gemm_tile(const GemmI8Params& p, int t) {
+    GemmTile g;
+    g.rs = t / p.ntiles;
+    int bx = t - g.rs * p.ntiles, kb_hi;
+    if (p.tri) {
+        // heavy tiles first: the k-range [2*it, kblks) shrinks with it
+        g.it = 0;
+        while (bx >= 2 * g.it + 2) { bx -= 2 * g.it + 2; ++g.it; }
+        g.jt = bx;
+        g.kb_lo = 2 * g.it;
+        kb_hi = p.kblks;
+    } else {
+        int r = bx / p.nColTiles;
+        // a k-range that grows with the row (trtri): last rows first
+        if (p.kbHiByRow) r = p.ntiles / p.nColTiles - 1 - r;
+        g.it = p.rowTile0 + r;
+        g.jt = p.colTile0 + bx % p.nColTiles;
+        g.kb_lo = p.kbLo;
+        kb_hi = p.kbHiByRow ? 2 * (g.it + 1) : p.kbHi;
+    }
+    g.beta = p.beta;
+    if (p.kbWinHi > 0) {
+        if (g.kb_lo < p.kbWinLo) { g.kb_lo = p.kbWinLo; g.beta = 1.0; }
+        if (kb_hi > p.kbWinHi) kb_hi = p.kbWinHi;
+    }
+    g.nkb = kb_hi - g.kb_lo;
+    return g;
+}
+
+// PERSISTENT (round 2), same pipeline as colsumsq_i8_kernel: at most one CTA per SM takes tiles from a global counter;
+// the producer warp runs on into the next tile's loads while the MMAs of the current one are still queued, TMEM and the
+// barriers are set up once per CTA, and the epilogue hands TMEM back as soon as its last tcgen05.ld has landed.  Round
+// 1 launched one CTA per tile and paid ~15 k cycles of set-up, first-load latency and epilogue per tile -- as much as
+// the MMAs of a 10-k-block tile, which is what the block columns at both ends of potrf / trtri consist of.
+// Tiles whose k-range misses the launch's window are skipped by the producer and never enter the pipeline.
 template <int GMAX>
 __global__ void __launch_bounds__(THREADS, 1) gemm_i8_kernel(const GemmI8Params p) {
     constexpr int NG = GMAX - 1;
     static_assert(NG * TN <= TMEM_COLS, "accumulators exceed TMEM");
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], done_bar;
+    __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], done_bar, tfree_bar;
     __shared__ uint32_t tmem_base_s;
+    __shared__ volatile int tile_ring[RING];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    int it, jt, kb_lo, kb_hi;
-    if (p.tri) {
-        // heavy tiles first: the k-range [2*it, kblks) shrinks with it
-        it = 0;
-        int rem = (int)blockIdx.x;
-        while (rem >= 2 * it + 2) { rem -= 2 * it + 2; ++it; }
-        jt = rem;
-        kb_lo = 2 * it;
-        kb_hi = p.kblks;
-    } else {
-        it = p.rowTile0 + (int)blockIdx.x / p.nColTiles;
-        jt = p.colTile0 + (int)blockIdx.x % p.nColTiles;
-        kb_lo = p.kbLo;
-        kb_hi = p.kbHiByRow ? 2 * (it + 1) : p.kbHi;
-    }
-    double beta = p.beta;
-    if (p.kbWinHi > 0) {
-        if (kb_lo < p.kbWinLo) { kb_lo = p.kbWinLo; beta = 1.0; }
-        if (kb_hi > p.kbWinHi) kb_hi = p.kbWinHi;
-    }
-    const int nkb = kb_hi - kb_lo;
-    if (nkb <= 0) return;  // uniform over the CTA, before any barrier or TMEM allocation
-    const int rs = (int)blockIdx.y;  // restart
+    const int total = p.ntiles * p.R;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; ++s) {
@@ -77,6 +99,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_i8_kernel(const GemmI8Params 
             mbar_init(&empty_bar[s], 1);
         }
         mbar_init(&done_bar, 1);
+        mbar_init(&tfree_bar, TM);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -92,88 +115,137 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_i8_kernel(const GemmI8Params 
 
     if (warp == 0) {
         // ===== producer: per slice two 4 KB copies for the 128 A rows and one for the 64 B rows =====
-        const uint8_t* base = p.S + (size_t)rs * p.restartStride;
-        const uint8_t* a0_src = base + ((size_t)(2 * it) * p.kblks) * B_TILE;
-        const uint8_t* a1_src = base + ((size_t)(2 * it + 1) * p.kblks) * B_TILE;
-        const uint8_t* b_src = p.SB ? p.SB + (size_t)rs * p.restartStrideB + ((size_t)(jt - p.colTile0) * p.kblks) * B_TILE
-                                    : base + ((size_t)jt * p.kblks) * B_TILE;
-        const long b_slice = p.SB ? p.sliceStrideB : p.sliceStride;
-        for (int i = 0; i < nkb; ++i) {
-            const int s = i % STAGES;
-            const size_t kb = (size_t)(kb_lo + i);
-            if (i >= STAGES) mbar_wait(&empty_bar[s], ((i / STAGES) - 1) & 1);
-            if (elect_one()) {
-                uint8_t* st = smem + (size_t)s * STAGE_BYTES;
-                mbar_expect_tx(&full_bar[s], STAGE_BYTES);
-#pragma unroll
-                for (int sl = 0; sl < S; ++sl) {
-                    const size_t so = (size_t)sl * p.sliceStride + kb * B_TILE;
-                    bulk_g2s(st + sl * A_TILE, a0_src + so, B_TILE, &full_bar[s]);
-                    bulk_g2s(st + sl * A_TILE + B_TILE, a1_src + so, B_TILE, &full_bar[s]);
-                    bulk_g2s(st + S * A_TILE + sl * B_TILE, b_src + (size_t)sl * b_slice + kb * B_TILE, B_TILE,
-                             &full_bar[s]);
-                }
+        uint32_t it = 0, ti = 0;  // k-blocks issued, tiles published
+        for (;;) {
+            int t = 0;
+            if (lane == 0) t = (int)atomicAdd(p.sched, 1u);
+            t = __shfl_sync(0xffffffffu, t, 0);
+            const bool last = t >= total;
+            GemmTile g{};
+            if (!last) {
+                g = gemm_tile(p, t);
+                if (g.nkb <= 0) continue;  // outside this launch's k-window
             }
-            __syncwarp();
+            const int nkb = last ? 1 : g.nkb;
+            const uint8_t* base = p.S + (size_t)g.rs * p.restartStride;
+            const uint8_t* a0_src = base + ((size_t)(2 * g.it) * p.kblks) * B_TILE;
+            const uint8_t* a1_src = base + ((size_t)(2 * g.it + 1) * p.kblks) * B_TILE;
+            const uint8_t* b_src =
+                p.SB ? p.SB + (size_t)g.rs * p.restartStrideB + ((size_t)(g.jt - p.colTile0) * p.kblks) * B_TILE
+                     : base + ((size_t)g.jt * p.kblks) * B_TILE;
+            const long b_slice = p.SB ? p.sliceStrideB : p.sliceStride;
+            for (int i = 0; i < nkb; ++i, ++it) {
+                const int s = it % STAGES;
+                const size_t kb = (size_t)(g.kb_lo + i);
+                if (it >= STAGES) mbar_wait(&empty_bar[s], ((it / STAGES) - 1) & 1);
+                if (elect_one()) {
+                    if (i == 0) tile_ring[ti % RING] = last ? -1 : t;
+                    if (last) {
+                        mbar_arrive(&full_bar[s]);
+                    } else {
+                        uint8_t* st = smem + (size_t)s * STAGE_BYTES;
+                        mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+#pragma unroll
+                        for (int sl = 0; sl < S; ++sl) {
+                            const size_t so = (size_t)sl * p.sliceStride + kb * B_TILE;
+                            bulk_g2s(st + sl * A_TILE, a0_src + so, B_TILE, &full_bar[s]);
+                            bulk_g2s(st + sl * A_TILE + B_TILE, a1_src + so, B_TILE, &full_bar[s]);
+                            bulk_g2s(st + S * A_TILE + sl * B_TILE, b_src + (size_t)sl * b_slice + kb * B_TILE, B_TILE,
+                                     &full_bar[s]);
+                        }
+                    }
+                }
+                __syncwarp();
+            }
+            ++ti;
+            if (last) break;
+        }
+        if (lane == 0) {
+            // every CTA has taken its end marker once the last one arrives here: leave the pair zeroed for its next user
+            if (atomicAdd(p.sched + 1, 1u) == gridDim.x - 1) {
+                atomicExch(p.sched, 0u);
+                atomicExch(p.sched + 1, 0u);
+            }
         }
     } else if (warp == 1) {
         // ===== MMA issuer =====
-        for (int i = 0; i < nkb; ++i) {
-            const int s = i % STAGES;
-            mbar_wait(&full_bar[s], (i / STAGES) & 1);
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint32_t a0 = smem_u32(smem + (size_t)s * STAGE_BYTES);
-            const uint64_t ad0 = make_desc(a0);
-            const uint64_t bd0 = make_desc(a0 + S * A_TILE);
-            if (elect_one()) {
-                if (i == 0) {
-                    issue_step<GMAX, 1, true, 0, 1>(tmem_base, ad0, bd0);
-                } else {
-                    issue_step<GMAX, 1, false, 0, 1>(tmem_base, ad0, bd0);
-                }
-                issue_step<GMAX, 1, false, 0, 1>(tmem_base, ad0 + (uint64_t)((2 * LBO) >> 4),
-                                                 bd0 + (uint64_t)((2 * LBO) >> 4));
-                umma_commit(&empty_bar[s]);
-                if (i == nkb - 1) umma_commit(&done_bar);
+        uint32_t it = 0;
+        for (uint32_t ti = 0;; ++ti) {
+            mbar_wait(&full_bar[it % STAGES], (it / STAGES) & 1);  // first stage of the tile: its id is visible now
+            const int t = tile_ring[ti % RING];
+            if (t < 0) {
+                if (ti > 0) mbar_wait(&tfree_bar, (ti - 1) & 1);
+                if (elect_one()) mbar_arrive(&done_bar);
+                __syncwarp();
+                break;
             }
-            __syncwarp();
+            const int nkb = gemm_tile(p, t).nkb;
+            for (int i = 0; i < nkb; ++i, ++it) {
+                const int s = it % STAGES;
+                if (i == 0 && ti > 0) mbar_wait(&tfree_bar, (ti - 1) & 1);  // previous tile's accumulators drained
+                if (i > 0) mbar_wait(&full_bar[s], (it / STAGES) & 1);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t a0 = smem_u32(smem + (size_t)s * STAGE_BYTES);
+                const uint64_t ad0 = make_desc(a0);
+                const uint64_t bd0 = make_desc(a0 + S * A_TILE);
+                if (elect_one()) {
+                    if (i == 0) {
+                        issue_step<GMAX, 1, true, 0, 1>(tmem_base, ad0, bd0);
+                    } else {
+                        issue_step<GMAX, 1, false, 0, 1>(tmem_base, ad0, bd0);
+                    }
+                    issue_step<GMAX, 1, false, 0, 1>(tmem_base, ad0 + (uint64_t)((2 * LBO) >> 4),
+                                                     bd0 + (uint64_t)((2 * LBO) >> 4));
+                    umma_commit(&empty_bar[s]);
+                    if (i == nkb - 1) umma_commit(&done_bar);
+                }
+                __syncwarp();
+            }
         }
     } else {
         // ===== epilogue: thread = output row (TMEM lane), 64 output columns =====
         const int q = warp & 3;
         const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
-        const int row = it * TM + q * 32 + lane;
-        const double srow = p.alpha * (p.scale ? p.scale[(size_t)rs * p.scaleStride + row] : 1.0);
-        double* crow = p.C + (size_t)rs * p.cStride + (size_t)row * p.ldc + (size_t)jt * TN;
-        const double* scol = (p.scaleB ? p.scaleB : p.scale) + (size_t)rs * p.scaleStride + jt * TN;
-        mbar_wait(&done_bar, 0);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        for (uint32_t ti = 0;; ++ti) {
+            mbar_wait(&done_bar, ti & 1);
+            const int t = tile_ring[ti % RING];
+            if (t < 0) break;
+            const GemmTile g = gemm_tile(p, t);
+            const int row = g.it * TM + q * 32 + lane;
+            const double srow = p.alpha * (p.scale ? p.scale[(size_t)g.rs * p.scaleStride + row] : 1.0);
+            double* crow = p.C + (size_t)g.rs * p.cStride + (size_t)row * p.ldc + (size_t)g.jt * TN;
+            const double* scol = (p.scaleB ? p.scaleB : p.scale) + (size_t)g.rs * p.scaleStride + g.jt * TN;
+            const double beta = g.beta;
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll 1
-        for (int cc = 0; cc < TN / 8; ++cc) {
-            uint32_t r[NG][8];
+            for (int cc = 0; cc < TN / 8; ++cc) {
+                uint32_t r[NG][8];
 #pragma unroll
-            for (int g = 0; g < NG; ++g) tmem_ld8(lane_base + g * TN + cc * 8, r[g]);
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-            double out[8];
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                // both operands carry digits b_s 2^(1-8s): group g = i+j has weight 2^(2-8g), smallest first
-                double v = 0.0;
-#pragma unroll
-                for (int g = NG - 1; g >= 0; --g) v = fma((double)(int)r[g][c], ldexp(1.0, 2 - 8 * (g + 2)), v);
-                out[c] = v * (srow * __ldg(scol + cc * 8 + c));
-            }
-            double2* dst = reinterpret_cast<double2*>(crow + cc * 8);
-            if (beta != 0.0) {
-#pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    const double2 old = dst[c];
-                    out[2 * c] = fma(beta, old.x, out[2 * c]);
-                    out[2 * c + 1] = fma(beta, old.y, out[2 * c + 1]);
+                for (int gg = 0; gg < NG; ++gg) tmem_ld8(lane_base + gg * TN + cc * 8, r[gg]);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (cc == TN / 8 - 1) {  // the accumulators are in registers: the next tile's MMAs may start
+                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                    mbar_arrive(&tfree_bar);
                 }
-            }
+                double out[8];
 #pragma unroll
-            for (int c = 0; c < 4; ++c) dst[c] = make_double2(out[2 * c], out[2 * c + 1]);
+                for (int c = 0; c < 8; ++c) {
+                    // both operands carry digits b_s 2^(1-8s): group g = i+j has weight 2^(2-8g), smallest first;
+                    // recombine() weighs with 2^(1-8g), the missing factor 2 is exact
+                    out[c] = recombine<NG>(r, c) * (2.0 * srow * __ldg(scol + cc * 8 + c));
+                }
+                double2* dst = reinterpret_cast<double2*>(crow + cc * 8);
+                if (beta != 0.0) {
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        const double2 old = dst[c];
+                        out[2 * c] = fma(beta, old.x, out[2 * c]);
+                        out[2 * c + 1] = fma(beta, old.y, out[2 * c + 1]);
+                    }
+                }
+#pragma unroll
+                for (int c = 0; c < 4; ++c) dst[c] = make_double2(out[2 * c], out[2 * c + 1]);
+            }
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -183,8 +255,22 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_i8_kernel(const GemmI8Params 
     }
 }
 
+// Scheduler counter pairs of the persistent launches: a pool in the caller's workspace, zeroed once per fit call and
+// handed out round-robin.  A pair is zero again when its launch has finished; launches of one fit call that may be in
+// flight together (main, side and look-ahead stream) are at most a few iterations apart, far less than the pool size.
+constexpr int SCHED_POOL = 128;
+struct SchedPool {
+    unsigned* base = nullptr;  // [SCHED_POOL][2]
+    int next = 0;
+    unsigned* take() {
+        unsigned* q = base + 2 * next;
+        next = (next + 1) % SCHED_POOL;
+        return q;
+    }
+};
+
 template <int GMAX>
-inline int launch_gemm_i8(const GemmI8Params& p, int ntiles, int R, cudaStream_t stream) {
+inline int launch_gemm_i8(const GemmI8Params& p0, int ntiles, int R, SchedPool& pool, int sm_count, cudaStream_t stream) {
     static DeviceOnce once;
     if (device_once(once, [] {
             TB_CUDA(cudaFuncSetAttribute(gemm_i8_kernel<GMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -193,10 +279,17 @@ inline int launch_gemm_i8(const GemmI8Params& p, int ntiles, int R, cudaStream_t
         }))
         return -1;
     if (ntiles <= 0 || R <= 0) return 0;
+    TB_CHECK(pool.base != nullptr && sm_count > 0, "fit GEMM: scheduler counters missing");
+    GemmI8Params p = p0;
+    p.ntiles = ntiles;
+    p.R = R;
+    const long total = (long)ntiles * R;
+    const unsigned grid = (unsigned)(total < sm_count ? total : sm_count);
     // the longest k-range any CTA of this launch can have
     const int span = p.tri ? p.kblks : (p.kbHiByRow ? p.kblks : p.kbHi) - p.kbLo;
     if (span <= PASS_KB) {
-        TB_LAUNCH((gemm_i8_kernel<GMAX>), dim3((unsigned)ntiles, (unsigned)R), dim3(THREADS), SMEM_BYTES, stream, p);
+        p.sched = pool.take();
+        TB_LAUNCH((gemm_i8_kernel<GMAX>), dim3(grid), dim3(THREADS), SMEM_BYTES, stream, p);
         return 0;
     }
     const int lo0 = p.tri ? 0 : p.kbLo, hi0 = p.tri ? p.kblks : (p.kbHiByRow ? p.kblks : p.kbHi);
@@ -204,7 +297,8 @@ inline int launch_gemm_i8(const GemmI8Params& p, int ntiles, int R, cudaStream_t
         GemmI8Params q = p;
         q.kbWinLo = w;
         q.kbWinHi = (w + PASS_KB < hi0) ? w + PASS_KB : hi0;
-        TB_LAUNCH((gemm_i8_kernel<GMAX>), dim3((unsigned)ntiles, (unsigned)R), dim3(THREADS), SMEM_BYTES, stream, q);
+        q.sched = pool.take();
+        TB_LAUNCH((gemm_i8_kernel<GMAX>), dim3(grid), dim3(THREADS), SMEM_BYTES, stream, q);
     }
     return 0;
 }

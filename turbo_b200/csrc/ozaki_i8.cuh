@@ -63,6 +63,7 @@ struct Params {
     long candSliceStride, linvSliceStride;  // bytes
     int kblks;               // K / 64 (tiles per row of tiles)
     int rowTiles, candTiles;
+    unsigned* sched;         // [2] tile counter + finished-CTA counter of the persistent grid: zero at launch
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -204,6 +205,7 @@ __device__ __forceinline__ void issue_step(uint32_t tmem_base, uint64_t ad0, uin
 // accumulators into 64 FP64 registers per thread (the rows of V must be complete before they are squared) and hand
 // TMEM back to the MMA warp.  One drain costs ~3k cycles against ~230k cycles of MMAs per pass.
 constexpr int PASS_KB = 128;  // 8192 of K: 7 pairs * 8192 * 255 * 128 < 2^31
+constexpr int RING = 8;       // tile ids in flight between the producer and the epilogue (at most 4 are live)
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -212,6 +214,39 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 // digit planes a kernel with cut-off GMAX reads: plane s pairs with planes 1..GMAX-s, so plane 7 is unused at GMAX = 7
 __host__ __device__ constexpr int planes_used(int gmax) { return gmax - 1 < S ? gmax - 1 : S; }
 
+// (double)(int)r * 2^E without the conversion unit: I2F.F64 is a quarter-rate instruction and the epilogue needs one per
+// accumulator (48 per 8 columns in round 1).  2^(52+E) + (r XOR 2^31) * 2^E is a double whose bit pattern is assembled
+// with one integer instruction; subtracting (2^52 + 2^31) * 2^E is exact.
+template <int E>
+__device__ __forceinline__ double s32_times_pow2(uint32_t r) {
+    constexpr int hi = (1075 + E) << 20;
+    return __hiloint2double(hi, (int)(r ^ 0x80000000u)) - __hiloint2double(hi, (int)0x80000000u);
+}
+// sum_g 2^(1-8(g+2)) G_g for one column, smallest weight first
+template <int NG, int G>
+__device__ __forceinline__ double recombine_from(const uint32_t (&r)[NG][8], int c, double v) {
+    if constexpr (G < 0) {
+        return v;
+    } else {
+        return recombine_from<NG, G - 1>(r, c, v + s32_times_pow2<1 - 8 * (G + 2)>(r[G][c]));
+    }
+}
+template <int NG>
+__device__ __forceinline__ double recombine(const uint32_t (&r)[NG][8], int c) {
+    return recombine_from<NG, NG - 2>(r, c, s32_times_pow2<1 - 8 * (NG + 1)>(r[NG - 1][c]));
+}
+
+// PERSISTENT kernel (round 2): one CTA per SM walks (64 Linv rows) x (128 candidates) tiles handed out heavy-first by a
+// global counter.  Round 1 launched one CTA per tile; ncu showed 25 % of the SM cycles outside the MMAs -- CTA launch,
+// barrier/TMEM set-up, the first loads' latency and the epilogue, ~15 k cycles per tile, none of it overlapped because a
+// 173 KB CTA has no neighbour (profiles/r2_variance_ncu_full.md).  Now the producer warp runs straight on into the next
+// tile's loads, TMEM and barriers are set up once, and only the drain of the accumulators (one TMEM buffer: 6 x 64
+// columns do not fit twice) separates two tiles' MMAs.
+//   warp 0 : fetches the next tile id (atomicAdd), publishes it in `tile_ring` with the first stage of the tile
+//   warp 1 : MMA issuer; starts a tile (or a pass) once the epilogue has drained the previous one (tfree_bar)
+//   2..5   : epilogue; releases TMEM right after its last tcgen05.ld, before the arithmetic of the last columns
+// p.sched = {next tile, CTAs finished}: zero at launch; the last CTA to finish zeroes it again for the next launch
+// (launches that share one sched pair must be stream-ordered -- they are: one variance stream per call).
 template <int GMAX, bool MULTI>
 __global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p) {
     constexpr int NG = GMAX - 1;  // groups g = 2..GMAX, one 64-column INT32 accumulator each
@@ -221,12 +256,10 @@ __global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p)
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], done_bar, tfree_bar;
     __shared__ uint32_t tmem_base_s;
+    __shared__ volatile int tile_ring[RING];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    // heavy row tiles first (k-range grows with the row tile)
-    const int rt = p.rowTiles - 1 - (int)(blockIdx.x / p.candTiles);
-    const int ct = blockIdx.x % p.candTiles;
-    const int nkb = rt + 1;
+    const int ntiles = p.rowTiles * p.candTiles;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; ++s) {
@@ -249,108 +282,153 @@ __global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p)
     const uint32_t tmem_base = tmem_base_s;
 
     if (warp == 0) {
-        // ===== producer: 14 bulk copies per k-block, issued by one elected lane of a converged warp =====
-        const uint8_t* a_src = p.candS + ((size_t)ct * p.kblks) * A_TILE;
-        const uint8_t* b_src = p.linvS + ((size_t)rt * p.kblks) * B_TILE;
-        for (int kb = 0; kb < nkb; ++kb) {
-            const int s = kb % STAGES;
-            if (kb >= STAGES) mbar_wait(&empty_bar[s], ((kb / STAGES) - 1) & 1);
-            if (elect_one()) {
-                uint8_t* st = smem + (size_t)s * STAGE_BYTES;
-                mbar_expect_tx(&full_bar[s], SU * (A_TILE + B_TILE));
+        // ===== producer: 2*SU bulk copies per k-block, issued by one elected lane of a converged warp =====
+        uint32_t it = 0;  // k-blocks issued so far (stage = it % STAGES)
+        for (uint32_t ti = 0;; ++ti) {
+            int t = 0;
+            if (lane == 0) t = (int)atomicAdd(p.sched, 1u);
+            t = __shfl_sync(0xffffffffu, t, 0);
+            const bool last = t >= ntiles;  // the end marker travels through the pipeline like a tile of one k-block
+            // heavy row tiles first (the k-range grows with the row tile)
+            const int rt = last ? 0 : p.rowTiles - 1 - t / p.candTiles;
+            const int ct = last ? 0 : t % p.candTiles;
+            const int nkb = rt + 1;
+            const uint8_t* a_src = p.candS + ((size_t)ct * p.kblks) * A_TILE;
+            const uint8_t* b_src = p.linvS + ((size_t)rt * p.kblks) * B_TILE;
+            for (int kb = 0; kb < nkb; ++kb, ++it) {
+                const int s = it % STAGES;
+                if (it >= STAGES) mbar_wait(&empty_bar[s], ((it / STAGES) - 1) & 1);
+                if (elect_one()) {
+                    // the tile id is published by the arrive on the first stage's barrier (release -> the waiter's acquire)
+                    if (kb == 0) tile_ring[ti % RING] = last ? -1 : t;
+                    if (last) {
+                        mbar_arrive(&full_bar[s]);
+                    } else {
+                        uint8_t* st = smem + (size_t)s * STAGE_BYTES;
+                        mbar_expect_tx(&full_bar[s], SU * (A_TILE + B_TILE));
 #pragma unroll
-                for (int sl = 0; sl < SU; ++sl) {
-                    bulk_g2s(st + sl * A_TILE, a_src + (size_t)sl * p.candSliceStride + (size_t)kb * A_TILE, A_TILE,
-                             &full_bar[s]);
-                    bulk_g2s(st + S * A_TILE + sl * B_TILE, b_src + (size_t)sl * p.linvSliceStride + (size_t)kb * B_TILE,
-                             B_TILE, &full_bar[s]);
+                        for (int sl = 0; sl < SU; ++sl) {
+                            bulk_g2s(st + sl * A_TILE, a_src + (size_t)sl * p.candSliceStride + (size_t)kb * A_TILE,
+                                     A_TILE, &full_bar[s]);
+                            bulk_g2s(st + S * A_TILE + sl * B_TILE,
+                                     b_src + (size_t)sl * p.linvSliceStride + (size_t)kb * B_TILE, B_TILE, &full_bar[s]);
+                        }
+                    }
                 }
+                __syncwarp();
             }
-            __syncwarp();
+            if (last) break;
+        }
+        if (lane == 0) {
+            // every CTA has taken its end marker once the last one arrives here: hand the next launch a zeroed pair
+            if (atomicAdd(p.sched + 1, 1u) == gridDim.x - 1) {
+                atomicExch(p.sched, 0u);
+                atomicExch(p.sched + 1, 0u);
+            }
         }
     } else if (warp == 1) {
         // ===== MMA issuer: the warp stays converged, one elected lane issues =====
-        for (int kb = 0; kb < nkb; ++kb) {
-            const int s = kb % STAGES;
-            const bool pass_start = MULTI ? (kb % PASS_KB == 0) : (kb == 0);
-            if (MULTI && pass_start && kb > 0) {
-                mbar_wait(&tfree_bar, ((kb / PASS_KB) - 1) & 1);  // accumulators of the previous pass drained
+        uint32_t it = 0, passes = 0;  // k-blocks consumed, accumulation passes committed
+        for (uint32_t ti = 0;; ++ti) {
+            mbar_wait(&full_bar[it % STAGES], (it / STAGES) & 1);  // first stage of the tile: its id is visible now
+            const int t = tile_ring[ti % RING];
+            if (t < 0) {
+                // the epilogue must have consumed the last real completion of done_bar before the end marker's plain
+                // arrive may complete another phase
+                if (passes > 0) mbar_wait(&tfree_bar, (passes - 1) & 1);
+                if (elect_one()) mbar_arrive(&done_bar);
+                __syncwarp();
+                break;
+            }
+            const int nkb = p.rowTiles - t / p.candTiles;
+            for (int kb = 0; kb < nkb; ++kb, ++it) {
+                const int s = it % STAGES;
+                const bool pass_start = MULTI ? (kb % PASS_KB == 0) : (kb == 0);
+                const bool pass_end = kb == nkb - 1 || (MULTI && (kb + 1) % PASS_KB == 0);
+                if (pass_start && passes > 0) mbar_wait(&tfree_bar, (passes - 1) & 1);  // previous accumulators drained
+                if (kb > 0) mbar_wait(&full_bar[s], (it / STAGES) & 1);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            }
-            mbar_wait(&full_bar[s], (kb / STAGES) & 1);
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint32_t a0 = smem_u32(smem + (size_t)s * STAGE_BYTES);
-            const uint64_t ad0 = make_desc(a0);
-            const uint64_t bd0 = make_desc(a0 + S * A_TILE);
-            if (elect_one()) {
-                // K = 32 per MMA: the second half of the 64-byte k-block is 2 LBO further (descriptor units of 16 B)
-                if (pass_start) {
-                    issue_step<GMAX, 1, true, 0>(tmem_base, ad0, bd0);
-                } else {
-                    issue_step<GMAX, 1, false, 0>(tmem_base, ad0, bd0);
+                const uint32_t a0 = smem_u32(smem + (size_t)s * STAGE_BYTES);
+                const uint64_t ad0 = make_desc(a0);
+                const uint64_t bd0 = make_desc(a0 + S * A_TILE);
+                if (elect_one()) {
+                    // K = 32 per MMA: the second half of the 64-byte k-block is 2 LBO further (descriptor units of 16 B)
+                    if (pass_start) {
+                        issue_step<GMAX, 1, true, 0>(tmem_base, ad0, bd0);
+                    } else {
+                        issue_step<GMAX, 1, false, 0>(tmem_base, ad0, bd0);
+                    }
+                    issue_step<GMAX, 1, false, 0>(tmem_base, ad0 + (uint64_t)((2 * LBO) >> 4),
+                                                  bd0 + (uint64_t)((2 * LBO) >> 4));
+                    umma_commit(&empty_bar[s]);  // frees the stage once these MMAs have read it
+                    if (pass_end) umma_commit(&done_bar);
                 }
-                issue_step<GMAX, 1, false, 0>(tmem_base, ad0 + (uint64_t)((2 * LBO) >> 4), bd0 + (uint64_t)((2 * LBO) >> 4));
-                umma_commit(&empty_bar[s]);  // frees the stage once these MMAs have read it
-                if (kb == nkb - 1 || (MULTI && (kb + 1) % PASS_KB == 0)) umma_commit(&done_bar);
+                __syncwarp();
+                if (pass_end) ++passes;
             }
-            __syncwarp();
         }
     } else {
         // ===== epilogue: thread = candidate (TMEM lane), 64 columns = Linv rows of this tile =====
         const int q = warp & 3;  // TMEM lane quarter this warp may access
         const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
-        double acc = 0.0;
-        if constexpr (!MULTI) {
-            mbar_wait(&done_bar, 0);
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-#pragma unroll 1
-            for (int cc = 0; cc < TN / 8; ++cc) {
-                uint32_t r[NG][8];
-#pragma unroll
-                for (int g = 0; g < NG; ++g) tmem_ld8(lane_base + g * TN + cc * 8, r[g]);
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-                for (int c = 0; c < 8; ++c) {
-                    // sum_g 2^(1-8(g+2)) G_g, smallest weight first
-                    double v = 0.0;
-#pragma unroll
-                    for (int g = NG - 1; g >= 0; --g) v = fma((double)(int)r[g][c], ldexp(1.0, 1 - 8 * (g + 2)), v);
-                    v *= __ldg(p.rowscale + rt * TN + cc * 8 + c);
-                    acc = fma(v, v, acc);
-                }
-            }
-        } else {
-            double vrow[TN];  // V[candidate, 64 rows] / rowscale, summed over the passes (registers: fully unrolled)
-            const int npass = (nkb + PASS_KB - 1) / PASS_KB;
-            for (int pass = 0; pass < npass; ++pass) {
-                mbar_wait(&done_bar, pass & 1);
+        uint32_t drains = 0;  // completions of done_bar consumed
+        for (uint32_t ti = 0;; ++ti) {
+            mbar_wait(&done_bar, drains & 1);
+            const int t = tile_ring[ti % RING];
+            if (t < 0) break;
+            const int rt = p.rowTiles - 1 - t / p.candTiles, ct = t % p.candTiles;
+            const double* rs = p.rowscale + rt * TN;
+            double acc = 0.0;
+            if constexpr (!MULTI) {
+                ++drains;
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-#pragma unroll
+#pragma unroll 1
                 for (int cc = 0; cc < TN / 8; ++cc) {
                     uint32_t r[NG][8];
 #pragma unroll
                     for (int g = 0; g < NG; ++g) tmem_ld8(lane_base + g * TN + cc * 8, r[g]);
                     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    if (cc == TN / 8 - 1) {  // the accumulators are in registers: the next tile's MMAs may start
+                        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                        mbar_arrive(&tfree_bar);
+                    }
 #pragma unroll
                     for (int c = 0; c < 8; ++c) {
-                        double v = 0.0;
-#pragma unroll
-                        for (int g = NG - 1; g >= 0; --g) v = fma((double)(int)r[g][c], ldexp(1.0, 1 - 8 * (g + 2)), v);
-                        vrow[cc * 8 + c] = (pass == 0) ? v : vrow[cc * 8 + c] + v;
+                        const double v = recombine<NG>(r, c) * __ldg(rs + cc * 8 + c);
+                        acc = fma(v, v, acc);
                     }
                 }
-                if (pass + 1 < npass) {
+            } else {
+                double vrow[TN];  // V[candidate, 64 rows] / rowscale, summed over the passes (registers: fully unrolled)
+                const int nkb = rt + 1;
+                const int npass = (nkb + PASS_KB - 1) / PASS_KB;
+                for (int pass = 0; pass < npass; ++pass) {
+                    if (pass > 0) mbar_wait(&done_bar, drains & 1);
+                    ++drains;
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+                    for (int cc = 0; cc < TN / 8; ++cc) {
+                        uint32_t r[NG][8];
+#pragma unroll
+                        for (int g = 0; g < NG; ++g) tmem_ld8(lane_base + g * TN + cc * 8, r[g]);
+                        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                        for (int c = 0; c < 8; ++c) {
+                            const double v = recombine<NG>(r, c);
+                            vrow[cc * 8 + c] = (pass == 0) ? v : vrow[cc * 8 + c] + v;
+                        }
+                    }
                     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                     mbar_arrive(&tfree_bar);
                 }
-            }
 #pragma unroll
-            for (int c = 0; c < TN; ++c) {
-                const double v = vrow[c] * __ldg(p.rowscale + rt * TN + c);
-                acc = fma(v, v, acc);
+                for (int c = 0; c < TN; ++c) {
+                    const double v = vrow[c] * __ldg(rs + c);
+                    acc = fma(v, v, acc);
+                }
             }
+            p.partial[(long)rt * p.ldp + (long)ct * TM + q * 32 + lane] = acc;
         }
-        p.partial[(long)rt * p.ldp + (long)ct * TM + q * 32 + lane] = acc;
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -360,7 +438,7 @@ __global__ void __launch_bounds__(THREADS, 1) colsumsq_i8_kernel(const Params p)
 }
 
 template <int GMAX, bool MULTI>
-inline int launch_colsumsq_i8_impl(const Params& p, cudaStream_t stream) {
+inline int launch_colsumsq_i8_impl(const Params& p, int sm_count, cudaStream_t stream) {
     static DeviceOnce once;
     if (device_once(once, [] {
             TB_CUDA(cudaFuncSetAttribute(colsumsq_i8_kernel<GMAX, MULTI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -372,16 +450,19 @@ inline int launch_colsumsq_i8_impl(const Params& p, cudaStream_t stream) {
             return 0;
         }))
         return -1;
-    TB_LAUNCH((colsumsq_i8_kernel<GMAX, MULTI>), dim3((unsigned)(p.rowTiles * p.candTiles)), dim3(THREADS), SMEM_BYTES,
-              stream, p);
+    const int tiles = p.rowTiles * p.candTiles;
+    TB_CHECK(p.sched != nullptr && sm_count > 0, "variance kernel: scheduler counters missing");
+    TB_LAUNCH((colsumsq_i8_kernel<GMAX, MULTI>), dim3((unsigned)(tiles < sm_count ? tiles : sm_count)), dim3(THREADS),
+              SMEM_BYTES, stream, p);
     return 0;
 }
 
+// sm_count: CTAs of the persistent grid (one per SM; 173 KB of shared memory keeps a second one off the SM)
 template <int GMAX>
-inline int launch_colsumsq_i8(const Params& p, cudaStream_t stream) {
+inline int launch_colsumsq_i8(const Params& p, int sm_count, cudaStream_t stream) {
     // the heaviest tile spans rowTiles k-blocks
-    return p.rowTiles <= PASS_KB ? launch_colsumsq_i8_impl<GMAX, false>(p, stream)
-                                 : launch_colsumsq_i8_impl<GMAX, true>(p, stream);
+    return p.rowTiles <= PASS_KB ? launch_colsumsq_i8_impl<GMAX, false>(p, sm_count, stream)
+                                 : launch_colsumsq_i8_impl<GMAX, true>(p, sm_count, stream);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -447,6 +528,117 @@ __global__ void __launch_bounds__(64, 1) i8_peak_kernel(int batches, int random,
             __syncwarp();
         }
         for (int b = (batches > 2 ? batches - 2 : 0); b < batches; ++b) mbar_wait(&bar[b & 1], (b >> 1) & 1);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Diagnostic (tb200_i8_mma_list): cycles one k-block costs when an arbitrary LIST of MMAs -- the variance kernel's own
+// (A plane, accumulator columns, N, first B row) list or a re-ordered / re-chunked variant of it -- is issued
+// back to back on operands that stay resident in shared memory.  No loads, no epilogue: what is measured is what the
+// tensor pipe makes of that instruction mix, dependencies between overlapping accumulator ranges included.  A k-block
+// is two K = 32 steps like in the kernels above.
+// ---------------------------------------------------------------------------------------------
+struct MmaOp { int plane, col0, n, brow0; };
+constexpr int MMA_LIST_MAX = 64;
+constexpr int MMA_LIST_VARIANTS = 12;
+
+// compile-time lists: the issuing lane executes nothing but uniform-register moves between two MMAs, as in the kernels
+template <int V> struct MmaList;
+#define TB_MMA_LIST(V, ...)                                                    \
+    template <> struct MmaList<V> {                                            \
+        static constexpr MmaOp ops[] = {__VA_ARGS__};                          \
+        static constexpr int n = (int)(sizeof(ops) / sizeof(MmaOp));           \
+    }
+// 0: the variance kernel's list at 21 products (plane i-1 x stacked planes 1..7-i, balanced chunks)
+TB_MMA_LIST(0, {0, 0, 192, 0}, {0, 192, 192, 192}, {1, 64, 160, 0}, {1, 224, 160, 160}, {2, 128, 256, 0}, {3, 192, 192, 0}, {4, 256, 128, 0}, {5, 320, 64, 0});
+// 1: the same instructions, ONE A plane;  2: one A plane and B rows from 0
+TB_MMA_LIST(1, {0, 0, 192, 0}, {0, 192, 192, 192}, {0, 64, 160, 0}, {0, 224, 160, 160}, {0, 128, 256, 0}, {0, 192, 192, 0}, {0, 256, 128, 0}, {0, 320, 64, 0});
+TB_MMA_LIST(2, {0, 0, 192, 0}, {0, 192, 192, 0}, {0, 64, 160, 0}, {0, 224, 160, 0}, {0, 128, 256, 0}, {0, 192, 192, 0}, {0, 256, 128, 0}, {0, 320, 64, 0});
+// 3: the kernel's operands and N sequence, accumulators alternating between the aligned halves of TMEM
+TB_MMA_LIST(3, {0, 0, 192, 0}, {0, 256, 192, 192}, {1, 0, 160, 0}, {1, 256, 160, 160}, {2, 0, 256, 0}, {3, 256, 192, 0}, {4, 0, 128, 0}, {5, 256, 64, 0});
+// 4: uniform: seven MMAs of N = 192 (the same 1344 columns), planes in turn, alternating halves
+TB_MMA_LIST(4, {0, 0, 192, 0}, {1, 256, 192, 0}, {2, 0, 192, 0}, {3, 256, 192, 0}, {4, 0, 192, 0}, {5, 256, 192, 0}, {0, 0, 192, 192});
+// 5: the kernel's list with every accumulator range starting at column 0
+TB_MMA_LIST(5, {0, 0, 192, 0}, {0, 0, 192, 192}, {1, 0, 160, 0}, {1, 0, 160, 160}, {2, 0, 256, 0}, {3, 0, 192, 0}, {4, 0, 128, 0}, {5, 0, 64, 0});
+// 6: the kernel's list, short instructions first
+TB_MMA_LIST(6, {5, 320, 64, 0}, {4, 256, 128, 0}, {3, 192, 192, 0}, {2, 128, 256, 0}, {1, 64, 160, 0}, {1, 224, 160, 160}, {0, 0, 192, 0}, {0, 192, 192, 192});
+// 7: chunks of 256 + remainder
+TB_MMA_LIST(7, {0, 0, 256, 0}, {0, 256, 128, 256}, {1, 64, 256, 0}, {1, 320, 64, 256}, {2, 128, 256, 0}, {3, 192, 192, 0}, {4, 256, 128, 0}, {5, 320, 64, 0});
+// 8: the kernel's list at 28 products
+TB_MMA_LIST(8, {0, 0, 224, 0}, {0, 224, 224, 224}, {1, 64, 192, 0}, {1, 256, 192, 192}, {2, 128, 160, 0}, {2, 288, 160, 160}, {3, 192, 256, 0}, {4, 256, 192, 0}, {5, 320, 128, 0}, {6, 384, 64, 0});
+// 9: 21 products, short and long instructions interleaved
+TB_MMA_LIST(9, {0, 0, 192, 0}, {5, 320, 64, 0}, {0, 192, 192, 192}, {4, 256, 128, 0}, {1, 64, 160, 0}, {1, 224, 160, 160}, {2, 128, 256, 0}, {3, 192, 192, 0});
+// 10: six MMAs of N = 224 (= 1344 columns);  11: five of 256 + one of 64
+TB_MMA_LIST(10, {0, 0, 224, 0}, {1, 256, 224, 0}, {2, 0, 224, 0}, {3, 256, 224, 0}, {4, 0, 224, 0}, {5, 256, 224, 0});
+TB_MMA_LIST(11, {0, 0, 256, 0}, {1, 256, 256, 0}, {2, 0, 256, 0}, {3, 256, 256, 0}, {4, 0, 256, 0}, {5, 256, 64, 0});
+#undef TB_MMA_LIST
+
+template <int V, int I = 0>
+__device__ __forceinline__ void issue_list(uint32_t tmem_base, uint64_t ad0, uint64_t bd0, uint32_t acc) {
+    if constexpr (I < MmaList<V>::n) {
+        constexpr MmaOp o = MmaList<V>::ops[I];
+        umma_i8(tmem_base + (uint32_t)o.col0, ad0 + (uint64_t)(o.plane * (A_TILE >> 4)),
+                bd0 + (uint64_t)((o.brow0 >> 3) * (SBO >> 4)), idesc(o.n), acc);
+        issue_list<V, I + 1>(tmem_base, ad0, bd0, acc);
+    }
+}
+
+template <int V>
+__global__ void __launch_bounds__(64, 1) i8_mma_list_kernel(int kblocks, long long* __restrict__ cycles) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    __shared__ uint64_t bar[2];
+    __shared__ uint32_t tmem_base_s;
+    const int warp = threadIdx.x >> 5;
+    for (int e = threadIdx.x; e < (int)(STAGE_BYTES / 16); e += blockDim.x) {
+        uint32_t w[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            uint32_t x = (uint32_t)(e * 4 + q) * 2654435761u + blockIdx.x * 40503u + 12345u;
+            x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+            w[q] = x;
+        }
+        reinterpret_cast<uint4*>(smem)[e] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (threadIdx.x == 0) {
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)),
+                     "r"(TMEM_COLS)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = tmem_base_s;
+    if (warp == 0) {
+        const uint64_t ad0 = make_desc(smem_u32(smem));
+        const uint64_t bd0 = make_desc(smem_u32(smem + S * A_TILE));
+        const uint64_t ko = (uint64_t)((2 * LBO) >> 4);
+        long long t0 = 0;
+        for (int b = 0; b < kblocks; ++b) {
+            if (b >= 2) mbar_wait(&bar[b & 1], ((b >> 1) - 1) & 1);
+            if (b == 2) t0 = clock64();  // the first two k-blocks fill the queue
+            if (elect_one()) {
+                issue_list<V>(tmem_base, ad0, bd0, b > 0 ? 1u : 0u);
+                issue_list<V>(tmem_base, ad0 + ko, bd0 + ko, 1u);
+                umma_commit(&bar[b & 1]);
+            }
+            __syncwarp();
+        }
+        for (int b = (kblocks > 2 ? kblocks - 2 : 0); b < kblocks; ++b) mbar_wait(&bar[b & 1], (b >> 1) & 1);
+        const long long t1 = clock64();
+        if (threadIdx.x == 0) cycles[blockIdx.x] = t1 - t0;
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
