@@ -189,9 +189,11 @@ int tb200_i8_peak(double ms, int random_digits, double* int8_tops_host);
 int tb200_i8_mma_rate(double ms, int random_digits, int n_cols, double* int8_tops_host);
 /* diagnostic: SM cycles per k-block (two K = 32 steps) of one of the compile-time MMA lists of csrc/ozaki_i8.cuh
  * (MmaList<variant>: the variance kernel's own instruction list and re-ordered / re-chunked / re-aligned variants of
- * it) issued back to back on resident shared-memory operands.  Separates what the instruction mix costs on the tensor
- * pipe from what loads and the epilogue cost (tools/i8_mma_list.py). */
-int tb200_i8_mma_list(int variant, int kblocks, double* cycles_per_kblock_host, int* mmas_per_step_host,
+ * it).  fill_planes = -1: issued back to back on resident shared-memory operands; fill_planes = 0..7: inside the
+ * kernels' two-stage pipeline, a producer warp refilling the idle stage with that many digit planes of both operands
+ * per k-block (0 = stage hand-over only).  Separates what the instruction mix costs on the tensor pipe from what the
+ * fill traffic into shared memory costs it (tools/i8_mma_list.py). */
+int tb200_i8_mma_list(int variant, int kblocks, int fill_planes, double* cycles_per_kblock_host, int* mmas_per_step_host,
                       int* columns_per_step_host);
 
 /* Incremental refit at fixed hyper-parameters (the reference's `training_iterations` callable returning 0,

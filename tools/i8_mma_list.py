@@ -25,19 +25,30 @@ NAMES = [
     "21 products, short and long instructions interleaved",
     "uniform: 6 x N=224, alternating halves",
     "5 x N=256 + 1 x N=64, alternating halves",
+    "the kernel's list, A kept in the collector for the second chunk of a range (collector::a::fill / lastuse)",
+    "... and short / long instructions interleaved",
 ]
+
+
+def run(lib, v, planes):
+    cyc, n, cols = C.c_double(), C.c_int(), C.c_int()
+    _lib.check(lib.tb200_i8_mma_list(v, 4000, planes, C.byref(cyc), C.byref(n), C.byref(cols)))
+    return cyc.value / 2, n.value, cols.value
 
 
 def main():
     lib = _lib.load()
     torch.cuda.set_device(0)
-    print("| # | list | MMAs per K=32 step | cycles per K=32 step | ideal (columns / 2) | ratio | cycles per MMA |")
-    print("|---|---|---|---|---|---|---|")
+    print("cycles per K = 32 step; resident = operands stay in shared memory; pipeline p = two-stage pipeline whose idle "
+          "stage is refilled with p digit planes of both operands per k-block (6 = the variance kernel at 21 products: "
+          "36 KB per step)")
+    print()
+    print("| # | list | MMAs per step | ideal (columns / 2) | resident | pipeline 0 | pipeline 2 | pipeline 4 | pipeline 6 | pipeline 7 |")
+    print("|---|---|---|---|---|---|---|---|---|---|")
     for v, name in enumerate(NAMES):
-        cyc, n, cols = C.c_double(), C.c_int(), C.c_int()
-        _lib.check(lib.tb200_i8_mma_list(v, 4000, C.byref(cyc), C.byref(n), C.byref(cols)))
-        per = cyc.value / 2
-        print("| %d | %s | %d | %.0f | %.0f | %.3f | %.1f |" % (v, name, n.value, per, cols.value / 2, per / (cols.value / 2), per / n.value))
+        res, n, cols = run(lib, v, -1)
+        row = [run(lib, v, p)[0] for p in (0, 2, 4, 6, 7)] if v in (0, 4, 8, 9, 10, 12, 13) else [float('nan')] * 5
+        print("| %d | %s | %d | %.0f | %.0f | %s |" % (v, name, n, cols / 2, res, " | ".join("%.0f" % r for r in row)))
 
 
 if __name__ == "__main__":

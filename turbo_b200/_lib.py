@@ -75,7 +75,8 @@ _SIGNATURES = {
     "tb200_fp64_peak": (C.c_int, [C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "tb200_i8_peak": (C.c_int, [C.c_double, C.c_int, C.POINTER(C.c_double)]),
     "tb200_i8_mma_rate": (C.c_int, [C.c_double, C.c_int, C.c_int, C.POINTER(C.c_double)]),
-    "tb200_i8_mma_list": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "tb200_i8_mma_list": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int),
+                                    C.POINTER(C.c_int)]),
     "tb200_append_workspace_bytes": (C.c_size_t, [C.c_int]),
     "tb200_factor_append": (C.c_int, [_P, _P, _P, _P, C.c_int, C.POINTER(KernelSpecC), _P, C.c_double, _P, _P,
                                       C.c_size_t, _P]),

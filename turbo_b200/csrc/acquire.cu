@@ -219,8 +219,8 @@ template <int KIND>
 __global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_kernel(
     const double* __restrict__ Xc, int64_t m_valid, const double* __restrict__ XsT, int n, int NP,
     tb200_kernel_spec spec, const double* __restrict__ theta, const double* __restrict__ alpha,
-    uint8_t* __restrict__ KsS, long slice_stride, double* __restrict__ mean, int jchunk, long mean_stride, int ngroups,
-    int ksplit) {
+    uint8_t* __restrict__ KsS, long slice_stride, int nplanes, double* __restrict__ mean, int jchunk, long mean_stride,
+    int ngroups, int ksplit) {
     extern __shared__ double sh[];  // xc[d][CPB] scaled candidates, red[4][CPB]
     const int d = spec.d;
     double* xc = sh;
@@ -295,7 +295,8 @@ __global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_kernel(
                     const uint32_t p23 = __byte_perm(src[4 * v + 2], src[4 * v + 3], byte | ((4 + byte) << 4));
                     w[v] = __byte_perm(p01, p23, 0x5410);
                 }
-                *reinterpret_cast<uint4*>(dst + (size_t)sl * slice_stride) = make_uint4(w[0], w[1], w[2], w[3]);
+                // planes the variance kernel's cut-off never reads (the 7th at 21 products) are not written
+                if (sl < nplanes) *reinterpret_cast<uint4*>(dst + (size_t)sl * slice_stride) = make_uint4(w[0], w[1], w[2], w[3]);
             }
         }
         // lanes with the same candidate (lane & 7) hold partial means: fold lane bits 3 and 4, then the 4 warps in order
@@ -333,7 +334,7 @@ template <int KIND, int NC>
 __global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_staged_kernel(
     const double* __restrict__ Xc, int64_t m_valid, const double* __restrict__ XsT, int n, int NP,
     tb200_kernel_spec spec, const double* __restrict__ theta, const double* __restrict__ alpha,
-    uint8_t* __restrict__ KsS, long slice_stride, double* __restrict__ mean, long mean_stride, int ngroups,
+    uint8_t* __restrict__ KsS, long slice_stride, int nplanes, double* __restrict__ mean, long mean_stride, int ngroups,
     int nsplit) {
     constexpr int CHUNK = ks_chunk(NC), ROW = ks_row(NC);
     extern __shared__ double sh[];
@@ -422,7 +423,8 @@ __global__ void __launch_bounds__(KS_THREADS) kstar_mean_i8_staged_kernel(
                     const uint32_t p23 = __byte_perm(src[4 * v + 2], src[4 * v + 3], byte | ((4 + byte) << 4));
                     w[v] = __byte_perm(p01, p23, 0x5410);
                 }
-                *reinterpret_cast<uint4*>(dst + (size_t)sl * slice_stride) = make_uint4(w[0], w[1], w[2], w[3]);
+                // planes the variance kernel's cut-off never reads (the 7th at 21 products) are not written
+                if (sl < nplanes) *reinterpret_cast<uint4*>(dst + (size_t)sl * slice_stride) = make_uint4(w[0], w[1], w[2], w[3]);
             }
         }
         // lanes with the same candidate (lane % NC) hold partial means: fold the point-group bits of the lane index
@@ -1052,15 +1054,22 @@ static int configure_carveout_device() {
 static int configure_carveout() { return device_once(g_carveout_once, configure_carveout_device); }
 
 template <int V>
-static int run_mma_list(int kblocks, int sms, long long* d_cyc) {
+static int run_mma_list(int kblocks, int planes, const uint8_t* src, long src_bytes, int sms, long long* d_cyc) {
     static DeviceOnce once;
     if (device_once(once, [] {
             TB_CUDA(cudaFuncSetAttribute(i8::i8_mma_list_kernel<V>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)(i8::STAGE_BYTES + 1024)));
+            TB_CUDA(cudaFuncSetAttribute(i8::i8_mma_pipe_kernel<V>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)i8::SMEM_BYTES));
             return 0;
         }))
         return -1;
-    TB_LAUNCH(i8::i8_mma_list_kernel<V>, dim3(sms), dim3(64), i8::STAGE_BYTES + 1024, 0, kblocks, d_cyc);
+    if (planes < 0) {
+        TB_LAUNCH(i8::i8_mma_list_kernel<V>, dim3(sms), dim3(64), i8::STAGE_BYTES + 1024, 0, kblocks, d_cyc);
+    } else {
+        TB_LAUNCH(i8::i8_mma_pipe_kernel<V>, dim3(sms), dim3(64), i8::SMEM_BYTES, 0, kblocks, planes, src, src_bytes,
+                  d_cyc);
+    }
     return 0;
 }
 
@@ -1227,10 +1236,11 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
             const int kitems = staged_ctas ? st_groups * staged_splits : ngroups * ksplit;
             const dim3 kgrid((unsigned)(kitems < kctas ? kitems : kctas));
             const size_t ksm_st = kstar_staged_smem(d, staged_nc);
+            const int kplanes = i8::planes_used(f8.gmax);
 #define TB_KSTAR_ST(KIND, NC)                                                                                          \
     TB_LAUNCH((kstar_mean_i8_staged_kernel<KIND, NC>), kgrid, dim3(KS_THREADS), ksm_st, s_small, xc, q.mb, XsT, n, NP, \
-              *spec, theta, alpha, reinterpret_cast<uint8_t*>(w.Ks), slice_stride, w.mean, (long)batch, st_groups,     \
-              staged_splits)
+              *spec, theta, alpha, reinterpret_cast<uint8_t*>(w.Ks), slice_stride, kplanes, w.mean, (long)batch,       \
+              st_groups, staged_splits)
 #define TB_KSTAR_I8(KIND)                                                                                              \
     if (staged_ctas && staged_nc == 16) {                                                                              \
         TB_KSTAR_ST(KIND, 16);                                                                                         \
@@ -1238,8 +1248,8 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
         TB_KSTAR_ST(KIND, 8);                                                                                          \
     } else {                                                                                                           \
         TB_LAUNCH(kstar_mean_i8_kernel<KIND>, kgrid, dim3(KS_THREADS), ksm8, s_small, xc, q.mb, XsT, n, NP, *spec,     \
-                  theta, alpha, reinterpret_cast<uint8_t*>(w.Ks), slice_stride, w.mean, jchunk, (long)batch, ngroups,  \
-                  ksplit);                                                                                             \
+                  theta, alpha, reinterpret_cast<uint8_t*>(w.Ks), slice_stride, kplanes, w.mean, jchunk, (long)batch,  \
+                  ngroups, ksplit);                                                                                    \
     }
             switch (spec->kind) {
                 case TB200_RBF: TB_KSTAR_I8(TB200_RBF); break;
@@ -1539,27 +1549,36 @@ int tb200_i8_mma_rate(double ms, int random_digits, int n_cols, double* int8_top
     return 0;
 }
 
-int tb200_i8_mma_list(int variant, int kblocks, double* cycles_per_kblock, int* mmas_per_step, int* columns_per_step) {
+int tb200_i8_mma_list(int variant, int kblocks, int fill_planes, double* cycles_per_kblock, int* mmas_per_step,
+                      int* columns_per_step) {
     TB_CHECK(cycles_per_kblock && mmas_per_step && columns_per_step, "NULL pointer argument");
-    TB_CHECK(variant >= 0 && variant < i8::MMA_LIST_VARIANTS && kblocks >= 4, "tb200_i8_mma_list: variant 0..11, >= 4 k-blocks");
+    TB_CHECK(variant >= 0 && variant < i8::MMA_LIST_VARIANTS && kblocks >= 8, "tb200_i8_mma_list: variant 0..13, >= 8 k-blocks");
+    TB_CHECK(fill_planes >= -1 && fill_planes <= i8::S, "tb200_i8_mma_list: fill_planes -1 (resident operands) .. 7");
     int dev = 0, sms = 0;
     TB_CUDA(cudaGetDevice(&dev));
     TB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     long long* d_cyc = nullptr;
+    uint8_t* d_src = nullptr;
+    const long src_bytes = 64l << 20;  // L2-resident scratch the fills read from (the values do not matter)
     TB_CUDA(cudaMalloc(&d_cyc, sizeof(long long) * sms));
+    if (fill_planes > 0) {
+        TB_CUDA(cudaMalloc(&d_src, src_bytes));
+        TB_CUDA(cudaMemset(d_src, 0x5a, src_bytes));
+    }
     double best = 0.0;
     int rc = 0;
+    const int skipped = fill_planes < 0 ? 2 : 4;  // k-blocks before the clock is started
     for (int rep = 0; rep < 3 && rc == 0; ++rep) {
         int n = 0, cols = 0;
 #define TB_RUN(V)                                                                \
     case V:                                                                      \
-        rc = run_mma_list<V>(kblocks, sms, d_cyc);                               \
+        rc = run_mma_list<V>(kblocks, fill_planes, d_src, src_bytes, sms, d_cyc); \
         n = i8::MmaList<V>::n;                                                   \
         for (int i = 0; i < n; ++i) cols += i8::MmaList<V>::ops[i].n;            \
         break
         switch (variant) {
-            TB_RUN(0); TB_RUN(1); TB_RUN(2); TB_RUN(3); TB_RUN(4); TB_RUN(5);
-            TB_RUN(6); TB_RUN(7); TB_RUN(8); TB_RUN(9); TB_RUN(10); TB_RUN(11);
+            TB_RUN(0); TB_RUN(1); TB_RUN(2); TB_RUN(3); TB_RUN(4); TB_RUN(5); TB_RUN(6);
+            TB_RUN(7); TB_RUN(8); TB_RUN(9); TB_RUN(10); TB_RUN(11); TB_RUN(12); TB_RUN(13);
         }
 #undef TB_RUN
         if (rc) break;
@@ -1572,10 +1591,11 @@ int tb200_i8_mma_list(int variant, int kblocks, double* cycles_per_kblock, int* 
         }
         double sum = 0.0;
         for (int i = 0; i < sms; ++i) sum += (double)h[i];
-        const double per = sum / sms / (double)(kblocks - 2);
+        const double per = sum / sms / (double)(kblocks - skipped);
         if (rep == 0 || per < best) best = per;
     }
     cudaFree(d_cyc);
+    if (d_src) cudaFree(d_src);
     *cycles_per_kblock = best;
     return rc;
 }

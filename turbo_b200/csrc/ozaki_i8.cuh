@@ -126,6 +126,31 @@ __device__ __forceinline__ void umma_i8(uint32_t d_tmem, uint64_t adesc, uint64_
         : "r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(0), "r"(0), "r"(0), "r"(0)
         : "memory");
 }
+// the same MMA with a collector hint for the A operand: COLL = 1 keeps A in the collector buffer after this instruction
+// (collector::a::fill), 2 takes it from there instead of reading shared memory again (collector::a::lastuse)
+template <int COLL>
+__device__ __forceinline__ void umma_i8_coll(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                             uint32_t accumulate) {
+    if constexpr (COLL == 1) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "setp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::i8.collector::a::fill [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}"
+            :
+            : "r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(0), "r"(0), "r"(0), "r"(0)
+            : "memory");
+    } else if constexpr (COLL == 2) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "setp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::i8.collector::a::lastuse [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}"
+            :
+            : "r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(0), "r"(0), "r"(0), "r"(0)
+            : "memory");
+    } else {
+        umma_i8(d_tmem, adesc, bdesc, idesc, accumulate);
+    }
+}
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                  : "memory");
@@ -161,15 +186,18 @@ __device__ __forceinline__ bool elect_one() {
 // N = 128 / 160 / 192 / 224 / 256) over a floor of ~50 cycles per instruction (58 at N = 64), so 384 columns are
 // cheaper as 192 + 192 (196 cycles) than as 256 + 128 (201), 320 as 160 + 160 (168) than as 256 + 64 (187): an A/B of
 // the two orders on the variance kernel gave 0.2541 vs 0.2555 ms (profiles/r2_ab_chunking.md).
-template <int N_LO, int N_HI, int ACC, int ASGN = 0>
+template <int N_LO, int N_HI, int ACC, int ASGN = 0, int FIRST_LO = N_LO>
 __device__ __forceinline__ void issue_range(uint32_t d_tmem, uint64_t ad, uint64_t bd0) {
     if constexpr (N_HI > N_LO) {
         constexpr int width = N_HI - N_LO;
         constexpr int nchunks = (width + 255) / 256;
         constexpr int chunk = ((width / nchunks) + 15) & ~15;
         constexpr int nc = chunk < width ? chunk : width;
-        umma_i8(d_tmem + N_LO, ad, bd0 + (uint64_t)((N_LO >> 3) * (SBO >> 4)), idesc(nc, ASGN), (uint32_t)ACC);
-        issue_range<N_LO + nc, N_HI, ACC, ASGN>(d_tmem, ad, bd0);
+        // a range cut into several chunks reads the same A tile for each: the first keeps it in the collector buffer,
+        // the last takes it from there (4 KB of shared-memory reads less per extra chunk)
+        constexpr int coll = (nc < width) ? 1 : (N_LO > FIRST_LO ? 2 : 0);
+        umma_i8_coll<coll>(d_tmem + N_LO, ad, bd0 + (uint64_t)((N_LO >> 3) * (SBO >> 4)), idesc(nc, ASGN), (uint32_t)ACC);
+        issue_range<N_LO + nc, N_HI, ACC, ASGN, FIRST_LO>(d_tmem, ad, bd0);
     }
 }
 
@@ -214,26 +242,36 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 // digit planes a kernel with cut-off GMAX reads: plane s pairs with planes 1..GMAX-s, so plane 7 is unused at GMAX = 7
 __host__ __device__ constexpr int planes_used(int gmax) { return gmax - 1 < S ? gmax - 1 : S; }
 
-// (double)(int)r * 2^E without the conversion unit: I2F.F64 is a quarter-rate instruction and the epilogue needs one per
-// accumulator (48 per 8 columns in round 1).  2^(52+E) + (r XOR 2^31) * 2^E is a double whose bit pattern is assembled
-// with one integer instruction; subtracting (2^52 + 2^31) * 2^E is exact.
+// sum_g 2^(1-8(g+2)) G_g for one column of the NG accumulator groups -- on the INTEGER pipe as far as it goes.  The
+// round-1 epilogue converted every accumulator (I2F.F64, a quarter-rate instruction: 48 per 8 columns) and chained NG
+// DFMAs; next to the K* kernel, which lives on the FP64 pipe, that made the drain of the accumulators -- the only time a
+// persistent CTA's tensor pipe waits -- the contended part.  Here three neighbouring groups are merged exactly into one
+// 64-bit integer, T = G_g 2^16 + G_{g+1} 2^8 + G_{g+2} (|T| < 2^48), and T 2^E is turned into a double without the
+// conversion unit: adding T to the bit pattern of 1.5 2^(52+E) gives the double (1.5 2^52 + T) 2^E, and subtracting
+// 1.5 2^(52+E) is exact.  Per column: ~10 integer instructions and NG/3 + 1 FP64 additions instead of NG conversions and
+// NG DFMAs.
 template <int E>
-__device__ __forceinline__ double s32_times_pow2(uint32_t r) {
-    constexpr int hi = (1075 + E) << 20;
-    return __hiloint2double(hi, (int)(r ^ 0x80000000u)) - __hiloint2double(hi, (int)0x80000000u);
+__device__ __forceinline__ double s64_times_pow2(long long t) {
+    constexpr long long C = ((long long)(1075 + E) << 52) | (1ll << 51);
+    return __longlong_as_double(t + C) - __longlong_as_double(C);
 }
-// sum_g 2^(1-8(g+2)) G_g for one column, smallest weight first
-template <int NG, int G>
+// groups [G0, NG) of column c, three at a time from the least significant end; E_LAST = weight exponent of group NG-1
+template <int NG, int HI>
 __device__ __forceinline__ double recombine_from(const uint32_t (&r)[NG][8], int c, double v) {
-    if constexpr (G < 0) {
+    if constexpr (HI < 0) {
         return v;
     } else {
-        return recombine_from<NG, G - 1>(r, c, v + s32_times_pow2<1 - 8 * (G + 2)>(r[G][c]));
+        constexpr int LO = HI - 2 < 0 ? 0 : HI - 2;  // merge groups LO..HI (1 to 3 of them)
+        long long t = (long long)(int)r[HI][c];
+        if constexpr (HI - 1 >= LO) t += (long long)(int)r[HI - 1][c] << 8;
+        if constexpr (HI - 2 >= LO) t += (long long)(int)r[HI - 2][c] << 16;
+        const double x = s64_times_pow2<1 - 8 * (HI + 2)>(t);
+        return recombine_from<NG, LO - 1>(r, c, HI == NG - 1 ? x : v + x);
     }
 }
 template <int NG>
 __device__ __forceinline__ double recombine(const uint32_t (&r)[NG][8], int c) {
-    return recombine_from<NG, NG - 2>(r, c, s32_times_pow2<1 - 8 * (NG + 1)>(r[NG - 1][c]));
+    return recombine_from<NG, NG - 1>(r, c, 0.0);
 }
 
 // PERSISTENT kernel (round 2): one CTA per SM walks (64 Linv rows) x (128 candidates) tiles handed out heavy-first by a
@@ -543,9 +581,9 @@ __global__ void __launch_bounds__(64, 1) i8_peak_kernel(int batches, int random,
 // tensor pipe makes of that instruction mix, dependencies between overlapping accumulator ranges included.  A k-block
 // is two K = 32 steps like in the kernels above.
 // ---------------------------------------------------------------------------------------------
-struct MmaOp { int plane, col0, n, brow0; };
+struct MmaOp { int plane, col0, n, brow0, coll = 0; };
 constexpr int MMA_LIST_MAX = 64;
-constexpr int MMA_LIST_VARIANTS = 12;
+constexpr int MMA_LIST_VARIANTS = 14;
 
 // compile-time lists: the issuing lane executes nothing but uniform-register moves between two MMAs, as in the kernels
 template <int V> struct MmaList;
@@ -576,14 +614,18 @@ TB_MMA_LIST(9, {0, 0, 192, 0}, {5, 320, 64, 0}, {0, 192, 192, 192}, {4, 256, 128
 // 10: six MMAs of N = 224 (= 1344 columns);  11: five of 256 + one of 64
 TB_MMA_LIST(10, {0, 0, 224, 0}, {1, 256, 224, 0}, {2, 0, 224, 0}, {3, 256, 224, 0}, {4, 0, 224, 0}, {5, 256, 224, 0});
 TB_MMA_LIST(11, {0, 0, 256, 0}, {1, 256, 256, 0}, {2, 0, 256, 0}, {3, 256, 256, 0}, {4, 0, 256, 0}, {5, 256, 64, 0});
+// 12: the kernel's list with the A operand of a two-chunk range kept in the collector for the second chunk
+TB_MMA_LIST(12, {0, 0, 192, 0, 1}, {0, 192, 192, 192, 2}, {1, 64, 160, 0, 1}, {1, 224, 160, 160, 2}, {2, 128, 256, 0}, {3, 192, 192, 0}, {4, 256, 128, 0}, {5, 320, 64, 0});
+// 13: the same, short and long instructions interleaved (list 9 with the hints)
+TB_MMA_LIST(13, {0, 0, 192, 0, 1}, {0, 192, 192, 192, 2}, {5, 320, 64, 0}, {1, 64, 160, 0, 1}, {1, 224, 160, 160, 2}, {4, 256, 128, 0}, {2, 128, 256, 0}, {3, 192, 192, 0});
 #undef TB_MMA_LIST
 
 template <int V, int I = 0>
 __device__ __forceinline__ void issue_list(uint32_t tmem_base, uint64_t ad0, uint64_t bd0, uint32_t acc) {
     if constexpr (I < MmaList<V>::n) {
         constexpr MmaOp o = MmaList<V>::ops[I];
-        umma_i8(tmem_base + (uint32_t)o.col0, ad0 + (uint64_t)(o.plane * (A_TILE >> 4)),
-                bd0 + (uint64_t)((o.brow0 >> 3) * (SBO >> 4)), idesc(o.n), acc);
+        umma_i8_coll<o.coll>(tmem_base + (uint32_t)o.col0, ad0 + (uint64_t)(o.plane * (A_TILE >> 4)),
+                             bd0 + (uint64_t)((o.brow0 >> 3) * (SBO >> 4)), idesc(o.n), acc);
         issue_list<V, I + 1>(tmem_base, ad0, bd0, acc);
     }
 }
@@ -643,6 +685,98 @@ __global__ void __launch_bounds__(64, 1) i8_mma_list_kernel(int kblocks, long lo
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (warp == 0) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+    }
+}
+
+// The same lists inside the kernels' two-stage pipeline: warp 0 refills the stage the MMAs are not reading with
+// `planes` digit planes of both operands (cp.async.bulk from an L2-resident scratch buffer; 0 = no copies, the barrier
+// is completed by a plain arrive), warp 1 issues list V on the other stage.  No epilogue, no tiles: the difference to
+// i8_mma_list_kernel is exactly the fill traffic into shared memory and the stage hand-over.
+template <int V>
+__global__ void __launch_bounds__(64, 1) i8_mma_pipe_kernel(int kblocks, int planes, const uint8_t* __restrict__ src,
+                                                           long src_bytes, long long* __restrict__ cycles) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES];
+    __shared__ uint32_t tmem_base_s;
+    const int warp = threadIdx.x >> 5;
+    for (int e = threadIdx.x; e < (int)(STAGES * STAGE_BYTES / 16); e += blockDim.x) {
+        uint32_t w[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            uint32_t x = (uint32_t)(e * 4 + q) * 2654435761u + blockIdx.x * 40503u + 12345u;
+            x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+            w[q] = x;
+        }
+        reinterpret_cast<uint4*>(smem)[e] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)),
+                     "r"(TMEM_COLS)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = tmem_base_s;
+    if (warp == 0) {
+        const long span = src_bytes - (long)STAGE_BYTES;
+        long off = ((long)blockIdx.x * 7919 * 4096) % span;
+        for (int it = 0; it < kblocks; ++it) {
+            const int s = it % STAGES;
+            if (it >= STAGES) mbar_wait(&empty_bar[s], ((it / STAGES) - 1) & 1);
+            if (elect_one()) {
+                uint8_t* st = smem + (size_t)s * STAGE_BYTES;
+                if (planes == 0) {
+                    mbar_arrive(&full_bar[s]);
+                } else {
+                    mbar_expect_tx(&full_bar[s], planes * (A_TILE + B_TILE));
+                    for (int sl = 0; sl < planes; ++sl) {
+                        bulk_g2s(st + sl * A_TILE, src + off + (size_t)sl * A_TILE, A_TILE, &full_bar[s]);
+                        bulk_g2s(st + S * A_TILE + sl * B_TILE, src + off + S * A_TILE + (size_t)sl * B_TILE, B_TILE,
+                                 &full_bar[s]);
+                    }
+                }
+            }
+            __syncwarp();
+            off = (off + 196608) % span;  // span is a multiple of 4096: every copy stays 16-byte aligned
+        }
+    } else {
+        const uint64_t ko = (uint64_t)((2 * LBO) >> 4);
+        long long t0 = 0;
+        for (int it = 0; it < kblocks; ++it) {
+            const int s = it % STAGES;
+            mbar_wait(&full_bar[s], (it / STAGES) & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            if (it == 4) t0 = clock64();
+            const uint32_t a0 = smem_u32(smem + (size_t)s * STAGE_BYTES);
+            const uint64_t ad0 = make_desc(a0);
+            const uint64_t bd0 = make_desc(a0 + S * A_TILE);
+            if (elect_one()) {
+                issue_list<V>(tmem_base, ad0, bd0, it > 0 ? 1u : 0u);
+                issue_list<V>(tmem_base, ad0 + ko, bd0 + ko, 1u);
+                umma_commit(&empty_bar[s]);
+            }
+            __syncwarp();
+        }
+        // the last commits: every MMA has retired once both stages are "empty" again
+        for (int it = kblocks - STAGES; it < kblocks; ++it) mbar_wait(&empty_bar[it % STAGES], (it / STAGES) & 1);
+        const long long t1 = clock64();
+        if (threadIdx.x == 32) cycles[blockIdx.x] = t1 - t0;
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 1) {
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
     }
 }
