@@ -209,6 +209,15 @@ int tb200_factor_append(const double* x_new, double* XsT, double* Linv, double* 
 int tb200_alpha_lml(const double* y_n, int n, const double* Linv, const double* Ldiag, double* alpha, double* lml,
                     void* work, size_t work_bytes, void* stream);
 
+/* tb200_alpha_lml without a workspace and without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, serving loops, harnesses
+ * that forbid it).  The scratch vectors live in a file-scope device array of the library (512.5 KB per GPU that loads
+ * it, held until exit); n <= 16384, larger n is rejected with an error (use tb200_alpha_lml).  Same results as
+ * tb200_alpha_lml.  Every call on a device shares that array: calls that overlap on the GPU (different streams) race;
+ * calls on one stream are safe back to back. */
+int tb200_alpha_lml_static(const double* y_n, int n, const double* Linv, const double* Ldiag, double* alpha, double* lml,
+                           void* stream);
+
 /* Per-epilogue-CTA running bests (value, global index; index -1 = unused) of the last tb200_acquire(_i8) call that
  * used `work`: tb200_acquire_local_best_count(batch, n) distinct good candidates, the starting points of the gradient
  * polish (the reference's `start_from_best` best random samples, auxiliary_optimisers.py:73-75). */

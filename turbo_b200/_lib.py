@@ -81,6 +81,7 @@ _SIGNATURES = {
     "tb200_factor_append": (C.c_int, [_P, _P, _P, _P, C.c_int, C.POINTER(KernelSpecC), _P, C.c_double, _P, _P,
                                       C.c_size_t, _P]),
     "tb200_alpha_lml": (C.c_int, [_P, C.c_int, _P, _P, _P, _P, _P, C.c_size_t, _P]),
+    "tb200_alpha_lml_static": (C.c_int, [_P, C.c_int, _P, _P, _P, _P, _P]),
     "tb200_acquire_local_best_count": (C.c_int, [C.c_int64, C.c_int]),
     "tb200_acquire_local_bests": (C.c_int, [_P, C.c_int, C.c_int, C.c_int64, C.c_int, _P, _P, _P]),
     "tb200_acquire_grad_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),

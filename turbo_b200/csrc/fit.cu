@@ -1408,6 +1408,43 @@ int tb200_alpha_lml(const double* y_n, int n, const double* Linv, const double* 
     return 0;
 }
 
+// tb200_alpha_lml for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid
+// cudaMalloc): the same kernels, with the scratch vectors in a file-scope device array instead of a caller workspace.
+// No counterpart in the reference.  The array is held by every GPU that
+// loads the library until exit (512.5 KB).  All calls on a device share it: calls that overlap on the GPU race.
+// Everything in it is rewritten by each call before it is read (ypad, z, logdet by their kernels, the info word by the
+// memset below), so the previous call's contents never matter.
+constexpr int ALPHA_LML_STATIC_MAX_N = 16384;
+constexpr size_t ALPHA_LML_STATIC_BYTES = 4 * (sizeof(double) * ALPHA_LML_STATIC_MAX_N) + 512;
+static __device__ __align__(256) unsigned char g_alpha_lml_scratch[ALPHA_LML_STATIC_BYTES];
+// In host code the array's name is a host-side stand-in, not a device address: the address is resolved once per
+// device, with that device current.
+static void* g_alpha_lml_scratch_ptr[tb200::MAX_DEVICES] = {};
+static std::mutex g_alpha_lml_scratch_mutex;
+
+int tb200_alpha_lml_static(const double* y_n, int n, const double* Linv, const double* Ldiag, double* alpha, double* lml,
+                           void* stream) {
+    TB_CHECK(n >= 1, "n must be >= 1");
+    TB_CHECK(n <= ALPHA_LML_STATIC_MAX_N,
+             "tb200_alpha_lml_static: n above 16384, the limit of the built-in scratch (use tb200_alpha_lml with a workspace)");
+    TB_CHECK(tb200_append_workspace_bytes(n) <= ALPHA_LML_STATIC_BYTES, "tb200_alpha_lml_static: scratch too small");
+    int dev = 0;
+    TB_CUDA(cudaGetDevice(&dev));
+    TB_CHECK(dev >= 0 && dev < tb200::MAX_DEVICES, "device ordinal out of range");
+    void* ptr = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_alpha_lml_scratch_mutex);
+        if (!g_alpha_lml_scratch_ptr[dev]) {
+            void* q = nullptr;
+            TB_CUDA(cudaGetSymbolAddress(&q, g_alpha_lml_scratch));
+            TB_CHECK(q != nullptr, "tb200_alpha_lml_static: no device address for the scratch array");
+            g_alpha_lml_scratch_ptr[dev] = q;
+        }
+        ptr = g_alpha_lml_scratch_ptr[dev];
+    }
+    return tb200_alpha_lml(y_n, n, Linv, Ldiag, alpha, lml, ptr, ALPHA_LML_STATIC_BYTES, stream);
+}
+
 int tb200_dgemm(int ta, int tb, int M, int N, int K, double alpha, const double* A, int lda, const double* B, int ldb,
                 double beta, double* C, int ldc, void* stream) {
     TB_CHECK(M > 0 && N > 0 && K > 0 && M % G_TM == 0 && N % G_TN == 0 && K % G_TK == 0,
