@@ -706,6 +706,100 @@ __global__ void __launch_bounds__(256) slice_operand_kernel(const double* __rest
 }
 
 // ---------------------------------------------------------------------------------------------
+// Recursive inverse of the factor (trtri_batched_i8): helpers.  Maxima are kept as upper bounds of the HIGH WORD of a
+// non-negative double (order-preserving as an unsigned integer: atomicMax / redux work on 32 bits); the GEMM epilogues
+// update them (ozaki_gemm.cuh), these kernels seed them and turn them into power-of-two scales.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned abs_hi_word(double v) {
+    const unsigned hw = (unsigned)__double2hiint(v) & 0x7fffffffu;
+    return hw >= 0x7ff00000u ? 0u : hw;  // NaN / Inf never enters a scale
+}
+
+// Linv diagonal tiles <- Dinv blocks (everything else of Linv was zeroed), and the row / column maxima of every block
+// (the level-0 operands of the recursion).  256 threads: thread = column j (two threads per column), rows alternate.
+__global__ void __launch_bounds__(256) place_diag_blocks_max_kernel(const double* __restrict__ Dinv, long strideD,
+                                                                    double* __restrict__ Linv, int NP,
+                                                                    unsigned* __restrict__ rowmax32,
+                                                                    unsigned* __restrict__ colmax32) {
+    const int kb = blockIdx.x, r = blockIdx.y, lane = threadIdx.x & 31;
+    const double* D = Dinv + (long)r * strideD + (long)kb * TILE * TILE;
+    double* out = Linv + (long)r * NP * NP + (long)kb * TILE * NP + (long)kb * TILE;
+    unsigned cm = 0;
+    for (int e = threadIdx.x; e < TILE * TILE; e += 256) {
+        const int i = e >> 7, j = e & 127;
+        const double v = D[e];
+        out[(long)i * NP + j] = v;
+        const unsigned hw = abs_hi_word(v);
+        cm = hw > cm ? hw : cm;
+        const unsigned rm = __reduce_max_sync(0xffffffffu, hw);  // the warp holds 32 consecutive columns of row i
+        if (lane == 0 && rm > 0) atomicMax(rowmax32 + (size_t)r * NP + kb * TILE + i, rm + 1);
+    }
+    if (cm > 0) atomicMax(colmax32 + (size_t)r * NP + kb * TILE + (threadIdx.x & 127), cm + 1);
+}
+
+// power-of-two covers of high-word maxima: out[e] = 2^k with 0.98 * 2^k >= max (1 where nothing was recorded)
+__global__ void cover32_kernel(const unsigned* __restrict__ hi32, long total, double* __restrict__ out) {
+    const long e = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e < total) out[e] = pow2_cover(__hiloint2double((int)hi32[e], 0));
+}
+
+// Digit planes of the operands of one recursion level (pairs of diagonal blocks A, C of h64 64-tiles, see
+// GemmI8Params::recur), written into the ONE plane buffer of the fit at tile (operand row / 64, k-block):
+//   MODE 0: rows of inv(C)      operand row = matrix row i in C,    k in C, k-block <= tile of i   scale = row cover
+//   MODE 1: columns of inv(A)   operand row = matrix column j in A, k in A, k-block >= tile of j   scale = column cover
+//   MODE 2: columns of T        operand row = matrix column j in A, k in C                         scale = cover of T's columns
+// The three regions and the planes of the rows of L (strictly below the diagonal blocks, written by the factorisation
+// and read by the first product of the level) never overlap within a level: rows of L and of inv(C) lie below or on
+// the diagonal, column operands above or on it, and A and C are different diagonal blocks.
+// One warp = 8 operand rows x 64 of K, as in slice_operand_kernel.
+template <int MODE>
+__global__ void __launch_bounds__(256) slice_level_kernel(const double* __restrict__ M, int NP, long mStride,
+                                                          const double* __restrict__ scale, int h64, int npairs,
+                                                          uint8_t* __restrict__ out, long sliceStride,
+                                                          long restartStride, int kblks) {
+    const int lane = threadIdx.x & 31;
+    const long piece = (long)blockIdx.x * 8 + (threadIdx.x >> 5);
+    const long per = (long)(8 * h64) * h64;  // row groups x k-blocks of one pair
+    if (piece >= per * npairs) return;
+    const int pr = (int)(piece / per), q = (int)(piece - (long)pr * per);
+    const int lrg = q / h64, lkb = q - lrg * h64;
+    const int a0 = 2 * pr * h64, c0 = a0 + h64;
+    const int rg = (MODE == 0 ? c0 : a0) * 8 + lrg;  // operand row group (8 rows)
+    const int kb = (MODE == 1 ? a0 : c0) + lkb;
+    if (rg * 8 >= NP || kb >= kblks) return;          // C cut short by the end of the matrix
+    if (MODE == 0 && kb > rg / 8) return;             // inv(C) is lower triangular
+    if (MODE == 1 && kb < rg / 8) return;
+    const int rs = blockIdx.y;
+    const int orow = rg * 8 + (lane & 7);
+    const int k0 = kb * 64 + (lane >> 3) * 16;
+    const double* src = M + (size_t)rs * mStride;
+    const double inv = 1.0 / scale[(size_t)rs * NP + orow];  // exact: power of two
+    uint32_t lo[16], hi[16];
+#pragma unroll
+    for (int u = 0; u < 16; ++u) {
+        const double v = MODE == 0 ? src[(size_t)orow * NP + k0 + u] : src[(size_t)(k0 + u) * NP + orow];
+        const unsigned long long y = fit_slice_signed(v * inv);
+        lo[u] = (uint32_t)y;
+        hi[u] = (uint32_t)(y >> 32);
+    }
+    const size_t off = (size_t)rs * restartStride + ((size_t)(orow / 64) * kblks + kb) * i8::B_TILE +
+                       (size_t)((orow % 64) >> 3) * i8::SBO + (lane >> 3) * i8::LBO + (lane & 7) * 16;
+#pragma unroll
+    for (int sl = 0; sl < i8::S; ++sl) {
+        const int byte = (sl < 3) ? 2 - sl : 6 - sl;
+        uint32_t w[4];
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+            const uint32_t* srcw = (sl < 3) ? hi : lo;
+            const uint32_t p01 = __byte_perm(srcw[4 * v], srcw[4 * v + 1], byte | ((4 + byte) << 4));
+            const uint32_t p23 = __byte_perm(srcw[4 * v + 2], srcw[4 * v + 3], byte | ((4 + byte) << 4));
+            w[v] = __byte_perm(p01, p23, 0x5410);
+        }
+        *reinterpret_cast<uint4*>(out + (size_t)sl * sliceStride + off) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // incremental refit: append one training point to a factor at fixed hyper-parameters
 //   L' = [[L, 0], [l^T, lam]],  l = L^-1 k,  lam^2 = k(x,x) + jitter - l.l
 //   L'^-1 = [[L^-1, 0], [-(L^-T l)^T / lam, 1 / lam]]
@@ -794,7 +888,9 @@ struct FitBuffers {
     unsigned long long* tmax;  // [R][NP] column maxima of X = L^-1 (bits of a double), trtri recurrence
     unsigned long long* smax;  // [R][NP] column maxima of the weighted L panels
     double* sigma;   // [R][NP] power-of-two scales of the weighted L panels
-    uint8_t* bpanel; // [R][7][2][NP/64][4096] byte slices of one weighted L panel (B operand of the trtri step)
+    uint8_t* bpanel; // unused since the recursive inverse (kept so that the workspace size is unchanged)
+    double* colcov;  // [R][NP] power-of-two column scales of the inverse factor so far (recursive inverse)
+    double* rowcov;  // [R][NP] ... row scales
     mutable i8::SchedPool sched;  // scheduler counters of the persistent INT8 GEMM launches (zeroed per fit call)
 };
 
@@ -873,15 +969,19 @@ size_t fit_workspace_layout(int n, int d, int R, int p, bool own_linv, bool own_
     }
     unsigned long long* tmax = nullptr; unsigned long long* smax = nullptr; double* sigma = nullptr; uint8_t* bpanel = nullptr;
     unsigned* sched = nullptr;
+    double* colcov = nullptr; double* rowcov = nullptr;
     if (i8fit) {
         tmax = reinterpret_cast<unsigned long long*>(take(sizeof(double) * R * NP));
         smax = reinterpret_cast<unsigned long long*>(take(sizeof(double) * R * NP));
         sigma = take(sizeof(double) * R * NP);
         bpanel = reinterpret_cast<uint8_t*>(take((size_t)i8::S * R * 2 * (NP / i8::KB) * i8::B_TILE));
         sched = reinterpret_cast<unsigned*>(take(sizeof(unsigned) * 2 * i8::SCHED_POOL));
+        colcov = take(sizeof(double) * R * NP);
+        rowcov = take(sizeof(double) * R * NP);
     }
     if (fb) {
         fb->sched.base = sched; fb->sched.next = 0;
+        fb->colcov = colcov; fb->rowcov = rowcov;
         fb->sliced = sliced; fb->scale = scale; fb->tmax = tmax; fb->smax = smax; fb->sigma = sigma; fb->bpanel = bpanel;
         fb->K = K; fb->Linv = Linv; fb->Dinv = Dinv; fb->XsT = XsT; fb->ypad = ypad; fb->z = z;
         fb->alpha = alpha; fb->logdet = logdet; fb->partial = partial;
@@ -1085,82 +1185,65 @@ __global__ void __launch_bounds__(256) place_diag_blocks_kernel(const double* __
     }
 }
 
-// Linv = L^-1 on the INT8 tensor cores, block column by block column from the right:
-//   X[i,c] = -( sum_{k=c+1..i} X[i,k] L[k,c] ) Dinv_c      (i > c; X[c,c] = Dinv_c)
-// Every X block column to the right of c is complete, so its column maxima t_k are known: the A operand is
-// X[i,k] / t_k (|.| <= 0.98, sliced once per block column as it completes) and the weight moves into the B operand
-// L[k,c] * t_k, a 128-column panel that is sliced (transposed, with its own column scales sigma) per step.
-// All scalings are powers of two, so the product is exact to the kept slice pairs as in ozaki_gemm.cuh.
+// Linv = L^-1 on the INT8 tensor cores by RECURSIVE DOUBLING (round 2; round 1 walked the block columns from the right:
+// 31 dependent steps of 8 launches at n = 4096, most of them latency-bound, 6.0 of the 14.7 ms of an LML+gradient
+// evaluation at 8 restarts).  The inverses of the 128x128 diagonal blocks are there (Dinv).  Level h = 128, 256, ...:
+// the matrix is cut into pairs of neighbouring diagonal blocks A, C of size h (C possibly cut short by the matrix
+// end) with B = L[C, A] between them, and
+//        inv [[A, 0], [B, C]] = [[inv A, 0], [-inv(C) B inv(A), inv C]]
+// so every pair needs two products,  T = B inv(A)  and  X = -inv(C) T,  and ALL pairs of a level and all restarts run in
+// the same two launches: log2(n / 128) levels of ~8 launches instead of n / 128 steps.  The flop count is the one of
+// the column recurrence (n^3 / 3): the triangular shape of inv(A) and inv(C) is used through the k-ranges.
+// Operands (all in the ONE plane buffer, slice_level_kernel): rows of L -- sliced by the factorisation with their a-priori
+// scale sqrt(K_rr), each block B is read by exactly one level; columns of inv(A), rows of inv(C), columns of T -- sliced
+// per level with the power-of-two cover of their current maxima, which the GEMM epilogues keep up to date (running row
+// and column maxima of the inverse; T's column maxima per level), so no pass over the matrix measures anything.
+// All scalings are powers of two: nothing is rounded outside the kept slice pairs, as in ozaki_gemm.cuh.
+// On exit fb.scale holds the column covers of Linv -- the operand scaling of the K^-1 = Linv^T Linv step that follows.
 static int trtri_batched_i8(const FitBuffers& fb, double* Linv, int NP, int R, cudaStream_t st) {
     const int NB = NP / TILE, kblks = NP / i8::KB;
     const long sK = (long)NP * NP, sD = (long)NB * TILE * TILE;
-    const long bSlice = (long)2 * kblks * i8::B_TILE, bRestart = (long)i8::S * bSlice;
+    const long total = (long)R * NP;
+    // high-word maxima: columns / rows of the inverse so far, columns of T (the two 8-byte arrays of round 1 hold them)
+    unsigned* colmax32 = reinterpret_cast<unsigned*>(fb.tmax);
+    unsigned* rowmax32 = colmax32 + total;
+    unsigned* tmax32 = reinterpret_cast<unsigned*>(fb.smax);
+    double* tcov = fb.sigma;
     TB_CUDA(cudaMemsetAsync(Linv, 0, sizeof(double) * (size_t)R * NP * NP, st));
-    TB_LAUNCH(place_diag_blocks_kernel, dim3(NB, R), dim3(256), 0, st, fb.Dinv, sD, Linv, NP);
-    TB_CUDA(cudaMemsetAsync(fb.tmax, 0, sizeof(double) * (size_t)R * NP, st));
-    TB_CUDA(cudaMemsetAsync(fb.smax, 0, sizeof(double) * (size_t)R * NP, st));
-    const double* none = nullptr;
-    double* tsc = fb.scale;  // column scales t_k of X as doubles (fb.scale is free between potrf and the K^-1 step)
-    // the byte slices of the finished X block column and the weighted L panel of this step only share their inputs:
-    // the former runs on the look-ahead stream next to the latter's column maxima, scales and slices
-    FitStreams* ov = nullptr;
-    if (fit_streams_for_device(&ov)) ov = nullptr;
-    for (int c = NB - 2; c >= 0; --c) {
-        const int c1 = c + 1, rem = NB - c1;
-        // column scales of the finished block column c1 of X, then its byte slices (rows >= c1*128, k-blocks 2c1, 2c1+1)
-        TB_LAUNCH(colmax_bits_kernel, dim3(rem, R), dim3(128), 0, st, Linv, NP, sK, c1 * TILE, c1 * TILE, none, fb.tmax);
-        TB_LAUNCH(cover_kernel, dim3(R), dim3(128), 0, st, fb.tmax, NP, c1 * TILE, tsc);
-        {
-            const int rg0 = c1 * (TILE / 8), rg1 = NP / 8;
-            const long pieces = (long)(rg1 - rg0) * 2;
-            cudaStream_t ss = st;
-            if (ov) {
-                TB_CUDA(cudaEventRecord(ov->fork_look, st));
-                TB_CUDA(cudaStreamWaitEvent(ov->look, ov->fork_look, 0));
-                ss = ov->look;
-            }
-            TB_LAUNCH(slice_operand_kernel<false>, dim3((unsigned)((pieces + 7) / 8), R), dim3(256), 0, ss, Linv, NP, sK,
-                      none, (const double*)tsc, 2, rg0, rg1, 2 * c1, 2 * c1 + 2, 0, 0, fb.sliced, sK, (long)i8::S * sK,
-                      kblks);
-            if (ov) TB_CUDA(cudaEventRecord(ov->look_done, ov->look));
-        }
-        // weighted panel L[k, c-block] * t_k (k >= c1*128): column scales, then transposed byte slices
-        TB_LAUNCH(colmax_bits_kernel, dim3(rem, R), dim3(128), 0, st, fb.K, NP, sK, c * TILE, c1 * TILE,
-                  (const double*)tsc, fb.smax);
-        TB_LAUNCH(cover_kernel, dim3(R), dim3(128), 0, st, fb.smax, NP, c * TILE, fb.sigma);
-        {
-            const int rg0 = c * (TILE / 8), rg1 = rg0 + TILE / 8;
-            const long pieces = (long)(rg1 - rg0) * (kblks - 2 * c1);
-            TB_LAUNCH(slice_operand_kernel<true>, dim3((unsigned)((pieces + 7) / 8), R), dim3(256), 0, st, fb.K, NP, sK,
-                      (const double*)fb.sigma, (const double*)tsc, 1, rg0, rg1, 2 * c1, kblks, 0, c * TILE, fb.bpanel,
-                      bSlice, bRestart, kblks);
-        }
-        // T[i, c-block] = -sum_k (X[i,k]/t_k) (L[k,c] t_k), rows of block rows c1.., k-blocks [2c1, 2(it+1))
-        if (ov) TB_CUDA(cudaStreamWaitEvent(st, ov->look_done, 0));
-        {
-            i8::GemmI8Params g{};
-            g.S = fb.sliced; g.restartStride = (long)i8::S * sK; g.sliceStride = sK;
-            g.scale = nullptr; g.scaleStride = NP;
-            g.SB = fb.bpanel; g.restartStrideB = bRestart; g.sliceStrideB = bSlice; g.scaleB = fb.sigma;
-            g.C = Linv; g.ldc = NP; g.cStride = sK;
-            g.kblks = kblks; g.tri = 0;
-            g.rowTile0 = c1; g.colTile0 = 2 * c; g.nColTiles = 2; g.kbLo = 2 * c1; g.kbHi = kblks; g.kbHiByRow = 1;
-            g.alpha = -1.0; g.beta = 0.0;
-            if (launch_fit_gemm_i8(fb, g, rem * 2, R, st, FIT_TRTRI)) return -1;
-        }
-        // X[i, c-block] = T[i, c-block] * Dinv_c  (in place, 128-deep DMMA GEMM)
-        {
-            double* col = Linv + (long)c1 * TILE * NP + (long)c * TILE;
-            GemmParams p = gemm_params(col, NP, fb.Dinv + (long)c * TILE * TILE, TILE, col, NP, rem, 1, TILE, 1.0, 0.0);
-            p.sA1 = sK; p.sB1 = sD; p.sC1 = sK;
-            p.b_tri = 2;  // X[i,j] = sum_{k>=j} T[i,k] Dinv_c[k,j]
-            if (launch_gemm<false, false>(p, R, 1, st)) return -1;
-        }
+    TB_CUDA(cudaMemsetAsync(fb.tmax, 0, sizeof(double) * (size_t)total, st));
+    TB_LAUNCH(place_diag_blocks_max_kernel, dim3(NB, R), dim3(256), 0, st, fb.Dinv, sD, Linv, NP, rowmax32, colmax32);
+    const unsigned cgrid = (unsigned)((total + 255) / 256);
+    for (int h64 = 2; h64 < kblks; h64 *= 2) {
+        const int npairs = (kblks - h64 + 2 * h64 - 1) / (2 * h64);  // pairs whose C is not empty: (2p+1) h64 < kblks
+        const long pieces = (long)(8 * h64) * h64 * npairs;
+        const dim3 sgrid((unsigned)((pieces + 7) / 8), R);
+        const int ntiles = npairs * (h64 / 2) * h64;
+        TB_LAUNCH(cover32_kernel, dim3(cgrid), dim3(256), 0, st, colmax32, total, fb.colcov);
+        TB_LAUNCH(cover32_kernel, dim3(cgrid), dim3(256), 0, st, rowmax32, total, fb.rowcov);
+        TB_LAUNCH(slice_level_kernel<1>, sgrid, dim3(256), 0, st, Linv, NP, sK, fb.colcov, h64, npairs, fb.sliced, sK,
+                  (long)i8::S * sK, kblks);
+        TB_LAUNCH(slice_level_kernel<0>, sgrid, dim3(256), 0, st, Linv, NP, sK, fb.rowcov, h64, npairs, fb.sliced, sK,
+                  (long)i8::S * sK, kblks);
+        TB_CUDA(cudaMemsetAsync(tmax32, 0, sizeof(unsigned) * (size_t)total, st));
+        i8::GemmI8Params g{};
+        g.S = fb.sliced; g.restartStride = (long)i8::S * sK; g.sliceStride = sK;
+        g.scaleStride = NP;
+        g.C = Linv; g.ldc = NP; g.cStride = sK;
+        g.kblks = kblks; g.tri = 0; g.h64 = h64;
+        g.beta = 0.0;
+        // T = L[C, A] inv(A), written where X will be
+        g.recur = 1; g.scale = fb.scale; g.scaleB = fb.colcov; g.alpha = 1.0;
+        g.rowmax32 = nullptr; g.colmax32 = tmax32;
+        if (launch_fit_gemm_i8(fb, g, ntiles, R, st, FIT_TRTRI)) return -1;
+        TB_LAUNCH(cover32_kernel, dim3(cgrid), dim3(256), 0, st, tmax32, total, tcov);
+        TB_LAUNCH(slice_level_kernel<2>, sgrid, dim3(256), 0, st, Linv, NP, sK, tcov, h64, npairs, fb.sliced, sK,
+                  (long)i8::S * sK, kblks);
+        // X = -inv(C) T
+        g.recur = 2; g.scale = fb.rowcov; g.scaleB = tcov; g.alpha = -1.0;
+        g.rowmax32 = rowmax32; g.colmax32 = colmax32;
+        if (launch_fit_gemm_i8(fb, g, ntiles, R, st, FIT_TRTRI)) return -1;
     }
-    // the recurrence never needed the scales of block column 0; with them fb.scale holds the power-of-two cover of
-    // every column maximum of X, which is exactly the operand scaling of the K^-1 = X^T X step that follows
-    TB_LAUNCH(colmax_bits_kernel, dim3(NB, R), dim3(128), 0, st, Linv, NP, sK, 0, 0, none, fb.tmax);
-    TB_LAUNCH(cover_kernel, dim3(R), dim3(128), 0, st, fb.tmax, NP, 0, tsc);
+    TB_LAUNCH(cover32_kernel, dim3(cgrid), dim3(256), 0, st, colmax32, total, fb.scale);
     return 0;
 }
 

@@ -35,6 +35,16 @@ struct GemmI8Params {
     // a window that does not contain the start of the CTA's range accumulates onto C (beta = 1) instead of applying
     // the caller's beta.  kbWinHi = 0: no window.
     int kbWinLo, kbWinHi;
+    // Recursive inverse of the triangular factor (fit.cu trtri_batched_i8), level h = 64 * h64: the matrix is cut into
+    // pairs of diagonal blocks (A = tiles [2p h64, (2p+1) h64), C = the next h64 tiles, possibly cut short by the matrix
+    // end); tile set = rows of C x columns of A of every pair.  recur = 1: T = L[C,A] inv(A), k over A from the column
+    // tile on (inv(A) is lower triangular); recur = 2: X = -inv(C) T, k over C up to the row tile.  0: off.
+    int recur, h64;
+    // optional running maxima of |C| after this launch, as upper bounds of the HIGH WORD of the double (exponent + 20
+    // mantissa bits, rounded up: all a power-of-two cover needs), one per output row / column; atomicMax, so the caller
+    // zeroes them.  Written only by the launch (k-window) that completes a tile.
+    unsigned* rowmax32;
+    unsigned* colmax32;
     int ntiles, R;         // tiles per restart and restarts (filled by launch_gemm_i8)
     unsigned* sched;       // [2] tile counter + finished-CTA counter of this launch (zero at launch, left zero)
 };
@@ -43,13 +53,29 @@ struct GemmI8Params {
 // scheduler ends a launch on its cheapest tiles) -> restart, row tile, column tile, k-range and beta
 struct GemmTile {
     int rs, it, jt, kb_lo, nkb;
+    bool final;  // this launch's k-window reaches the end of the tile's k-range: C holds the finished value afterwards
     double beta;
 };
 __device__ __forceinline__ GemmTile gemm_tile(const GemmI8Params& p, int t) {
     GemmTile g;
     g.rs = t / p.ntiles;
     int bx = t - g.rs * p.ntiles, kb_hi;
-    if (p.tri) {
+    if (p.recur) {
+        const int per = (p.h64 / 2) * p.h64;  // tiles of one pair: h64/2 row tiles of 128 x h64 column tiles of 64
+        const int pr = bx / per, q = bx - pr * per;
+        const int a0 = 2 * pr * p.h64, c0 = a0 + p.h64;  // first 64-tile of A and of C
+        g.it = c0 / 2 + q / p.h64;
+        g.jt = a0 + q % p.h64;
+        if (2 * g.it >= p.kblks) {  // C is cut short by the end of the matrix
+            g.kb_lo = kb_hi = 0;
+        } else if (p.recur == 1) {
+            g.kb_lo = g.jt;
+            kb_hi = c0;
+        } else {
+            g.kb_lo = c0;
+            kb_hi = 2 * (g.it + 1);
+        }
+    } else if (p.tri) {
         // heavy tiles first: the k-range [2*it, kblks) shrinks with it
         g.it = 0;
         while (bx >= 2 * g.it + 2) { bx -= 2 * g.it + 2; ++g.it; }
@@ -66,9 +92,10 @@ __device__ __forceinline__ GemmTile gemm_tile(const GemmI8Params& p, int t) {
         kb_hi = p.kbHiByRow ? 2 * (g.it + 1) : p.kbHi;
     }
     g.beta = p.beta;
+    g.final = true;
     if (p.kbWinHi > 0) {
         if (g.kb_lo < p.kbWinLo) { g.kb_lo = p.kbWinLo; g.beta = 1.0; }
-        if (kb_hi > p.kbWinHi) kb_hi = p.kbWinHi;
+        if (kb_hi > p.kbWinHi) { kb_hi = p.kbWinHi; g.final = false; }
     }
     g.nkb = kb_hi - g.kb_lo;
     return g;
@@ -216,6 +243,8 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_i8_kernel(const GemmI8Params 
             double* crow = p.C + (size_t)g.rs * p.cStride + (size_t)row * p.ldc + (size_t)g.jt * TN;
             const double* scol = (p.scaleB ? p.scaleB : p.scale) + (size_t)g.rs * p.scaleStride + g.jt * TN;
             const double beta = g.beta;
+            const bool want_max = g.final && (p.rowmax32 != nullptr || p.colmax32 != nullptr);
+            unsigned rmax = 0;
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll 1
             for (int cc = 0; cc < TN / 8; ++cc) {
@@ -245,7 +274,21 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_i8_kernel(const GemmI8Params 
                 }
 #pragma unroll
                 for (int c = 0; c < 4; ++c) dst[c] = make_double2(out[2 * c], out[2 * c + 1]);
+                if (want_max) {
+                    unsigned cm = 0;
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) {
+                        unsigned hw = (unsigned)__double2hiint(out[c]) & 0x7fffffffu;
+                        if (hw >= 0x7ff00000u) hw = 0;  // NaN / Inf of a failed member never enters a scale
+                        rmax = hw > rmax ? hw : rmax;
+                        const unsigned m = __reduce_max_sync(0xffffffffu, hw);
+                        if (lane == c) cm = m;
+                    }
+                    if (p.colmax32 && lane < 8 && cm > 0)
+                        atomicMax(p.colmax32 + (size_t)g.rs * p.scaleStride + g.jt * TN + cc * 8 + lane, cm + 1);
+                }
             }
+            if (want_max && p.rowmax32 && rmax > 0) atomicMax(p.rowmax32 + (size_t)g.rs * p.scaleStride + row, rmax + 1);
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -286,13 +329,14 @@ inline int launch_gemm_i8(const GemmI8Params& p0, int ntiles, int R, SchedPool& 
     const long total = (long)ntiles * R;
     const unsigned grid = (unsigned)(total < sm_count ? total : sm_count);
     // the longest k-range any CTA of this launch can have
-    const int span = p.tri ? p.kblks : (p.kbHiByRow ? p.kblks : p.kbHi) - p.kbLo;
+    const int span = p.recur ? p.h64 : p.tri ? p.kblks : (p.kbHiByRow ? p.kblks : p.kbHi) - p.kbLo;
     if (span <= PASS_KB) {
         p.sched = pool.take();
         TB_LAUNCH((gemm_i8_kernel<GMAX>), dim3(grid), dim3(THREADS), SMEM_BYTES, stream, p);
         return 0;
     }
-    const int lo0 = p.tri ? 0 : p.kbLo, hi0 = p.tri ? p.kblks : (p.kbHiByRow ? p.kblks : p.kbHi);
+    const int lo0 = (p.tri || p.recur) ? 0 : p.kbLo;
+    const int hi0 = (p.tri || p.recur) ? p.kblks : (p.kbHiByRow ? p.kblks : p.kbHi);
     for (int w = lo0; w < hi0; w += PASS_KB) {
         GemmI8Params q = p;
         q.kbWinLo = w;
