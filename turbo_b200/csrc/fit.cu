@@ -745,7 +745,7 @@ __global__ void cover32_kernel(const unsigned* __restrict__ hi32, long total, do
 
 // Digit planes of the operands of one recursion level (pairs of diagonal blocks A, C of h64 64-tiles, see
 // GemmI8Params::recur), written into the ONE plane buffer of the fit at tile (operand row / 64, k-block):
-//   MODE 0: rows of inv(C)      operand row = matrix row i in C,    k in C, k-block <= tile of i   scale = row cover
+//   MODE 0: rows of inv(C)      operand row = matrix row i in C,    k in C, k-block <= 128-row tile of i  scale = row cover
 //   MODE 1: columns of inv(A)   operand row = matrix column j in A, k in A, k-block >= tile of j   scale = column cover
 //   MODE 2: columns of T        operand row = matrix column j in A, k in C                         scale = cover of T's columns
 // The three regions and the planes of the rows of L (strictly below the diagonal blocks, written by the factorisation
@@ -767,7 +767,9 @@ __global__ void __launch_bounds__(256) slice_level_kernel(const double* __restri
     const int rg = (MODE == 0 ? c0 : a0) * 8 + lrg;  // operand row group (8 rows)
     const int kb = (MODE == 1 ? a0 : c0) + lkb;
     if (rg * 8 >= NP || kb >= kblks) return;          // C cut short by the end of the matrix
-    if (MODE == 0 && kb > rg / 8) return;             // inv(C) is lower triangular
+    // inv(C) is lower triangular; the GEMM reads its A operand in 128-row tiles up to the k-block of the tile's LAST
+    // row, so the zero 64x64 piece right of the diagonal in the upper half of a tile is sliced too
+    if (MODE == 0 && kb > 2 * (rg / 16) + 1) return;
     if (MODE == 1 && kb < rg / 8) return;
     const int rs = blockIdx.y;
     const int orow = rg * 8 + (lane & 7);
