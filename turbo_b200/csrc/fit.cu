@@ -176,6 +176,10 @@ constexpr size_t DIAG_SMEM = (size_t)(DB * DLD + DB * (DB + 1) / 2 + DB + DP * (
 //            diagonal kept from the factorisation.  A warp (8 columns) needs no barrier.
 // LAPACK dpotf2 scales by the reciprocal pivot as well.  Measured: 85.7 us per launch (164 K warp instructions per CTA,
 // IPC 1.0); what is left is the serial 8x8 factorisation of each panel and the short late panels.
+// A/B of round 2 (tools/gpu_round2_o.sh): the same kernel with S column-major and the eight pivot entries fetched as four
+// 16-byte loads was SLOWER (LML+gradient at 8 restarts 11.9 -> 12.4 ms with row stride 132, 13.3 ms with 136): a 16-byte
+// shared-memory load is served a quarter-warp at a time, so four of them cost more wavefronts than eight 8-byte
+// broadcasts.  The row-major layout below stays.
 __device__ __forceinline__ double diag_group_sum(double v) {
 #pragma unroll
     for (int o = DT / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -600,57 +604,15 @@ __global__ void rowscale_from_diag_kernel(const double* __restrict__ K, int NP, 
     scale[(size_t)rs * NP + r] = pow2_cover(sqrt(fabs(dg)));
 }
 
-// column maxima of |M[r, c] * kmul(r)| for columns [col0, col0+128) over rows [row0, NP), kept as the bit pattern of a
-// non-negative double (order-preserving as an integer, so atomicMax works); `out` must be zero beforehand.
-// kscale != NULL: row r is weighted by kscale[r] (the X column scale t_r of the trtri recurrence).
-__global__ void __launch_bounds__(128) colmax_bits_kernel(const double* __restrict__ M, int NP, long mStride, int col0,
-                                                          int row0, const double* __restrict__ kscale,
-                                                          unsigned long long* __restrict__ out) {
-    const int rs = blockIdx.y, c = col0 + threadIdx.x;
-    const int r_lo = row0 + blockIdx.x * 128, r_hi = min(NP, r_lo + 128);
-    const double* x = M + (size_t)rs * mStride + c;
-    double m = 0.0;
-    const double* ks = kscale ? kscale + (size_t)rs * NP : nullptr;
-    int r = r_lo;
-    for (; r + 8 <= r_hi; r += 8) {  // 8 independent loads in flight per thread
-        double v[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) v[u] = fabs(x[(size_t)(r + u) * NP]);
-        if (ks) {
-#pragma unroll
-            for (int u = 0; u < 8; ++u) v[u] *= ks[r + u];
-        }
-#pragma unroll
-        for (int u = 0; u < 8; ++u)
-            if (v[u] > m) m = v[u];  // NaN never enters
-    }
-    for (; r < r_hi; ++r) {
-        double v = fabs(x[(size_t)r * NP]);
-        if (ks) v *= ks[r];
-        if (v > m) m = v;
-    }
-    if (m > 0.0) atomicMax(out + (size_t)rs * NP + c, (unsigned long long)__double_as_longlong(m));
-}
-
-// power-of-two covers of 128 column maxima: out[c] = 2^e with 0.98 * 2^e >= max (1 for an all-zero column)
-__global__ void __launch_bounds__(128) cover_kernel(const unsigned long long* __restrict__ bits, int NP, int col0,
-                                                    double* __restrict__ out) {
-    const size_t e = (size_t)blockIdx.x * NP + col0 + threadIdx.x;
-    out[e] = pow2_cover(__longlong_as_double((long long)bits[e]));
-}
-
 // One warp = one (8 operand rows) x (64 of K) piece = 4 core matrices per slice, written as 128 contiguous bytes
 // per core matrix.  TRANSPOSED = false: operand row = matrix row, K = matrix column (rows of L / of X = L^-1);
 // TRANSPOSED = true: operand row = matrix column, K = matrix row (columns of L^-1, columns of an L panel).
 // Pieces are enumerated over operand row groups [rg0, rg1) x k-blocks [kb0, kb1); with `lower` set, pieces whose
 // k-block lies entirely before the 128-row block of the operand rows are skipped (never read by the tri GEMM).
-// Operand-row scale: `scale` (power-of-two doubles) or 1.  K-index weight: kmode 1 multiplies by kscale[k], kmode 2
-// divides by it (both exact: powers of two).  tileRow0: operand row of tile 0 of `out` (a panel buffer holds only its
-// own two 64-row tiles).
+// Operand-row scale: `scale` (power-of-two doubles) or 1.  tileRow0: operand row of tile 0 of `out`.
 template <bool TRANSPOSED>
 __global__ void __launch_bounds__(256) slice_operand_kernel(const double* __restrict__ M, int NP, long mStride,
                                                             const double* __restrict__ scale,
-                                                            const double* __restrict__ kscale, int kmode,
                                                             int rg0, int rg1, int kb0, int kb1, int lower, int tileRow0,
                                                             uint8_t* __restrict__ out, long sliceStride,
                                                             long restartStride, int kblks) {
@@ -665,24 +627,10 @@ __global__ void __launch_bounds__(256) slice_operand_kernel(const double* __rest
     const int k0 = kb * 64 + (lane >> 3) * 16;  // first of this lane's 16 K indices
     const double* src = M + (size_t)rs * mStride;
     const double inv = scale ? 1.0 / scale[(size_t)rs * NP + orow] : 1.0;  // exact: power of two
-    double kw[16];
-    if (kmode) {
-        const double4* kp = reinterpret_cast<const double4*>(kscale + (size_t)rs * NP + k0);
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            const double4 t = kp[q];
-            kw[4 * q] = t.x; kw[4 * q + 1] = t.y; kw[4 * q + 2] = t.z; kw[4 * q + 3] = t.w;
-        }
-        if (kmode == 2) {
-#pragma unroll
-            for (int q = 0; q < 16; ++q) kw[q] = 1.0 / kw[q];  // exact
-        }
-    }
     uint32_t lo[16], hi[16];
 #pragma unroll
     for (int q = 0; q < 16; ++q) {
-        double v = TRANSPOSED ? src[(size_t)(k0 + q) * NP + orow] : src[(size_t)orow * NP + k0 + q];
-        if (kmode) v *= kw[q];
+        const double v = TRANSPOSED ? src[(size_t)(k0 + q) * NP + orow] : src[(size_t)orow * NP + k0 + q];
         const unsigned long long y = fit_slice_signed(v * inv);
         lo[q] = (uint32_t)y;
         hi[q] = (uint32_t)(y >> 32);
@@ -887,10 +835,9 @@ struct FitBuffers {
     double* partial; // [R][ntiles64][p]
     uint8_t* sliced; // [R][7][NP/64][NP/64][4096]  byte slices of L rows, then of L^-1 columns (INT8 engine)
     double* scale;   // [R][NP] power-of-two row / column scales of the sliced operand
-    unsigned long long* tmax;  // [R][NP] column maxima of X = L^-1 (bits of a double), trtri recurrence
-    unsigned long long* smax;  // [R][NP] column maxima of the weighted L panels
-    double* sigma;   // [R][NP] power-of-two scales of the weighted L panels
-    uint8_t* bpanel; // unused since the recursive inverse (kept so that the workspace size is unchanged)
+    unsigned long long* tmax;  // [R][NP] 8 bytes each: running column and row maxima of the inverse (2 x 32-bit high words)
+    unsigned long long* smax;  // [R][NP] column maxima of T of the current recursion level (32-bit high words)
+    double* sigma;   // [R][NP] power-of-two column scales of T
     double* colcov;  // [R][NP] power-of-two column scales of the inverse factor so far (recursive inverse)
     double* rowcov;  // [R][NP] ... row scales
     mutable i8::SchedPool sched;  // scheduler counters of the persistent INT8 GEMM launches (zeroed per fit call)
@@ -969,14 +916,13 @@ size_t fit_workspace_layout(int n, int d, int R, int p, bool own_linv, bool own_
         sliced = reinterpret_cast<uint8_t*>(take((size_t)i8::S * R * NP * NP));
         scale = take(sizeof(double) * R * NP);
     }
-    unsigned long long* tmax = nullptr; unsigned long long* smax = nullptr; double* sigma = nullptr; uint8_t* bpanel = nullptr;
+    unsigned long long* tmax = nullptr; unsigned long long* smax = nullptr; double* sigma = nullptr;
     unsigned* sched = nullptr;
     double* colcov = nullptr; double* rowcov = nullptr;
     if (i8fit) {
         tmax = reinterpret_cast<unsigned long long*>(take(sizeof(double) * R * NP));
         smax = reinterpret_cast<unsigned long long*>(take(sizeof(double) * R * NP));
         sigma = take(sizeof(double) * R * NP);
-        bpanel = reinterpret_cast<uint8_t*>(take((size_t)i8::S * R * 2 * (NP / i8::KB) * i8::B_TILE));
         sched = reinterpret_cast<unsigned*>(take(sizeof(unsigned) * 2 * i8::SCHED_POOL));
         colcov = take(sizeof(double) * R * NP);
         rowcov = take(sizeof(double) * R * NP);
@@ -984,7 +930,7 @@ size_t fit_workspace_layout(int n, int d, int R, int p, bool own_linv, bool own_
     if (fb) {
         fb->sched.base = sched; fb->sched.next = 0;
         fb->colcov = colcov; fb->rowcov = rowcov;
-        fb->sliced = sliced; fb->scale = scale; fb->tmax = tmax; fb->smax = smax; fb->sigma = sigma; fb->bpanel = bpanel;
+        fb->sliced = sliced; fb->scale = scale; fb->tmax = tmax; fb->smax = smax; fb->sigma = sigma;
         fb->K = K; fb->Linv = Linv; fb->Dinv = Dinv; fb->XsT = XsT; fb->ypad = ypad; fb->z = z;
         fb->alpha = alpha; fb->logdet = logdet; fb->partial = partial;
     }
@@ -1145,7 +1091,7 @@ static int potrf_batched(const FitBuffers& fb, int NP, int R, int* info, cudaStr
             const int rg0 = (k + 1) * (TILE / 8), rg1 = NP / 8;
             const long pieces = (long)(rg1 - rg0) * 2;
             TB_LAUNCH(slice_operand_kernel<false>, dim3((unsigned)((pieces + 7) / 8), R), dim3(256), 0, st, fb.K, NP, sK,
-                      fb.scale, (const double*)nullptr, 0, rg0, rg1, 2 * k, 2 * k + 2, 0, 0, fb.sliced, sK,
+                      fb.scale, rg0, rg1, 2 * k, 2 * k + 2, 0, 0, fb.sliced, sK,
                       (long)i8::S * sK, NP / i8::KB);
         }
         if (rl && k + 2 < NB) {
@@ -1340,7 +1286,7 @@ static int fit_pipeline(const double* X, const double* y_n, int n, const tb200_k
             // column scales of Linv: left in fb.scale by the INT8 trtri recurrence
             const long pieces = (long)(NP / 8) * (NP / i8::KB);
             TB_LAUNCH(slice_operand_kernel<true>, dim3((unsigned)((pieces + 7) / 8), R), dim3(256), 0, st, Linv, NP, sK,
-                      fb.scale, (const double*)nullptr, 0, 0, NP / 8, 0, NP / i8::KB, 1, 0, fb.sliced, sK,
+                      fb.scale, 0, NP / 8, 0, NP / i8::KB, 1, 0, fb.sliced, sK,
                       (long)i8::S * sK, NP / i8::KB);
             i8::GemmI8Params g{};
             g.S = fb.sliced; g.restartStride = (long)i8::S * sK; g.sliceStride = sK;
