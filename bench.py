@@ -64,7 +64,7 @@ N_TRAIN, DIM = 4096, 10
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel at the headline shape, from the
 # committed `ncu --set full` captures under profiles/ (None until captured for that engine / shape)
 # profiles/r1_gemm_ncu_full.md, r1_i8v2_ncu_full.md, r2_variance_ncu_full.md (persistent kernel, 21 products)
-TRAFFIC = {"dmma": 197.2e6, "i8g8": 163.9e6, "i8g7": 124.4e6}
+TRAFFIC = {"dmma": 197.2e6, "i8g8": 163.9e6, "i8g7": 117.9e6}
 METRIC = "EI candidates/sec (n=4096,d=10)"
 KIND_RBF, KIND_MATERN52 = 0, 3
 

@@ -76,14 +76,14 @@ inline int device_once(DeviceOnce& o, F&& configure) {
 // The ONE debug hook of the library: the environment variable TB200_DEBUG, a comma-separated list of key=value pairs,
 // parsed once on first use (never on the call path afterwards; tb200_debug_reload() re-reads it for tests).
 //   fit_engine=dmma      keep the batched fit on the FP64 DMMA GEMM (the cross-check the tests compare the INT8 fit with)
-//   fit_gmax=7|8|9       slice-pair cut-off of every INT8 fit stage (default 8/8/7: potrf, trtri, K^-1)
-//   fit_gmax_trtri=..    the inverse-factor recurrence alone;   fit_gmax_kinv=..  the K^-1 product alone
+//   fit_gmax=7|8|9       slice-pair cut-off of every INT8 fit stage (default 8/7/7: potrf, trtri, K^-1)
+//   fit_gmax_trtri=..    the inverse factor alone;   fit_gmax_kinv=..  the K^-1 product alone
 // Everything else that used to be switchable (stream priorities, K* staging, look-ahead, schedule thresholds) was an
 // A/B question of round 1 and is settled; the measurements are under profiles/r1_*.
 // ---------------------------------------------------------------------------------------------
 struct DebugConfig {
     bool fit_dmma = false;
-    int fit_gmax[3] = {8, 8, 7};
+    int fit_gmax[3] = {8, 7, 7};
 };
 const DebugConfig& debug_config();
 void debug_config_reload();

@@ -845,12 +845,20 @@ struct FitBuffers {
 
 // slice products kept by the fit GEMMs, per stage: 9 (34 products, truncation 2^-64: below FP64 rounding), 8 (28
 // products, 2^-56: the size of FP64 rounding itself) or 7 (21 products, 2^-48).  Defaults: Cholesky column update 8 (its
-// error is amplified by the rest of the factorisation: 7 costs three digits of the LML on ill-conditioned members),
-// inverse factor 8, K^-1 = Linv^T Linv 7 (feeds only the gradient: 1.7e-10 of max|grad|).  Measured against the FP64
-// DMMA path in profiles/r1_fit_precision.md.  TB200_DEBUG=fit_gmax=.. sets all three stages, fit_gmax_trtri /
-// fit_gmax_kinv one stage (common.cuh).
-enum FitStage { FIT_POTRF = 0, FIT_TRTRI = 1, FIT_KINV = 2 };
-static int fit_gmax(int stage) { return debug_config().fit_gmax[stage]; }
+// error is amplified by the rest of the factorisation: 7 costs three digits of the LML on ill-conditioned members,
+// 3.4e-9), inverse factor 7 (recursive inverse, round 2: worst LML difference 5e-11, gradient 3.9e-10 of max|grad| on
+// the hard members), K^-1 = Linv^T Linv 7 (feeds only the gradient: 1.6e-10 of max|grad|).  Measured against the FP64
+// DMMA path in profiles/r1_fit_precision.md and profiles/r2_fit_precision.md (parity bars: 1e-6).
+// TB200_DEBUG=fit_gmax=.. sets all three stages, fit_gmax_trtri / fit_gmax_kinv one stage (common.cuh).
+// FIT_TRTRI_MODEL: the inverse factor of a model that will PREDICT (tb200_factor, or any LML-only evaluation): never below
+// 28 products.  With 21 the predictive mean of an ill-conditioned model (n = 12400, d = 3) moved by 2.8e-7 against the
+// FP64 DMMA path (tests/test_gpu_i8.py); the 21-product inverse is for the optimiser's LML+gradient evaluations only.
+enum FitStage { FIT_POTRF = 0, FIT_TRTRI = 1, FIT_KINV = 2, FIT_TRTRI_MODEL = 3 };
+static int fit_gmax(int stage) {
+    const DebugConfig& c = debug_config();
+    if (stage == FIT_TRTRI_MODEL) return c.fit_gmax[FIT_TRTRI] < 8 ? 8 : c.fit_gmax[FIT_TRTRI];
+    return c.fit_gmax[stage];
+}
 static int fit_sm_count() {  // CTAs of a persistent grid: one per SM of the current device
     static int sms[MAX_DEVICES] = {};
     int dev = 0;
@@ -1148,7 +1156,7 @@ __global__ void __launch_bounds__(256) place_diag_blocks_kernel(const double* __
 // and column maxima of the inverse; T's column maxima per level), so no pass over the matrix measures anything.
 // All scalings are powers of two: nothing is rounded outside the kept slice pairs, as in ozaki_gemm.cuh.
 // On exit fb.scale holds the column covers of Linv -- the operand scaling of the K^-1 = Linv^T Linv step that follows.
-static int trtri_batched_i8(const FitBuffers& fb, double* Linv, int NP, int R, cudaStream_t st) {
+static int trtri_batched_i8(const FitBuffers& fb, double* Linv, int NP, int R, int stage, cudaStream_t st) {
     const int NB = NP / TILE, kblks = NP / i8::KB;
     const long sK = (long)NP * NP, sD = (long)NB * TILE * TILE;
     const long total = (long)R * NP;
@@ -1182,24 +1190,25 @@ static int trtri_batched_i8(const FitBuffers& fb, double* Linv, int NP, int R, c
         // T = L[C, A] inv(A), written where X will be
         g.recur = 1; g.scale = fb.scale; g.scaleB = fb.colcov; g.alpha = 1.0;
         g.rowmax32 = nullptr; g.colmax32 = tmax32;
-        if (launch_fit_gemm_i8(fb, g, ntiles, R, st, FIT_TRTRI)) return -1;
+        if (launch_fit_gemm_i8(fb, g, ntiles, R, st, stage)) return -1;
         TB_LAUNCH(cover32_kernel, dim3(cgrid), dim3(256), 0, st, tmax32, total, tcov);
         TB_LAUNCH(slice_level_kernel<2>, sgrid, dim3(256), 0, st, Linv, NP, sK, tcov, h64, npairs, fb.sliced, sK,
                   (long)i8::S * sK, kblks);
         // X = -inv(C) T
         g.recur = 2; g.scale = fb.rowcov; g.scaleB = tcov; g.alpha = -1.0;
         g.rowmax32 = rowmax32; g.colmax32 = colmax32;
-        if (launch_fit_gemm_i8(fb, g, ntiles, R, st, FIT_TRTRI)) return -1;
+        if (launch_fit_gemm_i8(fb, g, ntiles, R, st, stage)) return -1;
     }
     TB_LAUNCH(cover32_kernel, dim3(cgrid), dim3(256), 0, st, colmax32, total, fb.scale);
     return 0;
 }
 
 // Linv = L^-1 for R factors, from the inverted diagonal blocks; GEMM only
-static int trtri_batched(const FitBuffers& fb, double* Linv, int NP, int R, cudaStream_t st) {
+static int trtri_batched(const FitBuffers& fb, double* Linv, int NP, int R, bool for_model, cudaStream_t st) {
     const int NB = NP / TILE;
     const long sK = (long)NP * NP, sD = (long)NB * TILE * TILE;
-    if (fit_uses_i8(NP, R) && fb.sliced != nullptr) return trtri_batched_i8(fb, Linv, NP, R, st);
+    if (fit_uses_i8(NP, R) && fb.sliced != nullptr)
+        return trtri_batched_i8(fb, Linv, NP, R, for_model ? FIT_TRTRI_MODEL : FIT_TRTRI, st);
     if (use_left_looking(NB, R)) {
         // row block i:  X[i,c] = -Dinv_i * sum_{k=c}^{i-1} L[i,k] X[k,c]  (c < i),  X[i,i] = Dinv_i
         TB_CUDA(cudaMemsetAsync(Linv, 0, sizeof(double) * (size_t)R * NP * NP, st));
@@ -1273,7 +1282,7 @@ static int fit_pipeline(const double* X, const double* y_n, int n, const tb200_k
     TB_LAUNCH(gram_train_kernel, dim3(nt64, R), dim3(256), gsm, st, XsT, n, NP, spec, theta, p, jitter, fb.K);
     if (potrf_batched(fb, NP, R, info, st)) return -1;
     TB_LAUNCH(logdet_kernel, dim3(R), dim3(256), 0, st, fb.K, NP, Ldiag, fb.logdet);
-    if (trtri_batched(fb, Linv, NP, R, st)) return -1;
+    if (trtri_batched(fb, Linv, NP, R, !with_grad, st)) return -1;
     TB_LAUNCH(trmv_lower_kernel, dim3(NP / 8, R), dim3(256), 0, st, Linv, NP, fb.ypad, 0L, fb.z);
     TB_LAUNCH(trmv_lower_t_kernel, dim3(NP / 64, R), dim3(256), 0, st, Linv, NP, fb.z, alpha);
     TB_LAUNCH(lml_kernel, dim3(R), dim3(256), 0, st, fb.ypad, 0L, alpha, NP, n, fb.logdet, info, lml);
