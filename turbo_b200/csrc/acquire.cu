@@ -1186,18 +1186,24 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
     // n=1024, d=6 the step is K*-bound and four direct-load CTAs per SM beat three staged ones (5.49e7 vs 5.00e7 /s).
     int staged_ctas = 0, staged_nc = 8;
     if (use_i8 && NP >= 2048) {
-        // at most two staged CTAs per SM: a third costs the variance kernel more than it gains (379.5 vs 375.5 ms per
-        // step at n=4096, d=10, round 1)
-        auto fit_of = [&](int nc) {
+        // Three CTAs of the 128-point chunk where they fit (d <= 12) -- with the integer-pipe epilogue of the persistent
+        // variance kernel the FP64 pipe belongs to K* alone and a third CTA pays: 308.0 vs 310.8 ms per step at n=4096,
+        // d=10 (a fourth: 308.2; round 1, when the variance epilogue competed for the FP64 pipe, a third CTA lost,
+        // 379.5 vs 375.5 ms).  Otherwise two CTAs: the 256-point chunk, or the 128-point chunk where only that fits twice.
+        auto fit_of = [&](int nc, int cap) {
             if ((NP + ks_chunk(nc) - 1) / ks_chunk(nc) > KS_STAGED_SPLITS) return 0;
             const int f = (int)((57 * 1024) / (kstar_staged_smem(d, nc) + 1024));
-            return f < 2 ? f : 2;
+            return f < cap ? f : cap;
         };
-        const int f8 = fit_of(8), f16 = fit_of(16);
-        // the 256-point chunk unless only the 128-point chunk fits twice (d = 11..21)
-        staged_nc = (f8 < 2 && f16 >= 2) ? 16 : 8;
-        const int f = staged_nc == 16 ? f16 : f8;
-        if (f >= 2) staged_ctas = f;
+        if (fit_of(16, 3) >= 3) {
+            staged_nc = 16;
+            staged_ctas = 3;
+        } else {
+            const int f8 = fit_of(8, 2), f16 = fit_of(16, 2);
+            staged_nc = (f8 < 2 && f16 >= 2) ? 16 : 8;
+            const int f = staged_nc == 16 ? f16 : f8;
+            if (f >= 2) staged_ctas = f;
+        }
     }
     const int staged_splits = (NP + ks_chunk(staged_nc) - 1) / ks_chunk(staged_nc);
     const int mean_splits = staged_ctas ? staged_splits : ksplit;
