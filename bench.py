@@ -440,15 +440,7 @@ def run_ours(args):
         for f in acq_objs:
             if world > 1:
                 a2 = device.Acquirer(model.factor, f._spec_c(), args.batch, engine=args.engine)
-                copy_stream, main = torch.cuda.Stream(), torch.cuda.current_stream()
-                for off in range(0, m, 1 << 18):
-                    cnt = min(1 << 18, m - off)
-                    with torch.cuda.stream(copy_stream):
-                        buf = Xc_host[off:off + cnt].to(device.device(), non_blocking=True)
-                        ev = torch.cuda.Event(); ev.record(copy_stream)
-                    main.wait_event(ev)
-                    a2.run(buf, cnt, lo_i + off, None)
-                    buf.record_stream(main)
+                a2.run_host(Xc_host, lo_i)
                 v, i = a2.best()
                 res.append(dist.allreduce_argmax(v, i, group))
             else:

@@ -81,23 +81,8 @@ class _DeviceFunction:
             if host.numel() * 8 >= (1 << 20) and not host.is_pinned():
                 host = host.pin_memory()
             # stream the shard in chunks: H2D of chunk i+1 overlaps the kernels of chunk i
-            copy_stream = torch.cuda.Stream()
-            main = torch.cuda.current_stream()
-            pending = None
             tops = []
-            for off in range(0, hi_i - lo_i, chunk):
-                cnt = min(chunk, hi_i - lo_i - off)
-                with torch.cuda.stream(copy_stream):
-                    buf = host[off:off + cnt].to(device.device(), non_blocking=True)
-                    ev = torch.cuda.Event()
-                    ev.record(copy_stream)
-                main.wait_event(ev)
-                a.run(buf, cnt, lo_i + off, None)
-                if keep_top:
-                    tops.append(a.local_bests())
-                buf.record_stream(main)
-                pending = buf
-            del pending
+            a.run_host(host, lo_i, chunk, (lambda: tops.append(a.local_bests())) if keep_top else None)
             cand_c = None
         else:
             mode = {'uniform': _lib.CAND_UNIFORM, 'lhs': _lib.CAND_LHS}[generator]

@@ -261,6 +261,41 @@ class Acquirer:
             C.byref(self.acq_c), _lib.ptr(mu), _lib.ptr(sigma), _lib.ptr(acq), _lib.ptr(self.best_val),
             _lib.ptr(self.best_idx), self.batch, _lib.ptr(self.work), self.nbytes, _lib.stream_ptr()))
 
+    def run_host(self, host, index_base=0, chunk=1 << 18, after_chunk=None):
+        """candidates from a (pinned) host tensor (m,d), streamed in chunks: the H2D copy of chunk i+1 overlaps the
+        kernels of chunk i.  TWO device buffers are allocated once and reused under events -- a fresh allocation per
+        chunk went through the caching allocator with `record_stream`, whose deferred frees made the end-to-end time
+        depend on the allocator's state (6.8e6 candidates/s in one run, 4.9e6 in the next).  after_chunk(): optional
+        callback after each chunk's kernels are queued (the polish stage collects the local bests there)."""
+        m, d = host.shape
+        if m == 0:
+            return
+        dev = device()
+        rows = min(int(chunk), m)
+        nchunks = (m + rows - 1) // rows
+        bufs = [torch.empty((rows, d), dtype=torch.float64, device=dev) for _ in range(min(2, nchunks))]
+        used = [None] * len(bufs)  # event after the kernels that read the buffer
+        copy_stream, main = torch.cuda.Stream(), torch.cuda.current_stream()
+        copy_stream.wait_stream(main)  # the buffers were allocated in main's stream order
+        for ci in range(nchunks):
+            off = ci * rows
+            cnt = min(rows, m - off)
+            b = bufs[ci % len(bufs)]
+            with torch.cuda.stream(copy_stream):
+                if used[ci % len(bufs)] is not None:
+                    copy_stream.wait_event(used[ci % len(bufs)])
+                b[:cnt].copy_(host[off:off + cnt], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(copy_stream)
+            main.wait_event(ev)
+            self.run(b, cnt, index_base + off, None)
+            if after_chunk is not None:
+                after_chunk()
+            done = torch.cuda.Event()
+            done.record(main)
+            used[ci % len(bufs)] = done
+        # the last user of every buffer is a kernel on `main`: freeing them in main's stream order is safe
+
     def best(self):
         """(value, global index); index -1 when nothing was selectable (all NaN / empty)"""
         return float(self.best_val.item()), int(self.best_idx.item())
