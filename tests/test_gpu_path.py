@@ -70,6 +70,35 @@ def test_fused_argmax_equals_evaluate_then_argmax():
             assert idx == O.argmax_first(ref)
 
 
+def test_host_candidates_streamed_in_chunks_through_two_buffers():
+    """argmax_over(candidates=host array) streams chunks through two reusable device buffers (Acquirer.run_host): ragged
+    chunk sizes, more chunks than buffers, a pinned torch tensor or a NumPy array -- always the oracle's argmax."""
+    import turbo_b200 as tb
+    rng = np.random.default_rng(8)
+    X = rng.random((150, 3))
+    y = np.cos(4 * X.sum(1))
+    spec = tb.KernelSpec(3, 3, True)
+    theta = np.log([0.9, 0.3, 0.4, 0.5, 1e-4])
+    model = _fixed_model(spec, theta, X, y)
+    acq = tb.GpuEI(0.01).construct_function(0, model, "min", float(y.min()))[0]
+    m = 3001
+    cands = rng.random((m, 3))
+    mu, sd = O.FittedGP(O.KernelSpec(3, 3, True), theta, X, y).predict(cands)
+    ref = O.acquisition(O.ACQ_EI, mu, sd, acq.scale_factor, float(y.min()), 0.01)
+    want = O.argmax_first(ref)
+    pinned = torch.from_numpy(cands.copy()).pin_memory()
+    for src in (cands, pinned):
+        for chunk in (1 << 18, 1000, 777, 128, m):
+            val, idx, x = acq.argmax_over(candidates=src, chunk=chunk, batch=256)
+            assert idx == want, (chunk, idx, want)
+            assert val == pytest.approx(ref[want], rel=1e-8)
+            np.testing.assert_array_equal(x, cands[want:want + 1])
+    # the top list of the polish stage is collected per chunk
+    val, idx, x, (tv, ti, tx) = acq.argmax_over(candidates=cands, chunk=500, batch=256, keep_top=4)
+    assert idx == want and ti[0] == want and len(set(ti.tolist())) == len(ti)
+    np.testing.assert_array_equal(tx, cands[ti])
+
+
 def test_argmax_edge_cases():
     import turbo_b200 as tb
     X = np.array([[0.1], [0.5], [0.9]])

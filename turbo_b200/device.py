@@ -46,10 +46,14 @@ def lml_batched(X_dev, yn_dev, n, spec, thetas, jitter, with_grad=True):
     thetas = np.ascontiguousarray(np.atleast_2d(thetas), dtype=np.float64)
     R, p = thetas.shape
     assert p == spec.p
-    free_bytes = torch.cuda.mem_get_info()[0] + torch.cuda.memory_reserved() - torch.cuda.memory_allocated()
     chunk = R
-    while chunk > 1 and lib.tb200_fit_workspace_bytes(n, spec.d, chunk, int(with_grad)) > 0.8 * free_bytes:
-        chunk = (chunk + 1) // 2
+    need = lib.tb200_fit_workspace_bytes(n, spec.d, R, int(with_grad))
+    # the driver is asked for the free memory only when the working set is a large part of the device: cudaMemGetInfo
+    # on the call path of every evaluation showed up as 2x outliers in the 8-process timing of the fit
+    if need > 0.2 * torch.cuda.get_device_properties(torch.cuda.current_device()).total_memory:
+        free_bytes = torch.cuda.mem_get_info()[0] + torch.cuda.memory_reserved() - torch.cuda.memory_allocated()
+        while chunk > 1 and lib.tb200_fit_workspace_bytes(n, spec.d, chunk, int(with_grad)) > 0.8 * free_bytes:
+            chunk = (chunk + 1) // 2
     if chunk < R:
         parts = [lml_batched(X_dev, yn_dev, n, spec, thetas[o:o + chunk], jitter, with_grad) for o in range(0, R, chunk)]
         return (np.concatenate([q[0] for q in parts]),
