@@ -1180,12 +1180,13 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
     // the INT8 K* kernel covers 256 points per pass of its 128 threads: a shorter chunk would idle half of them
     if (use_i8 && jchunk < 2 * TILE) jchunk = 2 * TILE;
     ksplit = (NP + jchunk - 1) / jchunk;
-    // staged K* kernel (training-point chunk in shared memory): 2048 <= n <= 4096 and at least two CTAs of it fit into
+    // staged K* kernel (training-point chunk in shared memory): 1024 <= n <= 4096 and at least two CTAs of it fit into
     // the ~57 KB the variance kernel leaves on an SM.  Measured
-    // (profiles/r1_kstar_ncu_full.md): n=4096, d=10 (variance-bound step) 388.8 -> 376.2 ms per 2^21 candidates; at
-    // n=1024, d=6 the step is K*-bound and four direct-load CTAs per SM beat three staged ones (5.49e7 vs 5.00e7 /s).
+    // (profiles/r1_kstar_ncu_full.md): n=4096, d=10 (variance-bound step) 388.8 -> 376.2 ms per 2^21 candidates.  (In
+    // round 1, with 256-point chunks, four direct-load CTAs per SM beat three staged ones at n=1024, d=6: 5.49e7 vs
+    // 5.00e7 /s; with 128-point chunks the staged kernel wins there too, see below.)
     int staged_ctas = 0, staged_nc = 8;
-    if (use_i8 && NP >= 2048) {
+    if (use_i8 && NP >= 1024) {
         // Three CTAs of the 128-point chunk where they fit (d <= 12) -- with the integer-pipe epilogue of the persistent
         // variance kernel the FP64 pipe belongs to K* alone and a third CTA pays: 308.0 vs 310.8 ms per step at n=4096,
         // d=10 (a fourth: 308.2; round 1, when the variance epilogue competed for the FP64 pipe, a third CTA lost,
@@ -1195,9 +1196,12 @@ static int acquire_impl(const double* Xc, int64_t m, int64_t index_base, const t
             const int f = (int)((57 * 1024) / (kstar_staged_smem(d, nc) + 1024));
             return f < cap ? f : cap;
         };
-        if (fit_of(16, 3) >= 3) {
+        // n < 2048 (the step is K*-bound there): up to four -- cfg2 (n=1024, d=6) 6.60e7 candidates/s against 6.55e7 with
+        // three and 6.39e7 with four CTAs of the direct-load kernel (tools/gpu_round2_z.sh)
+        const int cap = NP < 2048 ? 4 : 3;
+        if (fit_of(16, cap) >= 3) {
             staged_nc = 16;
-            staged_ctas = 3;
+            staged_ctas = fit_of(16, cap);
         } else {
             const int f8 = fit_of(8, 2), f16 = fit_of(16, 2);
             staged_nc = (f8 < 2 && f16 >= 2) ? 16 : 8;
