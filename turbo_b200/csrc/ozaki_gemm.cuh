@@ -246,22 +246,31 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_i8_kernel(const GemmI8Params 
             const bool want_max = g.final && (p.rowmax32 != nullptr || p.colmax32 != nullptr);
             unsigned rmax = 0;
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-#pragma unroll 1
+            // Phase 1: drain.  All 64 columns are recombined (integer pipe + a few FP64 additions) into registers and
+            // TMEM goes back to the MMA warp BEFORE the tile is scaled, merged with C and stored: with short k-ranges
+            // (the triangular products of the inverse: 16 k-blocks on average) the FP64 store phase was a fifth of a
+            // tile's time during which the tensor pipe waited (ncu: 63 % busy, profiles/r2_gemm_i8_large_ncu.md).
+            double v[TN];
+#pragma unroll
             for (int cc = 0; cc < TN / 8; ++cc) {
                 uint32_t r[NG][8];
 #pragma unroll
                 for (int gg = 0; gg < NG; ++gg) tmem_ld8(lane_base + gg * TN + cc * 8, r[gg]);
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                if (cc == TN / 8 - 1) {  // the accumulators are in registers: the next tile's MMAs may start
-                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-                    mbar_arrive(&tfree_bar);
-                }
+#pragma unroll
+                for (int c = 0; c < 8; ++c) v[cc * 8 + c] = recombine<NG>(r, c);
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            mbar_arrive(&tfree_bar);  // the accumulators are in registers: the next tile's MMAs may start
+            // Phase 2: scale, merge, store, maxima
+#pragma unroll
+            for (int cc = 0; cc < TN / 8; ++cc) {
                 double out[8];
 #pragma unroll
                 for (int c = 0; c < 8; ++c) {
                     // both operands carry digits b_s 2^(1-8s): group g = i+j has weight 2^(2-8g), smallest first;
                     // recombine() weighs with 2^(1-8g), the missing factor 2 is exact
-                    out[c] = recombine<NG>(r, c) * (2.0 * srow * __ldg(scol + cc * 8 + c));
+                    out[c] = v[cc * 8 + c] * (2.0 * srow * __ldg(scol + cc * 8 + c));
                 }
                 double2* dst = reinterpret_cast<double2*>(crow + cc * 8);
                 if (beta != 0.0) {
