@@ -669,7 +669,7 @@ def fit_block(args, cfg, model, spec, theta, X, y, rank, world, group, barrier):
     flop = float(n) ** 3 + float(n) ** 2 * (3 * d + 42)
     fit = {"lml_grad_batched_ms": min(fit_ms[1:]), "lml_grad_batched_ms_samples": [round(v, 3) for v in fit_ms[1:]],
            "restarts": R, "restarts_per_gpu": Rl,
-           "engine": "i8 (potrf column updates, trtri, K^-1 on tcgen05 kind::i8, 28/28/21 slice products) when the batch is "
+           "engine": "i8 (potrf column updates, trtri, K^-1 on tcgen05 kind::i8, 28/21/21 slice products) when the batch is "
                      "large enough for the left-looking schedule, else FP64 DMMA; TB200_DEBUG=fit_engine=dmma forces DMMA",
            "flop_per_evaluation": flop, "tflops": Rl * flop / (min(fit_ms[1:]) * 1e-3) / 1e12,
            "final_factor_ms": e0.elapsed_time(e1), "all_finite": bool(np.isfinite(lml).all())}
